@@ -1,0 +1,350 @@
+// oracle/ref_api.cpp -- TEST INFRASTRUCTURE ONLY (never on the product path).
+//
+// A thin extern "C" face over the UNMODIFIED reference sources where they lie under
+// /root/reference (nothing is copied into this repo).  Built by oracle/Makefile into
+// oracle/_ref/libhcref.so.  Used to (1) pin oracle/edge_oracle.c against the real
+// NewEdgeCalculator, (2) generate the golden fixtures under tests/golden/, and (3) time the
+// reference's own CPU scorer for bench.py's reference arm / cpu_baseline.
+//
+// The reference CLI translation unit is included whole (the reference's own unit test does the
+// same: test/unit/unit1.cpp:11-12), which gives us readBamFile (src/haploclique.cpp:143) and
+// the CLI entry as HaploMain.
+#define main HaploMain
+#include "haploclique.cpp"
+#undef main
+
+#include <atomic>
+#include <chrono>
+#include <cstring>
+#include <thread>
+
+namespace {
+
+struct RefCtx {
+    std::vector<AlignmentRecord*> recs;   // position-sorted arrival order
+    std::vector<std::string> names;       // readNameMap storage
+    std::unordered_map<std::string, AlignmentRecord*> open_mates;
+    NewEdgeCalculator* calc = nullptr;
+    // parameters kept so worker threads can build their own calculator
+    // (edgeBetween clears a mutable member: src/NewEdgeCalculator.h:43, .cpp:1265).
+    double Q = 0.9, cut_cliques = 0.99, ov_cliques = 0.9, cut_single = 0.95, ov_single = 0.6, cut_mixed = 0.97;
+    bool frameshift = false, no_prob0 = false;
+    unsigned max_position = 0;
+    size_t maxpos_done = 0;
+    std::unordered_map<int, double> simpson;
+    std::string err;
+    ~RefCtx() {
+        for (auto* r : recs) delete r;
+        for (auto& kv : open_mates) delete kv.second;
+        delete calc;
+    }
+    NewEdgeCalculator* make_calc() {
+        return new NewEdgeCalculator(Q, cut_cliques, ov_cliques, frameshift, simpson, cut_single, ov_single,
+                                     cut_mixed, max_position, no_prob0);
+    }
+};
+
+std::vector<BamTools::CigarOp> rle(const char* cig, int n) {
+    std::vector<BamTools::CigarOp> out;
+    for (int i = 0; i < n;) {
+        int j = i;
+        while (j < n && cig[j] == cig[i]) ++j;
+        out.push_back(BamTools::CigarOp(cig[i], (uint32_t)(j - i)));
+        i = j;
+    }
+    return out;
+}
+
+// The interval tests edgeBetween applies before the walk (src/NewEdgeCalculator.cpp:1252-1365),
+// restated so the harness knows for which pairs calling the public checkGapsCigar is defined.
+bool prefilter_pass(const AlignmentRecord& a, const AlignmentRecord& b) {
+    const auto& c1 = a.getCovmap();
+    const auto& c2 = b.getCovmap();
+    if (c1.back().ref < c2[0].ref || c2.back().ref < c1[0].ref) return false;
+    bool se1 = a.isSingleEnd(), se2 = b.isSingleEnd();
+    unsigned e11 = a.getEnd1(), s11 = a.getStart1(), e21 = b.getEnd1(), s21 = b.getStart1();
+    if (se1 && se2) {
+        if (e11 < s21) return false;
+        if (e21 < s11) return false;
+    } else if (!se1 && !se2) {
+        unsigned e12 = a.getEnd2(), s12 = a.getStart2(), e22 = b.getEnd2(), s22 = b.getStart2();
+        if (e11 < s21 && e12 < s22) return false;
+        if (e21 < s11 && e22 < s12) return false;
+        if (e21 < s12 && e12 < s22) return false;
+        if (e11 < s22 && e22 < s12) return false;
+        if (e21 < s11 && e11 < s22) return false;
+        if (e11 < s21 && e21 < s12) return false;
+    } else if (se1 && !se2) {
+        unsigned e22 = b.getEnd2(), s22 = b.getStart2();
+        if (e11 < s21) return false;
+        if (e21 < s11 && e11 < s22) return false;
+        if (e22 < s11) return false;
+    } else {
+        unsigned e12 = a.getEnd2(), s12 = a.getStart2();
+        if (e12 < s21) return false;
+        if (e11 < s21 && e21 < s12) return false;
+        if (e21 < s11) return false;
+    }
+    return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+void* hcref_new() { return new RefCtx(); }
+void hcref_free(void* p) { delete static_cast<RefCtx*>(p); }
+const char* hcref_error(void* p) { return static_cast<RefCtx*>(p)->err.c_str(); }
+
+// Runs the unmodified CLI (src/haploclique.cpp:203) with argv; cwd decides where the FASTA lands.
+int hcref_cli(int argc, char** argv) { return HaploMain(argc, argv); }
+
+// readBamFile (src/haploclique.cpp:143-201): mate pairing, leftover order and the sort included.
+int hcref_load_bam(void* p, const char* path) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    try {
+        BamTools::SamHeader header;
+        BamTools::RefVector refs;
+        unsigned maxpos = 0;
+        std::deque<AlignmentRecord*>* reads = readBamFile(path, c->names, maxpos, header, refs);
+        for (auto* r : *reads) c->recs.push_back(r);
+        delete reads;
+        c->max_position = std::max(c->max_position, maxpos);
+    } catch (const std::exception& e) {
+        c->err = e.what();
+        return -1;
+    }
+    return (int)c->recs.size();
+}
+
+// One alignment in BAM order, handled as the loop body of readBamFile does (:160-175):
+// first sight of a name -> new record, second sight -> pairWith + push.
+int hcref_add_alignment(void* p, const char* name, int pos0, const char* cigar_unrolled, int ncig,
+                        const char* bases, const char* quals, int nq) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    BamTools::BamAlignment al;
+    al.Name = name;
+    al.Position = pos0;
+    al.CigarData = rle(cigar_unrolled, ncig);
+    al.QueryBases.assign(bases, nq);
+    al.Qualities.assign(quals, nq);
+    al.Length = nq;
+    bool valid = false;
+    for (auto& op : al.CigarData) if (op.Type == 'M' && op.Length > 0) valid = true;
+    if (!valid) return 0;
+    auto it = c->open_mates.find(al.Name);
+    if (it != c->open_mates.end()) {
+        it->second->pairWith(al);
+        c->recs.push_back(it->second);
+        c->open_mates.erase(it);
+    } else {
+        c->open_mates[al.Name] = new AlignmentRecord(al, (int)c->names.size(), &c->names);
+        c->names.push_back(al.Name);
+    }
+    return 1;
+}
+
+// End of readBamFile: leftovers appended, optional sort by interval start, max_position (:178-198).
+int hcref_finish_load(void* p, int do_sort) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    for (auto& kv : c->open_mates) c->recs.push_back(kv.second);
+    c->open_mates.clear();
+    if (do_sort) {
+        std::sort(c->recs.begin(), c->recs.end(), [](AlignmentRecord* a, AlignmentRecord* b) {
+            return a->getIntervalStart() < b->getIntervalStart();
+        });
+    }
+    for (size_t k = c->maxpos_done; k < c->recs.size(); ++k)
+        c->max_position = std::max(c->max_position, c->recs[k]->getIntervalEnd());
+    c->maxpos_done = do_sort ? 0 : c->recs.size();
+    return (int)c->recs.size();
+}
+
+// Unit-test fixture loader (src/AlignmentRecord.cpp:2346), appended in call order.
+int hcref_restore_fixture(void* p, const char* path) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    AlignmentRecord* r = new AlignmentRecord();
+    r->restoreCompleteAlignmentRecord(path);
+    c->recs.push_back(r);
+    return (int)c->recs.size() - 1;
+}
+
+int hcref_n(void* p) { return (int)static_cast<RefCtx*>(p)->recs.size(); }
+unsigned hcref_max_position(void* p) { return static_cast<RefCtx*>(p)->max_position; }
+
+// out[12]: single_end,start1,end1,start2,end2,ncig1,nq1,ncig2,nq2,ncov,cov_first,cov_last
+int hcref_record_info(void* p, int i, int* out, char* name, int name_cap) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    const AlignmentRecord& r = *c->recs[i];
+    bool se = r.isSingleEnd();
+    out[0] = se;
+    out[1] = r.getStart1();
+    out[2] = r.getEnd1();
+    out[3] = se ? 0 : r.getStart2();
+    out[4] = se ? 0 : r.getEnd2();
+    out[5] = (int)r.getCigar1Unrolled().size();
+    out[6] = (int)r.getSequence1().size();
+    out[7] = se ? 0 : (int)r.getCigar2Unrolled().size();
+    out[8] = se ? 0 : (int)r.getSequence2().size();
+    const auto& cov = r.getCovmap();
+    out[9] = (int)cov.size();
+    out[10] = cov.empty() ? 0 : cov.front().ref;
+    out[11] = cov.empty() ? 0 : cov.back().ref;
+    std::string nm = r.getName();
+    std::snprintf(name, name_cap, "%s", nm.c_str());
+    return 0;
+}
+
+int hcref_record_data(void* p, int i, char* cig1, char* seq1, char* qual1, char* cig2, char* seq2, char* qual2) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    const AlignmentRecord& r = *c->recs[i];
+    const auto& c1 = r.getCigar1Unrolled();
+    std::memcpy(cig1, c1.data(), c1.size());
+    std::memcpy(seq1, r.getSequence1().toString().data(), r.getSequence1().size());
+    std::memcpy(qual1, r.getSequence1().qualityString().data(), r.getSequence1().size());
+    if (!r.isSingleEnd()) {
+        const auto& c2 = r.getCigar2Unrolled();
+        std::memcpy(cig2, c2.data(), c2.size());
+        std::memcpy(seq2, r.getSequence2().toString().data(), r.getSequence2().size());
+        std::memcpy(qual2, r.getSequence2().qualityString().data(), r.getSequence2().size());
+    }
+    return 0;
+}
+
+// NewEdgeCalculator construction (src/NewEdgeCalculator.h:58; call site src/haploclique.cpp:304).
+// max_position < 0 keeps the value derived while loading.
+int hcref_set_params(void* p, double Q, double cut_cliques, double ov_cliques, int frameshift,
+                     const int* simpson_pos, const double* simpson_val, int n_simpson, double cut_single,
+                     double ov_single, double cut_mixed, long max_position, int no_prob0) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    c->Q = Q; c->cut_cliques = cut_cliques; c->ov_cliques = ov_cliques; c->frameshift = frameshift != 0;
+    c->cut_single = cut_single; c->ov_single = ov_single; c->cut_mixed = cut_mixed; c->no_prob0 = no_prob0 != 0;
+    c->simpson.clear();
+    for (int i = 0; i < n_simpson; ++i) c->simpson[simpson_pos[i]] = simpson_val[i];
+    if (max_position >= 0) c->max_position = (unsigned)max_position;
+    delete c->calc;
+    c->calc = c->make_calc();
+    return 0;
+}
+
+// edgeBetween(records[i], records[j]) (src/NewEdgeCalculator.cpp:1247).
+int hcref_edge(void* p, int i, int j) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    return c->calc->edgeBetween(*c->recs[i], *c->recs[j]) ? 1 : 0;
+}
+
+int hcref_prefilter(void* p, int i, int j) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    return prefilter_pass(*c->recs[i], *c->recs[j]) ? 1 : 0;
+}
+
+// The walk alone through the public checkGapsCigar (src/NewEdgeCalculator.h:72), with the same
+// initial state edgeBetween gives it (:1256-1259). Only defined when the prefilter passes.
+int hcref_pair_detail(void* p, int i, int j, int* gap, int* cc, int* tc, double* probM, double* prob0) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    if (!prefilter_pass(*c->recs[i], *c->recs[j])) return 0;
+    int tcv = 0, ccv = 0;
+    double pm = 1.0, p0 = 0.0;
+    bool g = c->calc->checkGapsCigar(*c->recs[i], *c->recs[j], pm, p0, ccv, tcv);
+    *gap = g; *cc = ccv; *tc = tcv; *probM = pm; *prob0 = p0;
+    return 1;
+}
+
+// All ordered pairs (i = later arrival, j < i), CLEVER's order (src/CLEVER.cpp:218-232).
+// edge[k], and for prefilter-passing pairs the walk outputs; k enumerates (i,j) row-major over i>j.
+// Arrays may be null. Returns number of edges.
+long hcref_score_all(void* p, unsigned char* edge, unsigned char* pre, unsigned char* gap, int* cc, int* tc,
+                     double* probM, double* prob0) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    long n = (long)c->recs.size(), k = 0, edges = 0;
+    for (long i = 0; i < n; ++i) {
+        for (long j = 0; j < i; ++j, ++k) {
+            bool e = c->calc->edgeBetween(*c->recs[i], *c->recs[j]);
+            edges += e;
+            if (edge) edge[k] = e;
+            bool pf = prefilter_pass(*c->recs[i], *c->recs[j]);
+            if (pre) pre[k] = pf;
+            if (pf && (gap || cc || tc || probM || prob0)) {
+                int tcv = 0, ccv = 0; double pm = 1.0, p0 = 0.0;
+                bool g = c->calc->checkGapsCigar(*c->recs[i], *c->recs[j], pm, p0, ccv, tcv);
+                if (gap) gap[k] = g;
+                if (cc) cc[k] = ccv;
+                if (tc) tc[k] = tcv;
+                if (probM) probM[k] = pm;
+                if (prob0) prob0[k] = p0;
+            }
+        }
+    }
+    return edges;
+}
+
+// Times edgeBetween over an explicit pair list on `threads` host threads, one calculator per
+// thread. Returns seconds; *edges_out = number of edges found; edge_out (optional) per pair.
+double hcref_time_pairs(void* p, const int* pi, const int* pj, long npairs, int threads, long* edges_out,
+                        unsigned char* edge_out) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    if (threads < 1) threads = 1;
+    std::vector<NewEdgeCalculator*> calcs;
+    for (int t = 0; t < threads; ++t) calcs.push_back(c->make_calc());
+    std::atomic<long> total(0);
+    auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; ++t) {
+        pool.emplace_back([&, t]() {
+            long lo = npairs * t / threads, hi = npairs * (t + 1) / threads, e = 0;
+            for (long k = lo; k < hi; ++k) {
+                bool r = calcs[t]->edgeBetween(*c->recs[pi[k]], *c->recs[pj[k]]);
+                e += r;
+                if (edge_out) edge_out[k] = r;
+            }
+            total += e;
+        });
+    }
+    for (auto& th : pool) th.join();
+    auto t1 = std::chrono::steady_clock::now();
+    for (auto* q : calcs) delete q;
+    if (edges_out) *edges_out = total.load();
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
+// One pass of the CLI's main loop body (src/haploclique.cpp:349-372) with CLEVER or BronKerbosch:
+// consumes the current records, replaces them by the collector's position-sorted super-reads.
+// state[0]=ct (in/out), state[1]=edges (out), state[2]=converged (out); stdev in/out.
+int hcref_iterate(void* p, int use_bk, int filter_singletons, double significance, int* state, double* stdev,
+                  const char* logfile) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    int ct = state[0];
+    std::vector<unsigned int> read_clique_counter(c->names.size());
+    LogWriter* lw = (logfile && logfile[0]) ? new LogWriter(logfile, read_clique_counter) : nullptr;
+    CliqueCollector collector(lw);
+    CliqueFinder* finder;
+    if (use_bk) finder = new BronKerbosch(*c->calc, collector, lw);
+    else finder = new CLEVER(*c->calc, collector, lw, 0, 0, c->names.size(), filter_singletons != 0);
+    finder->initialize();
+    if (lw) lw->initialize();
+    int size = (int)c->recs.size();
+    int edgecounter = 0;
+    double sd = *stdev;
+    for (auto* r : c->recs) {
+        std::unique_ptr<AlignmentRecord> al(r);
+        bool drop = (ct == 1 && filter_singletons && al->getReadCount() <= 1) ||
+                    (ct > 1 && significance != 0.0 && al->getProbability() < 1.0 / size - significance * sd);
+        if (drop) continue;
+        finder->addAlignment(al, edgecounter);
+    }
+    c->recs.clear();
+    finder->finish();
+    std::deque<AlignmentRecord*>* next = collector.finish();
+    if (lw) lw->finish();
+    *stdev = setProbabilities(*next);
+    for (auto* r : *next) c->recs.push_back(r);
+    delete next;
+    state[0] = ct + 1;
+    state[1] = edgecounter;
+    state[2] = finder->hasConverged() ? 1 : 0;
+    delete finder;
+    delete lw;
+    return (int)c->recs.size();
+}
+
+}  // extern "C"
