@@ -1,0 +1,791 @@
+// hc_gpu.cu -- sm_100a kernels and the CUDA half of the C ABI (include/hc_edge.h).
+//
+// What one "pair" is: the decision NewEdgeCalculator::edgeBetween(ap1, ap2) makes
+// (reference src/NewEdgeCalculator.cpp:1247-1376) for ap1 = the later arrival, ap2 = an earlier read.
+// The reference walks two unrolled CIGARs in lock step; here every read is a run of 16-bit op records
+// (op | base | quality code) so one load per side per column step feeds the classification, the base
+// compare and the probability-table index. The fp64 match product is formed with one __dmul_rn per
+// shared column in increasing reference order, exactly the reference's order, so probM is bit-identical
+// (including its underflow to 0 on long weak overlaps).
+//
+// Layouts (which segment of which read is walked against which, and up to where) are rows of a small
+// phase-program table in constant memory; one interpreter runs them. Row numbering and bound ids are
+// defined below; each row cites the reference lines it stands for.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "hc_internal.h"
+
+namespace {
+
+// ---- bound ids: ext*8 + side*4 + seg*2 + is_end; side 0 = ap1 ("A"), 1 = ap2 ("B") -------------------
+#define BID(ext, side, seg, is_end) ((ext) * 8 + (side) * 4 + (seg) * 2 + (is_end))
+enum : uint8_t {
+    As1 = BID(0, 0, 0, 0), Ae1 = BID(0, 0, 0, 1), As2 = BID(0, 0, 1, 0), Ae2 = BID(0, 0, 1, 1),
+    Bs1 = BID(0, 1, 0, 0), Be1 = BID(0, 1, 0, 1), Bs2 = BID(0, 1, 1, 0), Be2 = BID(0, 1, 1, 1),
+    xAs1 = BID(1, 0, 0, 0), xAe1 = BID(1, 0, 0, 1), xAs2 = BID(1, 0, 1, 0), xAe2 = BID(1, 0, 1, 1),
+    xBs1 = BID(1, 1, 0, 0), xBe1 = BID(1, 1, 0, 1), xBs2 = BID(1, 1, 1, 0), xBe2 = BID(1, 1, 1, 1)
+};
+
+// ---- phase programs ---------------------------------------------------------------------------------
+enum : uint8_t {
+    PH_END = 0,
+    PH_START,    // ref = v[a]
+    PH_TAIL_LT,  // while (ref <  v[a]) tail step on (side x, seg y)
+    PH_TAIL_LE,  // while (ref <= v[a]) tail step on (side x, seg y)
+    PH_OVL,      // while (ref <= v[a]) lock step A.seg x / B.seg y
+    PH_OVL2,     // while (ref <= v[a] && ref <= v[b]) lock step
+    PH_OVL2_QX,  // same, but ap1's bases are indexed by the untouched query cursor of ap1's other segment (:629)
+    PH_SEAT,     // cursor of (side x, seg y) skips the leading clips (computeSOffset)
+    PH_FIN       // if (ref-1 == v[a]) tail owner(b) to v[b]; else if (ref-1 == v[b]) tail owner(a) to v[a]
+};
+struct Phase { uint8_t op, x, y, a, b; };
+#define P_START(a) {PH_START, 0, 0, a, 0}
+#define P_TLT(sd, sg, a) {PH_TAIL_LT, sd, sg, a, 0}
+#define P_TLE(sd, sg, a) {PH_TAIL_LE, sd, sg, a, 0}
+#define P_OVL(sa, sb, a) {PH_OVL, sa, sb, a, 0}
+#define P_OVL2(sa, sb, a, b) {PH_OVL2, sa, sb, a, b}
+#define P_OVLQX(sa, sb, a, b) {PH_OVL2_QX, sa, sb, a, b}
+#define P_SEAT(sd, sg) {PH_SEAT, sd, sg, 0, 0}
+#define P_FIN(a, b) {PH_FIN, 0, 0, a, b}
+#define P_END {PH_END, 0, 0, 0, 0}
+#define MAXPH 12
+enum { PROG_PP0 = 0, PROG_PS0 = 12, PROG_SP0 = 14, N_PROGS = 16 };
+
+__constant__ Phase c_prog[N_PROGS][MAXPH] = {
+    // paired x paired, checkGapsPaired branches 2..13 (src/NewEdgeCalculator.cpp)
+    /* :444 */ {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), P_OVL(1, 0, Be1),
+                P_TLT(0, 1, Bs2), P_SEAT(1, 1), P_OVL2(1, 1, xBe2, xAe2), P_FIN(xBe2, xAe2), P_END},
+    /* :482 */ {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1),
+                P_OVL2(1, 0, xBe1, xAe2), P_FIN(xBe1, xAe2), P_END},
+    /* :513 */ {P_START(xBs1), P_TLT(1, 0, xAs2), P_OVL(1, 0, Be1), P_TLT(0, 1, Bs2), P_SEAT(1, 1),
+                P_OVL2(1, 1, xBe2, xAe2), P_FIN(xBe2, xAe2), P_END},
+    /* :543 */ {P_START(xAs2), P_TLT(0, 1, xBs1), P_OVL(1, 0, Be1), P_TLT(0, 1, Bs2), P_SEAT(1, 1),
+                P_OVL2(1, 1, xAe2, xBe2), P_FIN(xAe2, xBe2), P_END},
+    /* :574 */ {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), P_OVL(0, 1, Ae1),
+                P_TLT(1, 1, As2), P_SEAT(0, 1), P_OVL2(1, 1, xBe2, xAe2), P_FIN(xBe2, xAe2), P_END},
+    /* :613 */ {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1),
+                P_OVLQX(0, 1, xAe1, xBe2), P_FIN(xAe1, xBe2), P_END},
+    /* :646 */ {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), P_OVL(1, 0, Be1),
+                P_TLT(0, 1, Bs2), P_SEAT(1, 1), P_OVL2(1, 1, xAe2, xBe2), P_FIN(xAe2, xBe2), P_END},
+    /* :684 */ {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1),
+                P_OVL2(1, 0, xBe1, xAe2), P_FIN(xBe1, xAe2), P_END},
+    /* :714 */ {P_START(xAs1), P_TLT(0, 0, xBs2), P_OVL(0, 1, Ae1), P_TLT(1, 1, As2), P_SEAT(0, 1),
+                P_OVL2(1, 1, xAe2, xBe2), P_FIN(xAe2, xBe2), P_END},
+    /* :744 */ {P_START(xBs2), P_TLT(1, 1, xAs1), P_OVL(0, 1, Ae1), P_TLT(1, 1, As2), P_SEAT(0, 1),
+                P_OVL2(1, 1, xAe2, xBe2), P_FIN(xAe2, xBe2), P_END},
+    /* :774 */ {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), P_OVL(0, 1, Ae1),
+                P_TLT(1, 1, As2), P_SEAT(0, 1), P_OVL2(1, 1, xBe2, xAe2), P_FIN(xBe2, xAe2), P_END},
+    /* :813 */ {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1),
+                P_OVL2(0, 1, xAe1, xBe2), P_FIN(xAe1, xBe2), P_END},
+    // ap1 paired x ap2 single-end, checkGapsMixed (:893, :922)
+    {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), P_OVL2(1, 0, xAe2, xBe1),
+     P_FIN(xAe2, xBe1), P_END},
+    {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), P_OVL2(1, 0, xAe2, xBe1),
+     P_FIN(xAe2, xBe1), P_END},
+    // ap1 single-end x ap2 paired, checkGapsMixed (:993, :1025)
+    {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), P_OVL2(0, 1, xBe2, xAe1),
+     P_FIN(xBe2, xAe1), P_END},
+    {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), P_OVL2(0, 1, xBe2, xAe1),
+     P_FIN(xBe2, xAe1), P_END},
+};
+
+// ---- scoring parameters on the device ----------------------------------------------------------------
+struct DevParams {
+    double log_cutoff[3];      // log10 of {cliques, mixed, single} cutoffs, host libm (:1112-1116)
+    double min_overlap[2];     // {cliques, single}
+    double log10_quarter;      // std::log10(0.25) from host libm (:140)
+    double amb_tol;
+    const double* table;       // [2][K][K]: equal-base block, then unequal-base block
+    const double* simpson;     // dense map or nullptr
+    const double* ladder;      // F[n] = n sequential additions of log10(0.25)
+    int K, KK;
+    int simpson_len;
+    int ladder_len;
+    int no_prob0;
+};
+
+struct PairOut {
+    int status, edge, gap, cc, tc, ambiguous;
+    double probM, prob0, score, cutoff;
+};
+
+// classification of an op pair in the lock step (overlapCheckgap, :173-231)
+enum { ACT_SCORE = 0, ACT_SKIP = 1, ACT_ADV_A = 2, ACT_ADV_B = 3, ACT_GAP = 4 };
+__device__ __forceinline__ int op_action(int oa, int ob) {
+    // rows oa = M I D S H, cols ob = M I D S H, 3 bits each
+    //  M: S G G K K | I: G S G A A | D: G G K K K | S: K B K K K | H: K B K K K   (S=score K=skip A/B=advance one G=gap)
+    const unsigned long long lo =
+        (0ull << 0) | (4ull << 3) | (4ull << 6) | (1ull << 9) | (1ull << 12) |          // M row
+        (4ull << 15) | (0ull << 18) | (4ull << 21) | (2ull << 24) | (2ull << 27) |      // I row
+        (4ull << 30) | (4ull << 33) | (1ull << 36) | (1ull << 39) | (1ull << 42) |      // D row
+        (1ull << 45) | (3ull << 48) | (1ull << 51) | (1ull << 54) | (1ull << 57) |      // S row
+        (1ull << 60);                                                                   // H,M
+    const unsigned hi = (3u << 0) | (1u << 3) | (1u << 6) | (1u << 9);                  // H,I H,D H,S H,H
+    const int idx = oa * 5 + ob;
+    return idx < 21 ? (int)((lo >> (3 * idx)) & 7ull) : (int)((hi >> (3 * (idx - 21))) & 7u);
+}
+
+struct Seg {
+    const uint16_t* ops;
+    int n;
+};
+
+struct WalkState {
+    int ref;
+    int cc, tc;
+    double probM, prob0;
+    bool undefined;
+};
+
+__device__ __forceinline__ bool consumes_query(int op) { return op == HC_OP_M || op == HC_OP_I || op == HC_OP_S; }
+
+// noOverlapCheckgap loop (:234-267): columns only one read covers. limit is exclusive.
+__device__ __forceinline__ void tail_loop(const DevParams& P, WalkState& w, const Seg s, int& c, int limit) {
+    while (w.ref < limit) {
+        if (c >= s.n) { w.undefined = true; return; }
+        const int op = s.ops[c] >> HC_OP_SHIFT;
+        if (op == HC_OP_M || op == HC_OP_I) {
+            w.tc++;
+            if (P.simpson != nullptr) {                                        // computeProb0 (:133-143)
+                double d = 0.0;
+                if (w.ref < 0 || w.ref >= P.simpson_len) {
+                    // the reference reads SIMPSON_MAP out of bounds here; harmless only when prob0 is ignored (:1132)
+                    if (!P.no_prob0) { w.undefined = true; return; }
+                } else {
+                    d = __ldg(P.simpson + w.ref);
+                }
+                w.prob0 = __dadd_rn(w.prob0, d != 0.0 ? d : P.log10_quarter);
+            }
+        }
+        if (op != HC_OP_I) w.ref++;
+        c++;
+    }
+}
+
+// overlapCheckgap loop (:145-232): columns both reads cover. hi is inclusive. Returns true on gap conflict.
+template <bool QX>
+__device__ __forceinline__ bool ovl_loop(const DevParams& P, WalkState& w, const Seg A, int& ca, const Seg B, int& cb,
+                                         int hi) {
+    int cq = 0;   // QX only: op index in A of the base the reference's stray query cursor points at
+    if (QX) {
+        while (cq < A.n && !consumes_query(A.ops[cq] >> HC_OP_SHIFT)) cq++;
+    }
+    while (w.ref <= hi) {
+        if (ca >= A.n || cb >= B.n) { w.undefined = true; return false; }
+        const unsigned ra = A.ops[ca], rb = B.ops[cb];
+        const int oa = ra >> HC_OP_SHIFT, ob = rb >> HC_OP_SHIFT;
+        const int act = ((ra | rb) >> HC_OP_SHIFT) == 0 ? ACT_SCORE : op_action(oa, ob);
+        if (act == ACT_SCORE) {
+            unsigned sa = ra;
+            if (QX) {
+                if (cq >= A.n) { w.undefined = true; return false; }
+                sa = A.ops[cq];
+            }
+            const int idx = (int)(sa & 127u) * P.K + (int)(rb & 127u) + ((((sa ^ rb) >> HC_BASE_SHIFT) & 7u) ? P.KK : 0);
+            w.probM = __dmul_rn(w.probM, __ldg(P.table + idx));                // computeProbM (:122-131)
+            w.cc++;
+            if (oa == HC_OP_M) w.ref++;
+            ca++; cb++;
+            if (QX) { cq++; while (cq < A.n && !consumes_query(A.ops[cq] >> HC_OP_SHIFT)) cq++; }
+        } else if (act == ACT_SKIP) {
+            w.ref++; ca++; cb++;
+            if (QX && consumes_query(oa)) { cq++; while (cq < A.n && !consumes_query(A.ops[cq] >> HC_OP_SHIFT)) cq++; }
+        } else if (act == ACT_ADV_A) {
+            ca++;
+            if (QX) { cq++; while (cq < A.n && !consumes_query(A.ops[cq] >> HC_OP_SHIFT)) cq++; }
+        } else if (act == ACT_ADV_B) {
+            cb++;
+        } else {
+            return true;
+        }
+    }
+    return false;
+}
+
+struct PairCtx {
+    Seg seg[2][2];     // [side][segment]
+    int cur[2][2];     // CIGAR cursors
+    int lead[2][2];    // leading clip count (raw start - ext start)
+    int v[16];         // bounds by id
+};
+
+// Runs one phase program. Returns true on gap conflict.
+__device__ bool run_program(const DevParams& P, WalkState& w, PairCtx& pc, const Phase* __restrict__ pg) {
+    for (int k = 0; k < MAXPH; ++k) {
+        const Phase ph = pg[k];
+        switch (ph.op) {
+            case PH_END: return false;
+            case PH_START: w.ref = pc.v[ph.a]; break;
+            case PH_TAIL_LT: tail_loop(P, w, pc.seg[ph.x][ph.y], pc.cur[ph.x][ph.y], pc.v[ph.a]); break;
+            case PH_TAIL_LE: tail_loop(P, w, pc.seg[ph.x][ph.y], pc.cur[ph.x][ph.y], pc.v[ph.a] + 1); break;
+            case PH_SEAT: pc.cur[ph.x][ph.y] += pc.lead[ph.x][ph.y]; break;
+            case PH_OVL:
+                if (ovl_loop<false>(P, w, pc.seg[0][ph.x], pc.cur[0][ph.x], pc.seg[1][ph.y], pc.cur[1][ph.y], pc.v[ph.a]))
+                    return true;
+                break;
+            case PH_OVL2:
+                if (ovl_loop<false>(P, w, pc.seg[0][ph.x], pc.cur[0][ph.x], pc.seg[1][ph.y], pc.cur[1][ph.y],
+                                    min(pc.v[ph.a], pc.v[ph.b])))
+                    return true;
+                break;
+            case PH_OVL2_QX:
+                if (ovl_loop<true>(P, w, pc.seg[0][ph.x], pc.cur[0][ph.x], pc.seg[1][ph.y], pc.cur[1][ph.y],
+                                   min(pc.v[ph.a], pc.v[ph.b])))
+                    return true;
+                break;
+            case PH_FIN: {
+                int which = -1;                                   // bound id whose owner still has columns left
+                if (w.ref - 1 == pc.v[ph.a]) which = ph.b;
+                else if (w.ref - 1 == pc.v[ph.b]) which = ph.a;
+                if (which >= 0) {
+                    const int sd = (which >> 2) & 1, sg = (which >> 1) & 1;
+                    tail_loop(P, w, pc.seg[sd][sg], pc.cur[sd][sg], pc.v[which] + 1);
+                }
+                break;
+            }
+        }
+        if (w.undefined) return false;
+    }
+    return false;
+}
+
+// checkGapsSingle (:269-395): segment sa of ap1 against segment sb of ap2 with fresh cursors.
+__device__ bool walk_single(const DevParams& P, WalkState& w, PairCtx& pc, int sa, int sb) {
+    const int xs1 = pc.v[BID(1, 0, sa, 0)], xe1 = pc.v[BID(1, 0, sa, 1)];
+    const int xs2 = pc.v[BID(1, 1, sb, 0)], xe2 = pc.v[BID(1, 1, sb, 1)];
+    int ca = 0, cb = 0;
+    const Seg A = pc.seg[0][sa], B = pc.seg[1][sb];
+    // the reference's four shapes in order (:331, :346, :361, :376); together they are exhaustive
+    int shape;
+    if (xs1 <= xs2 && xe1 <= xe2) shape = 0;
+    else if (xs1 <= xs2 && xe1 >= xe2) shape = 1;
+    else if (xs1 >= xs2 && xe1 <= xe2) shape = 2;
+    else shape = 3;
+    if (shape < 2) { w.ref = xs1; tail_loop(P, w, A, ca, xs2); }
+    else { w.ref = xs2; tail_loop(P, w, B, cb, xs1); }
+    if (w.undefined) return false;
+    const int ovl_hi = (shape == 0 || shape == 2) ? xe1 : xe2;
+    if (ovl_loop<false>(P, w, A, ca, B, cb, ovl_hi)) return true;
+    if (w.undefined) return false;
+    if (shape == 0 || shape == 2) tail_loop(P, w, B, cb, xe2 + 1);
+    else tail_loop(P, w, A, ca, xe1 + 1);
+    return false;
+}
+
+// The interval rejects in front of the walk (:1268-1365). true = rejected.
+__device__ __forceinline__ bool layout_reject(bool se1, bool se2, const int* v) {
+    if (se1 && se2) return v[Ae1] < v[Bs1] || v[Be1] < v[As1];
+    if (!se1 && !se2)
+        return (v[Ae1] < v[Bs1] && v[Ae2] < v[Bs2]) || (v[Be1] < v[As1] && v[Be2] < v[As2]) ||
+               (v[Be1] < v[As2] && v[Ae2] < v[Bs2]) || (v[Ae1] < v[Bs2] && v[Be2] < v[As2]) ||
+               (v[Be1] < v[As1] && v[Ae1] < v[Bs2]) || (v[Ae1] < v[Bs1] && v[Be1] < v[As2]);
+    if (se1) return v[Ae1] < v[Bs1] || (v[Be1] < v[As1] && v[Ae1] < v[Bs2]) || v[Be2] < v[As1];
+    return v[Ae2] < v[Bs1] || (v[Ae1] < v[Bs1] && v[Be1] < v[As2]) || v[Be1] < v[As1];
+}
+
+// checkGapsCigar dispatch (:1063-1074) and the layout choice inside checkGapsPaired/Mixed.
+__device__ bool walk_pair(const DevParams& P, WalkState& w, PairCtx& pc, bool se1, bool se2) {
+    const int* v = pc.v;
+    if (se1 && se2) return walk_single(P, w, pc, 0, 0);
+    if (!se1 && !se2) {
+        if (v[Ae1] < v[Bs2] && v[As2] > v[Be1]) {                                      // :436
+            if (walk_single(P, w, pc, 0, 0)) return true;
+            if (w.undefined) return false;
+            return walk_single(P, w, pc, 1, 1);
+        }
+        int k = -1;
+        if      (v[xAs1] <= v[xBs1] && v[Ae1] >= v[Bs1] && v[As2] <= v[Be1] && v[Ae2] >= v[Bs2]) k = 0;
+        else if (v[xAs1] <= v[xBs1] && v[Ae1] >= v[Bs1] && v[As2] <= v[Be1] && v[Ae2] <  v[Bs2]) k = 1;
+        else if (v[xBs1] <= v[xAs2] && v[Ae1] <  v[Bs1] && v[As2] <= v[Be1] && v[Ae2] >= v[Bs2]) k = 2;
+        else if (v[xAs2] <= v[xBs1] && v[Ae1] <  v[Bs1] && v[As2] <= v[Be1] && v[Ae2] >= v[Bs2]) k = 3;
+        else if (v[xAs1] <= v[xBs1] && v[As1] <= v[Be1] && v[Ae1] >= v[Bs2] && v[As2] <= v[Be2]) k = 4;
+        else if (v[xAs1] <= v[xBs1] && v[As2] >  v[Be2] && v[Ae1] >= v[Bs2] && v[As1] <= v[Be1]) k = 5;
+        else if (v[xBs1] <= v[xAs1] && v[Ae1] >= v[Bs1] && v[As2] <= v[Be1] && v[Ae2] >= v[Bs2]) k = 6;
+        else if (v[xBs1] <= v[xAs1] && v[Ae1] >= v[Bs1] && v[As2] <= v[Be1] && v[Ae2] <  v[Bs2]) k = 7;
+        else if (v[xAs1] <= v[xBs2] && v[As1] >  v[Be1] && v[Ae1] >= v[Bs2] && v[As2] <= v[Be2]) k = 8;
+        else if (v[xBs2] <= v[xAs1] && v[Be1] <  v[As1] && v[Ae1] >= v[Bs2] && v[As2] <= v[Be2]) k = 9;
+        else if (v[xBs1] <= v[xAs1] && v[As1] <= v[Be1] && v[Ae1] >= v[Bs2] && v[As2] <= v[Be2]) k = 10;
+        else if (v[xBs1] <= v[xAs1] && v[As2] >  v[Be2] && v[As1] <= v[Be1] && v[Ae1] >= v[Bs2]) k = 11;
+        if (k < 0) return false;                      // no layout matches: cc stays 0 (:841-844 under NDEBUG)
+        return run_program(P, w, pc, c_prog[PROG_PP0 + k]);
+    }
+    if (se2) {                                        // ap1 paired, ap2 single-end (:850-954)
+        if (v[Be1] < v[As2]) return walk_single(P, w, pc, 0, 0);
+        if (v[Bs1] > v[Ae1]) return walk_single(P, w, pc, 1, 0);
+        return run_program(P, w, pc, c_prog[PROG_PS0 + (v[xBs1] <= v[xAs1] ? 0 : 1)]);
+    }
+    if (v[Ae1] < v[Bs2]) return walk_single(P, w, pc, 0, 0);   // ap1 single-end, ap2 paired (:955-1056)
+    if (v[As1] > v[Be1]) return walk_single(P, w, pc, 0, 1);
+    return run_program(P, w, pc, c_prog[PROG_SP0 + (v[xAs1] <= v[xBs1] ? 0 : 1)]);
+}
+
+// edgeBetween (:1247-1376) + similarityCriterion (:1107-1141) for ap1 = hdr[i], ap2 = hdr[j].
+__device__ void score_pair(const DevParams& P, const hc_read_hdr* __restrict__ hdr, const uint16_t* __restrict__ ops,
+                           int i, int j, PairOut& o) {
+    o.status = HC_ST_REJECT_COV; o.edge = 0; o.gap = 0; o.cc = 0; o.tc = 0; o.ambiguous = 0;
+    o.probM = 1.0; o.prob0 = 0.0; o.score = __longlong_as_double(0x7ff8000000000000ll); o.cutoff = 0.0;
+    // headers: 64 B each, four 16-B loads
+    const int4* ha = reinterpret_cast<const int4*>(hdr + i);
+    const int4* hb = reinterpret_cast<const int4*>(hdr + j);
+    const int4 a3 = __ldg(ha + 3), b3 = __ldg(hb + 3);     // ncov_flags, cov_first, cov_last, has_ins
+    if (a3.z < b3.y || b3.z < a3.y) return;                 // covered intervals disjoint (:1252)
+    PairCtx pc;
+    const int4 a0 = __ldg(ha), a1 = __ldg(ha + 1), a2 = __ldg(ha + 2);
+    const int4 b0 = __ldg(hb), b1 = __ldg(hb + 1), b2 = __ldg(hb + 2);
+    pc.v[0] = a0.x; pc.v[1] = a0.y; pc.v[2] = a0.z; pc.v[3] = a0.w;
+    pc.v[4] = b0.x; pc.v[5] = b0.y; pc.v[6] = b0.z; pc.v[7] = b0.w;
+    pc.v[8] = a1.x; pc.v[9] = a1.y; pc.v[10] = a1.z; pc.v[11] = a1.w;
+    pc.v[12] = b1.x; pc.v[13] = b1.y; pc.v[14] = b1.z; pc.v[15] = b1.w;
+    const unsigned fa = (unsigned)a3.x, fb = (unsigned)b3.x;
+    const bool se1 = fa & HC_FLAG_SINGLE_END, se2 = fb & HC_FLAG_SINGLE_END;
+    if (layout_reject(se1, se2, pc.v)) { o.status = HC_ST_REJECT_LAYOUT; return; }
+    pc.seg[0][0] = Seg{ops + (unsigned)a2.x, a2.z};
+    pc.seg[0][1] = Seg{ops + (unsigned)a2.y, a2.w};
+    pc.seg[1][0] = Seg{ops + (unsigned)b2.x, b2.z};
+    pc.seg[1][1] = Seg{ops + (unsigned)b2.y, b2.w};
+    pc.lead[0][0] = a0.x - a1.x; pc.lead[0][1] = a0.z - a1.z;
+    pc.lead[1][0] = b0.x - b1.x; pc.lead[1][1] = b0.z - b1.z;
+    pc.cur[0][0] = pc.cur[0][1] = pc.cur[1][0] = pc.cur[1][1] = 0;
+    WalkState w;
+    w.ref = 0; w.cc = 0; w.tc = 0; w.probM = 1.0; w.prob0 = 0.0; w.undefined = false;
+    const bool gap = walk_pair(P, w, pc, se1, se2);
+    if (P.simpson == nullptr && !w.undefined) {
+        if (w.tc >= P.ladder_len) w.undefined = true;
+        else w.prob0 = __ldg(P.ladder + w.tc);        // tc sequential additions of log10(0.25)
+    }
+    o.gap = gap; o.cc = w.cc; o.tc = w.tc; o.probM = w.probM; o.prob0 = w.prob0;
+    if (w.undefined) { o.status = HC_ST_UNDEFINED; return; }
+    o.status = HC_ST_WALKED;
+    if (gap || w.cc == 0) return;                     // :1367, :1371
+    const bool cl1 = fa & HC_FLAG_IS_CLIQUE, cl2 = fb & HC_FLAG_IS_CLIQUE;
+    const int sel = (cl1 && cl2) ? 0 : ((cl1 || cl2) ? 1 : 2);
+    const double cutoff = P.log_cutoff[sel];
+    const double min_overlap = P.min_overlap[(cl1 && cl2) ? 0 : 1];
+    const unsigned smaller = min(fa & 0x3fffffffu, fb & 0x3fffffffu);
+    o.cutoff = cutoff;
+    if ((double)w.cc <= __dmul_rn(min_overlap, (double)smaller)) return;      // :1127
+    double prob, potence;
+    if (P.no_prob0) { prob = log10(w.probM); potence = __ddiv_rn(1.0, (double)w.cc); }
+    else { prob = __dadd_rn(log10(w.probM), w.prob0); potence = __ddiv_rn(1.0, (double)(w.cc + w.tc)); }
+    const double score = __dmul_rn(prob, potence);    // :1139
+    o.score = score;
+    o.edge = score >= cutoff;
+    o.ambiguous = fabs(score - cutoff) <= P.amb_tol * fabs(cutoff);
+}
+
+// ---- kernels ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) score_pairs_kernel(DevParams P, const hc_read_hdr* __restrict__ hdr,
+                                                         const uint16_t* __restrict__ ops, const int32_t* __restrict__ pi,
+                                                         const int32_t* __restrict__ pj, long long npairs,
+                                                         hc_pair_result* __restrict__ out) {
+    for (long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x; k < npairs; k += (long long)gridDim.x * blockDim.x) {
+        PairOut o;
+        score_pair(P, hdr, ops, pi[k], pj[k], o);
+        hc_pair_result r;
+        r.status = o.status; r.edge = o.edge; r.gap = o.gap; r.cc = o.cc; r.tc = o.tc; r.ambiguous = o.ambiguous;
+        r.probM = o.probM; r.prob0 = o.prob0; r.score = o.score;
+        out[k] = r;
+    }
+}
+
+struct BandStatsDev {
+    unsigned long long pairs_total, pairs_scored, pairs_walked, edges, sum_cc, sum_tc, undefined, ambiguous;
+};
+
+__device__ __forceinline__ unsigned long long warp_sum(unsigned long long x) {
+    for (int d = 16; d > 0; d >>= 1) x += __shfl_down_sync(0xffffffffu, x, d);
+    return x;
+}
+
+// One warp per 32-bit adjacency word: the 32 lanes hold 32 consecutive earlier reads j against the same
+// later read i, so ap1's header and op records are a broadcast and the edge bits come out of one ballot.
+__global__ void __launch_bounds__(256) score_band_kernel(DevParams P, const hc_read_hdr* __restrict__ hdr,
+                                                        const uint16_t* __restrict__ ops, int row_begin, int nrows,
+                                                        const int32_t* __restrict__ col0,
+                                                        const long long* __restrict__ word_off, long long total_words,
+                                                        uint32_t* __restrict__ adj, BandStatsDev* __restrict__ stats,
+                                                        hc_ambiguous* __restrict__ amb, int amb_cap) {
+    const int lane = threadIdx.x & 31;
+    const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    unsigned long long n_total = 0, n_scored = 0, n_walked = 0, n_edges = 0, s_cc = 0, s_tc = 0, n_undef = 0;
+    for (long long wd = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; wd < total_words; wd += warps) {
+        int lo = 0, hi = nrows;                       // last row with word_off[row] <= wd
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (word_off[mid] <= wd) lo = mid; else hi = mid;
+        }
+        const int i = row_begin + lo;
+        const int j = col0[lo] + (int)(wd - word_off[lo]) * 32 + lane;
+        bool edge = false;
+        if (j < i) {
+            PairOut o;
+            score_pair(P, hdr, ops, i, j, o);
+            edge = o.edge;
+            n_total++;
+            n_scored += o.status != HC_ST_REJECT_COV;
+            if (o.status == HC_ST_WALKED) { n_walked++; s_cc += o.cc; s_tc += o.tc; }
+            n_undef += o.status == HC_ST_UNDEFINED;
+            if (o.ambiguous) {
+                const unsigned long long slot = atomicAdd(&stats->ambiguous, 1ull);
+                if (amb != nullptr && slot < (unsigned long long)amb_cap) {
+                    hc_ambiguous a;
+                    a.i = i; a.j = j; a.cc = o.cc; a.tc = o.tc; a.probM = o.probM; a.prob0 = o.prob0;
+                    a.score = o.score; a.cutoff = o.cutoff;
+                    amb[slot] = a;
+                }
+            }
+        }
+        const unsigned bits = __ballot_sync(0xffffffffu, edge);
+        if (lane == 0) adj[wd] = bits;
+        n_edges += edge;
+    }
+    n_total = warp_sum(n_total); n_scored = warp_sum(n_scored); n_walked = warp_sum(n_walked);
+    n_edges = warp_sum(n_edges); s_cc = warp_sum(s_cc); s_tc = warp_sum(s_tc); n_undef = warp_sum(n_undef);
+    if (lane == 0) {
+        atomicAdd(&stats->pairs_total, n_total); atomicAdd(&stats->pairs_scored, n_scored);
+        atomicAdd(&stats->pairs_walked, n_walked); atomicAdd(&stats->edges, n_edges);
+        atomicAdd(&stats->sum_cc, s_cc); atomicAdd(&stats->sum_tc, s_tc); atomicAdd(&stats->undefined, n_undef);
+    }
+}
+
+}  // namespace
+
+// ======================================= host side of the C ABI =======================================
+struct hc_ctx {
+    hc_params par{};
+    std::vector<double> simpson_host;
+    std::vector<double> eq, uneq;          // 127x127 each
+    int device = 0, sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // resident batch
+    int n_reads = 0, K = 0, max_ops = 0;
+    hc_read_hdr* d_hdr = nullptr;
+    uint16_t* d_ops = nullptr;
+    double* d_table = nullptr;
+    double* d_simpson = nullptr;
+    double* d_ladder = nullptr;
+    int ladder_len = 0;
+    std::vector<int32_t> cov_first, cov_last_pmax;   // host copies for the band layout
+    // band scratch (grown on demand)
+    int32_t* d_col0 = nullptr; long long* d_word_off = nullptr; size_t rows_cap = 0;
+    uint32_t* d_adj = nullptr; size_t adj_cap = 0;
+    BandStatsDev* d_stats = nullptr;
+    hc_ambiguous* d_amb = nullptr; int amb_cap = 0;
+    // pair-list scratch
+    int32_t* d_pi = nullptr; int32_t* d_pj = nullptr; hc_pair_result* d_res = nullptr; size_t pairs_cap = 0;
+    std::vector<int32_t> lay_col0; std::vector<long long> lay_off; int lay_begin = -1, lay_end = -1;
+    void* d_flush = nullptr; size_t flush_bytes = 0;
+    std::string err;
+};
+
+namespace {
+
+#define CU_TRY(ctx, call)                                                                      \
+    do {                                                                                       \
+        cudaError_t e__ = (call);                                                              \
+        if (e__ != cudaSuccess) {                                                              \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e__);                  \
+            return HC_E_CUDA;                                                                  \
+        }                                                                                      \
+    } while (0)
+
+template <class T>
+int grow(hc_ctx* c, T*& ptr, size_t& cap, size_t need) {
+    if (need <= cap && ptr) return HC_OK;
+    if (ptr) CU_TRY(c, cudaFree(ptr));
+    ptr = nullptr;
+    cap = 0;
+    const size_t n = std::max<size_t>(need + need / 8, 1024);
+    CU_TRY(c, cudaMalloc(reinterpret_cast<void**>(&ptr), n * sizeof(T)));
+    cap = n;
+    return HC_OK;
+}
+
+DevParams dev_params(const hc_ctx* c) {
+    DevParams P{};
+    P.log_cutoff[0] = std::log10(c->par.edge_quasi_cutoff_cliques);
+    P.log_cutoff[1] = std::log10(c->par.edge_quasi_cutoff_mixed);
+    P.log_cutoff[2] = std::log10(c->par.edge_quasi_cutoff_single);
+    P.min_overlap[0] = c->par.min_overlap_cliques;
+    P.min_overlap[1] = c->par.min_overlap_single;
+    P.log10_quarter = std::log10(0.25);
+    P.amb_tol = c->par.ambiguity_rel_tol > 0 ? c->par.ambiguity_rel_tol : 1e-12;
+    P.table = c->d_table;
+    P.simpson = c->d_simpson;
+    P.ladder = c->d_ladder;
+    P.K = c->K;
+    P.KK = c->K * c->K;
+    P.simpson_len = (int)c->simpson_host.size();
+    P.ladder_len = c->ladder_len;
+    P.no_prob0 = c->par.no_prob0;
+    return P;
+}
+
+int compute_layout(hc_ctx* c, int row_begin, int row_end) {
+    if (c->lay_begin == row_begin && c->lay_end == row_end) return HC_OK;
+    const int nrows = row_end - row_begin;
+    c->lay_col0.assign(nrows, 0);
+    c->lay_off.assign((size_t)nrows + 1, 0);
+    long long acc = 0;
+    for (int k = 0; k < nrows; ++k) {
+        const int i = row_begin + k;
+        // first j whose running maximum of cov_last reaches cov_first[i]; everything before it is disjoint
+        const auto it = std::lower_bound(c->cov_last_pmax.begin(), c->cov_last_pmax.begin() + i, c->cov_first[i]);
+        int lo = (int)(it - c->cov_last_pmax.begin());
+        lo &= ~31;
+        c->lay_col0[k] = lo;
+        c->lay_off[k] = acc;
+        acc += (i - lo + 31) / 32;
+    }
+    c->lay_off[nrows] = acc;
+    c->lay_begin = row_begin;
+    c->lay_end = row_end;
+    return HC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int hc_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char* hc_last_error(const hc_ctx* ctx) { return ctx ? ctx->err.c_str() : hc::global_error(); }
+
+int hc_create(const hc_params* params, hc_ctx** out) {
+    if (!params || !out) { hc::set_global_error("hc_create: null argument"); return HC_E_INVALID; }
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        hc::set_global_error("hc_create: no CUDA device (this library has no CPU scoring path)");
+        return HC_E_CUDA;
+    }
+    if (params->device < 0 || params->device >= ndev) { hc::set_global_error("hc_create: bad device ordinal"); return HC_E_INVALID; }
+    hc_ctx* c = new hc_ctx();
+    c->par = *params;
+    c->device = params->device;
+    if (params->simpson && params->simpson_len > 0) c->simpson_host.assign(params->simpson, params->simpson + params->simpson_len);
+    bool any = false;
+    for (double d : c->simpson_host) any |= (d != 0.0);
+    if (!any) c->simpson_host.clear();           // no entry set: every tail column adds log10(0.25)
+    c->par.simpson = nullptr;
+    c->eq.resize(127 * 127);
+    c->uneq.resize(127 * 127);
+    hc::build_match_tables(c->eq.data(), c->uneq.data());
+    auto fail = [&](const char* what, cudaError_t err) {
+        hc::set_global_error(std::string("hc_create: ") + what + ": " + cudaGetErrorString(err));
+        hc_destroy(c);
+        return HC_E_CUDA;
+    };
+    if ((e = cudaSetDevice(c->device)) != cudaSuccess) return fail("cudaSetDevice", e);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, c->device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
+    c->sm_count = prop.multiProcessorCount;
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaMalloc((void**)&c->d_stats, sizeof(BandStatsDev))) != cudaSuccess) return fail("cudaMalloc", e);
+    if (!c->simpson_host.empty()) {
+        const size_t bytes = c->simpson_host.size() * sizeof(double);
+        if ((e = cudaMalloc((void**)&c->d_simpson, bytes)) != cudaSuccess) return fail("cudaMalloc", e);
+        if ((e = cudaMemcpy(c->d_simpson, c->simpson_host.data(), bytes, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("cudaMemcpy", e);
+    }
+    *out = c;
+    return HC_OK;
+}
+
+void hc_destroy(hc_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaFree(c->d_hdr); cudaFree(c->d_ops); cudaFree(c->d_table); cudaFree(c->d_simpson); cudaFree(c->d_ladder);
+    cudaFree(c->d_col0); cudaFree(c->d_word_off); cudaFree(c->d_adj); cudaFree(c->d_stats); cudaFree(c->d_amb);
+    cudaFree(c->d_pi); cudaFree(c->d_pj); cudaFree(c->d_res); cudaFree(c->d_flush);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int hc_set_params(hc_ctx* c, const hc_params* p) {
+    if (!c || !p) return HC_E_INVALID;
+    const int dev = c->par.device;
+    c->par = *p;
+    c->par.device = dev;
+    c->par.simpson = nullptr;
+    return HC_OK;
+}
+
+int hc_l2_flush(hc_ctx* c) {
+    if (!c) return HC_E_INVALID;
+    CU_TRY(c, cudaSetDevice(c->device));
+    if (!c->d_flush) {
+        c->flush_bytes = (size_t)256 << 20;                      // 2x the 126 MB L2
+        CU_TRY(c, cudaMalloc(&c->d_flush, c->flush_bytes));
+    }
+    CU_TRY(c, cudaMemsetAsync(c->d_flush, 0x5a, c->flush_bytes, c->stream));
+    return HC_OK;
+}
+
+void* hc_host_alloc(int64_t bytes) {
+    void* p = nullptr;
+    if (bytes <= 0 || cudaHostAlloc(&p, (size_t)bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void hc_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int hc_get_tables(const hc_ctx* c, double* eq, double* uneq) {
+    if (!c || !eq || !uneq) return HC_E_INVALID;
+    std::memcpy(eq, c->eq.data(), sizeof(double) * 127 * 127);
+    std::memcpy(uneq, c->uneq.data(), sizeof(double) * 127 * 127);
+    return HC_OK;
+}
+
+int hc_upload(hc_ctx* c, const hc_packed* p) {
+    if (!c || !p) return HC_E_INVALID;
+    CU_TRY(c, cudaSetDevice(c->device));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    cudaFree(c->d_hdr); cudaFree(c->d_ops); cudaFree(c->d_table); cudaFree(c->d_ladder);
+    c->d_hdr = nullptr; c->d_ops = nullptr; c->d_table = nullptr; c->d_ladder = nullptr;
+    c->n_reads = p->n_reads;
+    c->K = std::max(p->n_qual_codes, 1);
+    c->max_ops = p->max_ops_per_read;
+    c->lay_begin = c->lay_end = -1;
+    const size_t nh = std::max(p->n_reads, 1);
+    CU_TRY(c, cudaMalloc((void**)&c->d_hdr, nh * sizeof(hc_read_hdr)));
+    CU_TRY(c, cudaMalloc((void**)&c->d_ops, ((size_t)p->n_ops_total + 64) * sizeof(uint16_t)));
+    CU_TRY(c, cudaMemcpyAsync(c->d_hdr, p->hdr, (size_t)p->n_reads * sizeof(hc_read_hdr), cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(c->d_ops, p->ops, ((size_t)p->n_ops_total + 64) * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
+    // probability tables re-indexed by quality code: [equal | unequal][code1][code2]
+    const int K = c->K;
+    std::vector<double> tab((size_t)2 * K * K, 0.0);
+    for (int a = 0; a < p->n_qual_codes; ++a)
+        for (int b = 0; b < p->n_qual_codes; ++b) {
+            const int qa = p->qual_chars[a], qb = p->qual_chars[b];
+            tab[(size_t)a * K + b] = c->eq[qa * 127 + qb];
+            tab[(size_t)K * K + (size_t)a * K + b] = c->uneq[qa * 127 + qb];
+        }
+    CU_TRY(c, cudaMalloc((void**)&c->d_table, tab.size() * sizeof(double)));
+    CU_TRY(c, cudaMemcpyAsync(c->d_table, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    std::vector<double> ladder;
+    c->ladder_len = 2 * c->max_ops + 2;
+    hc::build_prob0_ladder(ladder, c->ladder_len - 1);
+    CU_TRY(c, cudaMalloc((void**)&c->d_ladder, ladder.size() * sizeof(double)));
+    CU_TRY(c, cudaMemcpyAsync(c->d_ladder, ladder.data(), ladder.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    c->cov_first.resize(p->n_reads);
+    c->cov_last_pmax.resize(p->n_reads);
+    int run = INT32_MIN;
+    for (int r = 0; r < p->n_reads; ++r) {
+        c->cov_first[r] = p->hdr[r].cov_first;
+        run = std::max(run, p->hdr[r].cov_last);
+        c->cov_last_pmax[r] = run;
+    }
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    return HC_OK;
+}
+
+int hc_band_layout(hc_ctx* c, int32_t row_begin, int32_t row_end, int32_t* col0, int64_t* word_off, int64_t* n_words) {
+    if (!c) return HC_E_INVALID;
+    if (!c->d_hdr) { c->err = "hc_band_layout: no batch uploaded"; return HC_E_STATE; }
+    if (row_begin < 0 || row_end < row_begin || row_end > c->n_reads) { c->err = "hc_band_layout: bad row range"; return HC_E_INVALID; }
+    compute_layout(c, row_begin, row_end);
+    const int nrows = row_end - row_begin;
+    if (col0) std::memcpy(col0, c->lay_col0.data(), sizeof(int32_t) * nrows);
+    if (word_off) for (int k = 0; k <= nrows; ++k) word_off[k] = c->lay_off[k];
+    if (n_words) *n_words = c->lay_off[nrows];
+    return HC_OK;
+}
+
+int hc_score_band(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32_t* adj, int64_t n_words, hc_ambiguous* amb,
+                  int32_t amb_cap, hc_band_stats* stats) {
+    if (!c) return HC_E_INVALID;
+    if (!c->d_hdr) { c->err = "hc_score_band: no batch uploaded"; return HC_E_STATE; }
+    if (row_begin < 0 || row_end < row_begin || row_end > c->n_reads) { c->err = "hc_score_band: bad row range"; return HC_E_INVALID; }
+    CU_TRY(c, cudaSetDevice(c->device));
+    compute_layout(c, row_begin, row_end);
+    const int nrows = row_end - row_begin;
+    const long long total = c->lay_off[nrows];
+    if (adj && n_words < total) { c->err = "hc_score_band: adjacency buffer smaller than hc_band_layout's n_words"; return HC_E_INVALID; }
+    int rc;
+    size_t cap2 = c->rows_cap;
+    if ((rc = grow(c, c->d_col0, c->rows_cap, (size_t)nrows + 1)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_word_off, cap2, (size_t)nrows + 1)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_adj, c->adj_cap, (size_t)std::max<long long>(total, 1))) != HC_OK) return rc;
+    if (amb_cap > c->amb_cap) {
+        cudaFree(c->d_amb); c->d_amb = nullptr; c->amb_cap = 0;
+        CU_TRY(c, cudaMalloc((void**)&c->d_amb, (size_t)amb_cap * sizeof(hc_ambiguous)));
+        c->amb_cap = amb_cap;
+    }
+    CU_TRY(c, cudaMemcpyAsync(c->d_col0, c->lay_col0.data(), sizeof(int32_t) * nrows, cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(c->d_word_off, c->lay_off.data(), sizeof(long long) * ((size_t)nrows + 1), cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemsetAsync(c->d_stats, 0, sizeof(BandStatsDev), c->stream));
+    int launches = 0;
+    CU_TRY(c, cudaEventRecord(c->ev0, c->stream));
+    if (total > 0) {
+        const int threads = 256;
+        const long long want = (total + (threads / 32) - 1) / (threads / 32);
+        const int blocks = (int)std::min<long long>(want, (long long)c->sm_count * 8);
+        score_band_kernel<<<blocks, threads, 0, c->stream>>>(dev_params(c), c->d_hdr, c->d_ops, row_begin, nrows, c->d_col0,
+                                                             c->d_word_off, total, c->d_adj, c->d_stats,
+                                                             amb ? c->d_amb : nullptr, amb ? amb_cap : 0);
+        CU_TRY(c, cudaGetLastError());
+        launches = 1;
+    }
+    CU_TRY(c, cudaEventRecord(c->ev1, c->stream));
+    BandStatsDev hs{};
+    CU_TRY(c, cudaMemcpyAsync(&hs, c->d_stats, sizeof(hs), cudaMemcpyDeviceToHost, c->stream));
+    if (adj && total > 0) CU_TRY(c, cudaMemcpyAsync(adj, c->d_adj, (size_t)total * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    if (amb && amb_cap > 0 && hs.ambiguous > 0) {
+        const size_t k = (size_t)std::min<unsigned long long>(hs.ambiguous, (unsigned long long)amb_cap);
+        CU_TRY(c, cudaMemcpy(amb, c->d_amb, k * sizeof(hc_ambiguous), cudaMemcpyDeviceToHost));
+    }
+    if (stats) {
+        stats->pairs_total = (int64_t)hs.pairs_total; stats->pairs_scored = (int64_t)hs.pairs_scored;
+        stats->pairs_walked = (int64_t)hs.pairs_walked; stats->edges = (int64_t)hs.edges;
+        stats->sum_cc = (int64_t)hs.sum_cc; stats->sum_tc = (int64_t)hs.sum_tc; stats->undefined = (int64_t)hs.undefined;
+        stats->ambiguous = (int64_t)hs.ambiguous;
+        float ms = 0.f;
+        CU_TRY(c, cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+        stats->kernel_ms = ms;
+        stats->launches = launches;
+    }
+    return HC_OK;
+}
+
+int hc_score_pairs(hc_ctx* c, const int32_t* pi, const int32_t* pj, int64_t npairs, hc_pair_result* out) {
+    if (!c || npairs < 0 || (npairs > 0 && (!pi || !pj || !out))) return HC_E_INVALID;
+    if (!c->d_hdr) { c->err = "hc_score_pairs: no batch uploaded"; return HC_E_STATE; }
+    for (int64_t k = 0; k < npairs; ++k)
+        if (pi[k] < 0 || pi[k] >= c->n_reads || pj[k] < 0 || pj[k] >= c->n_reads) { c->err = "hc_score_pairs: read index out of range"; return HC_E_INVALID; }
+    if (npairs == 0) return HC_OK;
+    CU_TRY(c, cudaSetDevice(c->device));
+    int rc;
+    size_t cap_i = c->pairs_cap, cap_j = c->pairs_cap;
+    if ((rc = grow(c, c->d_pi, cap_i, (size_t)npairs)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_pj, cap_j, (size_t)npairs)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_res, c->pairs_cap, (size_t)npairs)) != HC_OK) return rc;
+    CU_TRY(c, cudaMemcpyAsync(c->d_pi, pi, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(c->d_pj, pj, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, c->stream));
+    const int threads = 128;
+    const int blocks = (int)std::min<long long>((npairs + threads - 1) / threads, (long long)c->sm_count * 16);
+    score_pairs_kernel<<<blocks, threads, 0, c->stream>>>(dev_params(c), c->d_hdr, c->d_ops, c->d_pi, c->d_pj, npairs, c->d_res);
+    CU_TRY(c, cudaGetLastError());
+    CU_TRY(c, cudaMemcpyAsync(out, c->d_res, sizeof(hc_pair_result) * npairs, cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    return HC_OK;
+}
+
+}  // extern "C"

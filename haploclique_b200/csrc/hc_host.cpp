@@ -1,0 +1,242 @@
+// Host side of libhcgpu.so: AlignmentRecord fields -> packed SoA (headers + 16-bit op records).
+// Reference for the fields: src/AlignmentRecord.h:54-77; clip-extended bounds: computeOffset /
+// computeRevOffset (src/AlignmentRecord.cpp:126-156) as used at src/NewEdgeCalculator.cpp:413-421.
+#include <cmath>
+#include <cstring>
+#include <mutex>
+#include <new>
+
+#include <cuda_runtime_api.h>
+
+#include <cstdlib>
+
+#include "hc_internal.h"
+
+namespace hc {
+
+bool HostBuf::alloc(size_t bytes) {
+    release();
+    if (bytes == 0) bytes = 64;
+    static int have_gpu = -1;
+    if (have_gpu < 0) {
+        int n = 0;
+        have_gpu = (cudaGetDeviceCount(&n) == cudaSuccess && n > 0) ? 1 : 0;
+        if (!have_gpu) cudaGetLastError();
+    }
+    if (have_gpu && cudaHostAlloc(&p, bytes, cudaHostAllocDefault) == cudaSuccess) { pinned = true; return true; }
+    if (have_gpu) cudaGetLastError();
+    p = std::malloc(bytes);
+    pinned = false;
+    return p != nullptr;
+}
+
+void HostBuf::release() {
+    if (!p) return;
+    if (pinned) cudaFreeHost(p); else std::free(p);
+    p = nullptr;
+}
+
+static std::mutex g_err_mu;
+static std::string g_err;
+
+void set_global_error(const std::string& msg) {
+    std::lock_guard<std::mutex> lk(g_err_mu);
+    g_err = msg;
+}
+const char* global_error() { return g_err.c_str(); }
+
+void build_match_tables(double* eq, double* uneq) {
+    std::memset(eq, 0, sizeof(double) * 127 * 127);
+    std::memset(uneq, 0, sizeof(double) * 127 * 127);
+    float e[127], e3[127];
+    for (int c = 33; c < 127; ++c) {
+        // error probability of quality char c: 10^(-(c-33)/10) evaluated in double, kept as float
+        e[c] = static_cast<float>(std::pow(10.0, static_cast<double>(-(c - 33)) / 10.0));
+        e3[c] = e[c] / 3;                        // float division, as the reference's e/3
+    }
+    for (int a = 33; a < 127; ++a) {
+        const double ok_a = 1.0 - e[a];
+        for (int b = 33; b < 127; ++b) {
+            const double ok_b = 1.0 - e[b];
+            const float both_wrong_same = e[a] * e3[b];          // float * float
+            const float both_wrong_diff = 2 * e3[a] * e3[b];     // (2*float)*float in float
+            eq[a * 127 + b] = ok_a * ok_b + both_wrong_same;
+            uneq[a * 127 + b] = ok_a * e3[b] + ok_b * e3[a] + both_wrong_diff;
+        }
+    }
+}
+
+void build_prob0_ladder(std::vector<double>& F, int n_max) {
+    F.assign(static_cast<size_t>(n_max) + 1, 0.0);
+    const double step = std::log10(0.25);
+    double acc = 0.0;
+    for (int k = 1; k <= n_max; ++k) {
+        acc += step;
+        F[k] = acc;
+    }
+}
+
+}  // namespace hc
+
+namespace {
+
+inline int op_code(uint8_t c) {
+    switch (c) {
+        case 'M': return HC_OP_M;
+        case 'I': return HC_OP_I;
+        case 'D': return HC_OP_D;
+        case 'S': return HC_OP_S;
+        case 'H': return HC_OP_H;
+        default: return -1;
+    }
+}
+
+inline int base_code(uint8_t c) {
+    switch (c) {
+        case 'A': case 'a': return 0;
+        case 'C': case 'c': return 1;
+        case 'G': case 'g': return 2;
+        case 'T': case 't': return 3;
+        default: return 4;                       // ShortDnaSequence maps everything else to 'N'
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int hc_abi_version(void) { return HC_ABI_VERSION; }
+
+int hc_pack(const hc_reads* rd, hc_packed** out) {
+    if (!rd || !out || rd->n < 0) {
+        hc::set_global_error("hc_pack: null argument or negative read count");
+        return HC_E_INVALID;
+    }
+    *out = nullptr;
+    const int n = rd->n;
+    hc_packed* p = nullptr;
+    hc::PackedOwner* own = nullptr;
+    try {
+        p = new hc_packed();
+        own = new hc::PackedOwner();
+    } catch (const std::bad_alloc&) {
+        delete p;
+        hc::set_global_error("hc_pack: out of memory");
+        return HC_E_NOMEM;
+    }
+    std::memset(p, 0, sizeof(*p));
+    p->owner = own;
+
+    // pass 1: which quality chars occur -> dense codes; total op count
+    bool seen[256] = {false};
+    int64_t total_ops = 0;
+    for (int r = 0; r < n; ++r) {
+        const int nseg = rd->single_end[r] ? 1 : 2;
+        for (int s = 0; s < nseg; ++s) {
+            const int k = 2 * r + s;
+            const uint8_t* q = rd->qual + rd->seq_off[k];
+            for (int t = 0; t < rd->seq_len[k]; ++t) seen[q[t]] = true;
+            total_ops += rd->cig_len[k];
+        }
+    }
+    int code_of[256];
+    int K = 0;
+    for (int c = 0; c < 256; ++c) {
+        code_of[c] = -1;
+        if (!seen[c]) continue;
+        if (c < 33 || c > 126) {
+            hc::set_global_error("hc_pack: quality character outside 33..126 (the reference's tables are undefined there)");
+            hc_packed_free(p);
+            return HC_E_INVALID;
+        }
+        p->qual_chars[K] = static_cast<uint8_t>(c);
+        code_of[c] = K++;
+    }
+    if (total_ops >= (int64_t(1) << 32) - 64) {
+        hc::set_global_error("hc_pack: more than 2^32 CIGAR ops in one batch; split the batch");
+        hc_packed_free(p);
+        return HC_E_INVALID;
+    }
+    if (!own->hdr.alloc(sizeof(hc_read_hdr) * static_cast<size_t>(n)) ||
+        !own->ops.alloc(sizeof(uint16_t) * (static_cast<size_t>(total_ops) + 64))) {   // padding: kernels may over-read
+        hc_packed_free(p);
+        hc::set_global_error("hc_pack: out of memory");
+        return HC_E_NOMEM;
+    }
+    hc_read_hdr* hdr_out = static_cast<hc_read_hdr*>(own->hdr.p);
+    uint16_t* ops_out = static_cast<uint16_t*>(own->ops.p);
+    std::memset(ops_out + total_ops, 0, sizeof(uint16_t) * 64);
+
+    // pass 2: headers and op records
+    int64_t w = 0;
+    int max_ops = 0;
+    for (int r = 0; r < n; ++r) {
+        hc_read_hdr& h = hdr_out[r];
+        std::memset(&h, 0, sizeof(h));
+        const bool single = rd->single_end[r] != 0;
+        h.ncov_flags = (static_cast<uint32_t>(rd->ncov[r]) & 0x3fffffffu) | (single ? HC_FLAG_SINGLE_END : 0u) |
+                       (rd->is_clique[r] ? HC_FLAG_IS_CLIQUE : 0u);
+        h.cov_first = rd->cov_first[r];
+        h.cov_last = rd->cov_last[r];
+        int read_ops = 0;
+        for (int s = 0; s < (single ? 1 : 2); ++s) {
+            const int k = 2 * r + s;
+            const uint8_t* cg = rd->cig + rd->cig_off[k];
+            const uint8_t* sq = rd->seq + rd->seq_off[k];
+            const uint8_t* ql = rd->qual + rd->seq_off[k];
+            const int nc = rd->cig_len[k], nq = rd->seq_len[k];
+            int lead = 0, trail = 0;
+            while (lead < nc && (cg[lead] == 'S' || cg[lead] == 'H')) ++lead;
+            while (trail < nc && (cg[nc - 1 - trail] == 'S' || cg[nc - 1 - trail] == 'H')) ++trail;
+            h.raw[2 * s] = rd->seg_start[k];
+            h.raw[2 * s + 1] = rd->seg_end[k];
+            h.ext[2 * s] = rd->seg_start[k] - lead;
+            h.ext[2 * s + 1] = rd->seg_end[k] + trail;
+            h.ops_off[s] = static_cast<uint32_t>(w);
+            h.n_ops[s] = nc;
+            int qi = 0;
+            bool ins = false;
+            for (int t = 0; t < nc; ++t) {
+                const int op = op_code(cg[t]);
+                if (op < 0) {
+                    hc::set_global_error(std::string("hc_pack: CIGAR op '") + static_cast<char>(cg[t]) +
+                                         "' is outside MIDSH (the reference's walk does not define it)");
+                    hc_packed_free(p);
+                    return HC_E_INVALID;
+                }
+                uint16_t rec = static_cast<uint16_t>(op << HC_OP_SHIFT);
+                if (op == HC_OP_M || op == HC_OP_I || op == HC_OP_S) {
+                    if (qi >= nq) {
+                        hc::set_global_error("hc_pack: CIGAR consumes more query bases than the read has");
+                        hc_packed_free(p);
+                        return HC_E_INVALID;
+                    }
+                    rec |= static_cast<uint16_t>(base_code(sq[qi]) << HC_BASE_SHIFT) | static_cast<uint16_t>(code_of[ql[qi]]);
+                    ++qi;
+                }
+                ins |= (op == HC_OP_I);
+                ops_out[static_cast<size_t>(w++)] = rec;
+            }
+            h.has_ins[s] = ins ? 1 : 0;
+            read_ops += nc;
+        }
+        if (single) h.ops_off[1] = static_cast<uint32_t>(w);
+        if (read_ops > max_ops) max_ops = read_ops;
+    }
+    p->n_reads = n;
+    p->n_qual_codes = K;
+    p->hdr = hdr_out;
+    p->ops = ops_out;
+    p->n_ops_total = total_ops;
+    p->max_ops_per_read = max_ops;
+    *out = p;
+    return HC_OK;
+}
+
+void hc_packed_free(hc_packed* p) {
+    if (!p) return;
+    delete static_cast<hc::PackedOwner*>(p->owner);
+    delete p;
+}
+
+}  // extern "C"

@@ -1,0 +1,356 @@
+"""Host-side mirror of the reference's edge-calculator plugin interface over libhcgpu.so.
+
+``EdgeCalculator`` / ``NewEdgeCalculator`` keep the reference's names, constructor argument order and
+meaning (``src/EdgeCalculator.h:24-37``, ``src/NewEdgeCalculator.h:58``). The scoring itself happens in the
+sm_100a kernels behind the C ABI (``include/hc_edge.h``); there is no CPU scoring path here: without the
+built library or without a CUDA device every scoring call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Dict, Optional, Sequence, Union
+
+import numpy as np
+
+from .records import AlignmentRecord, ReadBatch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libhcgpu.so")
+
+HC_OK = 0
+ST_REJECT_COV, ST_REJECT_LAYOUT, ST_WALKED, ST_UNDEFINED = 0, 1, 2, 3
+
+
+class HcError(RuntimeError):
+    pass
+
+
+class _Params(C.Structure):
+    _fields_ = [("edge_quasi_cutoff_cliques", C.c_double), ("edge_quasi_cutoff_mixed", C.c_double),
+                ("edge_quasi_cutoff_single", C.c_double), ("min_overlap_cliques", C.c_double),
+                ("min_overlap_single", C.c_double), ("no_prob0", C.c_int32), ("simpson_len", C.c_int32),
+                ("simpson", C.c_void_p), ("device", C.c_int32), ("reserved", C.c_int32),
+                ("ambiguity_rel_tol", C.c_double)]
+
+
+class _Reads(C.Structure):
+    _fields_ = [("n", C.c_int32)] + [(k, C.c_void_p) for k in (
+        "single_end", "is_clique", "ncov", "cov_first", "cov_last", "seg_start", "seg_end", "cig_off", "cig_len",
+        "seq_off", "seq_len", "cig", "seq", "qual")]
+
+
+class _Packed(C.Structure):
+    _fields_ = [("n_reads", C.c_int32), ("n_qual_codes", C.c_int32), ("qual_chars", C.c_uint8 * 128),
+                ("hdr", C.c_void_p), ("ops", C.c_void_p), ("n_ops_total", C.c_int64),
+                ("max_ops_per_read", C.c_int32), ("reserved", C.c_int32), ("owner", C.c_void_p)]
+
+
+class _BandStats(C.Structure):
+    _fields_ = [("pairs_total", C.c_int64), ("pairs_scored", C.c_int64), ("pairs_walked", C.c_int64),
+                ("edges", C.c_int64), ("sum_cc", C.c_int64), ("sum_tc", C.c_int64), ("undefined", C.c_int64),
+                ("ambiguous", C.c_int64), ("kernel_ms", C.c_float), ("launches", C.c_int32)]
+
+
+PAIR_RESULT_DTYPE = np.dtype([("status", np.int32), ("edge", np.int32), ("gap", np.int32), ("cc", np.int32),
+                              ("tc", np.int32), ("ambiguous", np.int32), ("probM", np.float64),
+                              ("prob0", np.float64), ("score", np.float64)], align=True)
+AMBIGUOUS_DTYPE = np.dtype([("i", np.int32), ("j", np.int32), ("cc", np.int32), ("tc", np.int32),
+                            ("probM", np.float64), ("prob0", np.float64), ("score", np.float64),
+                            ("cutoff", np.float64)], align=True)
+HDR_DTYPE = np.dtype([("raw", np.int32, 4), ("ext", np.int32, 4), ("ops_off", np.uint32, 2), ("n_ops", np.int32, 2),
+                      ("ncov_flags", np.uint32), ("cov_first", np.int32), ("cov_last", np.int32),
+                      ("has_ins", np.uint16, 2)], align=True)
+
+_lib = None
+
+
+def load_library():
+    """Loads libhcgpu.so; fails loudly when the CUDA extension has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise HcError("haploclique_b200/libhcgpu.so is missing: build it with "
+                          "`python -c 'import __graft_entry__ as g; g.build()'` (there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.hc_last_error.restype = C.c_char_p
+        L.hc_last_error.argtypes = [C.c_void_p]
+        L.hc_host_alloc.restype = C.c_void_p
+        L.hc_host_alloc.argtypes = [C.c_int64]
+        L.hc_host_free.argtypes = [C.c_void_p]
+        L.hc_create.argtypes = [C.c_void_p, C.c_void_p]
+        L.hc_destroy.argtypes = [C.c_void_p]
+        L.hc_pack.argtypes = [C.c_void_p, C.c_void_p]
+        L.hc_packed_free.argtypes = [C.c_void_p]
+        L.hc_upload.argtypes = [C.c_void_p, C.c_void_p]
+        L.hc_set_params.argtypes = [C.c_void_p, C.c_void_p]
+        L.hc_band_layout.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.hc_score_band.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32,
+                                    C.c_void_p]
+        L.hc_score_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+        L.hc_get_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        assert C.sizeof(_BandStats) == 72 and HDR_DTYPE.itemsize == 64
+        _lib = L
+    return _lib
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class PinnedBuffer:
+    """Page-locked host array (cudaHostAlloc through the C ABI)."""
+
+    def __init__(self, n: int, dtype=np.uint32):
+        self._L = load_library()
+        self.nbytes = max(int(n), 1) * np.dtype(dtype).itemsize
+        self._p = self._L.hc_host_alloc(self.nbytes)
+        if not self._p:
+            raise HcError("cudaHostAlloc failed")
+        buf = (C.c_uint8 * self.nbytes).from_address(self._p)
+        self.array = np.frombuffer(buf, dtype=dtype, count=int(n))
+
+    def __del__(self):
+        try:
+            if self._p:
+                self.array = None
+                self._L.hc_host_free(self._p)
+                self._p = None
+        except Exception:
+            pass
+
+
+class PackedBatch:
+    """Result of hc_pack: 64-byte headers + 16-bit op records, owned by the library."""
+
+    def __init__(self, batch: ReadBatch):
+        L = load_library()
+        self.batch = batch
+        rd = _Reads(batch.n, *[_ptr(np.ascontiguousarray(getattr(batch, k))) for k in (
+            "single_end", "is_clique", "ncov", "cov_first", "cov_last", "seg_start", "seg_end", "cig_off", "cig_len",
+            "seq_off", "seq_len", "cig", "seq", "qual")])
+        self._h = C.c_void_p()
+        rc = L.hc_pack(C.byref(rd), C.byref(self._h))
+        if rc != HC_OK:
+            raise HcError("hc_pack failed (%d): %s" % (rc, L.hc_last_error(None).decode()))
+        self.c = C.cast(self._h, C.POINTER(_Packed)).contents
+
+    @property
+    def n_reads(self) -> int:
+        return self.c.n_reads
+
+    @property
+    def n_ops_total(self) -> int:
+        return self.c.n_ops_total
+
+    def nbytes(self) -> int:
+        return self.c.n_reads * 64 + (self.c.n_ops_total + 64) * 2
+
+    def headers(self) -> np.ndarray:
+        buf = (C.c_uint8 * (64 * self.c.n_reads)).from_address(self.c.hdr)
+        return np.frombuffer(buf, dtype=HDR_DTYPE).copy()
+
+    def ops(self) -> np.ndarray:
+        buf = (C.c_uint16 * self.c.n_ops_total).from_address(self.c.ops)
+        return np.frombuffer(buf, dtype=np.uint16).copy()
+
+    def __del__(self):
+        try:
+            if self._h:
+                load_library().hc_packed_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+class Adjacency:
+    """Banded adjacency of one scored batch: row i holds one bit per earlier read j in [col0[i], i)."""
+
+    def __init__(self, row_begin: int, row_end: int, col0: np.ndarray, word_off: np.ndarray, words: np.ndarray,
+                 stats: Dict[str, float], ambiguous: np.ndarray):
+        self.row_begin, self.row_end = row_begin, row_end
+        self.col0, self.word_off, self.words = col0, word_off, words
+        self.stats, self.ambiguous = stats, ambiguous
+
+    def edge(self, i: int, j: int) -> bool:
+        """edgeBetween(read i, read j) for i the later arrival; anything left of the band is a non-overlap."""
+        if j >= i:
+            raise ValueError("adjacency holds ordered pairs with j < i")
+        k = i - self.row_begin
+        c0 = int(self.col0[k])
+        if j < c0:
+            return False
+        w = int(self.word_off[k]) + ((j - c0) >> 5)
+        return bool((int(self.words[w]) >> ((j - c0) & 31)) & 1)
+
+    def row(self, i: int) -> np.ndarray:
+        k = i - self.row_begin
+        w0, w1 = int(self.word_off[k]), int(self.word_off[k + 1])
+        bits = np.unpackbits(self.words[w0:w1].view(np.uint8), bitorder="little")
+        return int(self.col0[k]) + np.nonzero(bits)[0]
+
+    def edges(self):
+        """(i, j) arrays of all edges, row-major."""
+        ii, jj = [], []
+        for i in range(self.row_begin, self.row_end):
+            r = self.row(i)
+            ii.append(np.full(r.shape[0], i, np.int32))
+            jj.append(r.astype(np.int32))
+        if not ii:
+            return np.zeros(0, np.int32), np.zeros(0, np.int32)
+        return np.concatenate(ii), np.concatenate(jj)
+
+    def count(self) -> int:
+        return int(np.unpackbits(self.words.view(np.uint8)).sum())
+
+
+class EdgeCalculator:
+    """The reference's pure-virtual plugin API (src/EdgeCalculator.h:24-37)."""
+
+    def edgeBetween(self, ar1, ar2) -> bool:
+        raise NotImplementedError
+
+    def getPartnerLengthRange(self, ar):
+        raise NotImplementedError
+
+    def setOverlapCliques(self, d: float) -> None:
+        pass
+
+
+class NewEdgeCalculator(EdgeCalculator):
+    """GPU-backed drop-in for the reference's NewEdgeCalculator. Constructor arguments in the reference's
+    order (src/NewEdgeCalculator.h:58); ``device`` is the only addition."""
+
+    def __init__(self, Q: float = 0.9, edge_quasi_cutoff: float = 0.99, overlap: float = 0.9,
+                 frameshift_merge: bool = False, simpson_map: Optional[Dict[int, float]] = None,
+                 edge_quasi_cutoff_single: float = 0.95, overlap_single: float = 0.6,
+                 edge_quasi_cutoff_mixed: float = 0.97, maxPosition: int = 0, noProb0: bool = False,
+                 device: int = 0, ambiguity_rel_tol: float = 1e-12):
+        self.L = load_library()
+        self.Q, self.FRAMESHIFT_MERGE = Q, frameshift_merge       # stored, unused by the scorer (as in the reference)
+        self._simpson = None
+        if simpson_map:
+            self._simpson = np.zeros(int(maxPosition) + 1, np.float64)   # SIMPSON_MAP.resize(maxPosition+1) (:85)
+            for k, v in simpson_map.items():
+                self._simpson[int(k)] = v
+        self._par = _Params(edge_quasi_cutoff, edge_quasi_cutoff_mixed, edge_quasi_cutoff_single, overlap,
+                            overlap_single, int(bool(noProb0)), 0 if self._simpson is None else self._simpson.shape[0],
+                            None if self._simpson is None else self._simpson.ctypes.data, device, 0, ambiguity_rel_tol)
+        self._ctx = C.c_void_p()
+        rc = self.L.hc_create(C.byref(self._par), C.byref(self._ctx))
+        if rc != HC_OK:
+            raise HcError("hc_create failed (%d): %s" % (rc, self.L.hc_last_error(None).decode()))
+        self._packed: Optional[PackedBatch] = None
+        self._index: Dict[int, int] = {}
+        self._adj: Optional[Adjacency] = None
+
+    def __del__(self):
+        try:
+            if self._ctx:
+                self.L.hc_destroy(self._ctx)
+                self._ctx = None
+        except Exception:
+            pass
+
+    def _check(self, rc: int, what: str):
+        if rc != HC_OK:
+            raise HcError("%s failed (%d): %s" % (what, rc, self.L.hc_last_error(self._ctx).decode()))
+
+    # -- reference interface ---------------------------------------------------------------------------
+    def setOverlapCliques(self, d: float) -> None:            # src/NewEdgeCalculator.cpp:1382
+        self._par.min_overlap_cliques = d
+        self._check(self.L.hc_set_params(self._ctx, C.byref(self._par)), "hc_set_params")
+        self._adj = None
+
+    def getOverlapCliques(self) -> float:
+        return self._par.min_overlap_cliques
+
+    def getPartnerLengthRange(self, ar):                       # the reference asserts false here (:1378-1380)
+        raise AssertionError("NewEdgeCalculator::getPartnerLengthRange is not implemented in the reference either")
+
+    def edgeBetween(self, ap1: AlignmentRecord, ap2: AlignmentRecord) -> bool:
+        """Answers from the adjacency of the last scoreBatch when both records belong to it (the clique
+        finders' calls); any other two records are packed as a 2-read batch and scored on the GPU."""
+        i, j = self._index.get(id(ap1)), self._index.get(id(ap2))
+        if i is not None and j is not None and self._adj is not None and j < i:
+            return self._adj.edge(i, j)
+        if i is not None and j is not None and self._packed is not None:
+            return bool(self.score_pairs([i], [j])["edge"][0])
+        # records outside the resident batch (the reference's unit tests call it this way)
+        pair = PackedBatch(ReadBatch.from_records([ap2, ap1]))
+        try:
+            self._check(self.L.hc_upload(self._ctx, pair._h), "hc_upload")
+            pi, pj = np.array([1], np.int32), np.array([0], np.int32)
+            out = np.zeros(1, PAIR_RESULT_DTYPE)
+            self._check(self.L.hc_score_pairs(self._ctx, _ptr(pi), _ptr(pj), 1, _ptr(out)), "hc_score_pairs")
+            return bool(out["edge"][0])
+        finally:
+            if self._packed is not None:
+                self._check(self.L.hc_upload(self._ctx, self._packed._h), "hc_upload")
+
+    # -- batch interface (the driver hook of SURVEY.md 8(b)) -------------------------------------------
+    def upload(self, reads: Union[ReadBatch, Sequence[AlignmentRecord], PackedBatch]) -> PackedBatch:
+        if isinstance(reads, PackedBatch):
+            packed = reads
+        else:
+            if not isinstance(reads, ReadBatch):
+                recs = list(reads)
+                self._index = {id(r): k for k, r in enumerate(recs)}
+                reads = ReadBatch.from_records(recs)
+            packed = PackedBatch(reads)
+        self._check(self.L.hc_upload(self._ctx, packed._h), "hc_upload")
+        self._packed = packed
+        self._adj = None
+        return packed
+
+    def band_layout(self, row_begin: int = 0, row_end: Optional[int] = None):
+        row_end = self._packed.n_reads if row_end is None else row_end
+        nrows = row_end - row_begin
+        col0 = np.zeros(max(nrows, 1), np.int32)
+        off = np.zeros(nrows + 1, np.int64)
+        nw = C.c_int64(0)
+        self._check(self.L.hc_band_layout(self._ctx, row_begin, row_end, _ptr(col0), _ptr(off), C.byref(nw)),
+                    "hc_band_layout")
+        return col0[:nrows], off, int(nw.value)
+
+    def score_band(self, row_begin: int = 0, row_end: Optional[int] = None, out: Optional[np.ndarray] = None,
+                   amb_cap: int = 4096, fetch: bool = True) -> Adjacency:
+        row_end = self._packed.n_reads if row_end is None else row_end
+        col0, off, nw = self.band_layout(row_begin, row_end)
+        if fetch and out is None:
+            out = np.zeros(max(nw, 1), np.uint32)
+        amb = np.zeros(max(amb_cap, 1), AMBIGUOUS_DTYPE)
+        st = _BandStats()
+        self._check(self.L.hc_score_band(self._ctx, row_begin, row_end, _ptr(out) if fetch else None, nw,
+                                         _ptr(amb) if amb_cap > 0 else None, amb_cap, C.byref(st)), "hc_score_band")
+        stats = {k: getattr(st, k) for k, _ in _BandStats._fields_}
+        words = out[:nw] if fetch else np.zeros(0, np.uint32)
+        return Adjacency(row_begin, row_end, col0, off, words, stats, amb[:min(int(st.ambiguous), amb_cap)].copy())
+
+    def scoreBatch(self, reads) -> Adjacency:
+        """One call per clique-finder iteration: pack, upload, score the whole band, fetch the adjacency."""
+        self.upload(reads)
+        self._adj = self.score_band()
+        return self._adj
+
+    def score_pairs(self, pi, pj) -> np.ndarray:
+        pi = np.ascontiguousarray(pi, np.int32)
+        pj = np.ascontiguousarray(pj, np.int32)
+        out = np.zeros(pi.shape[0], PAIR_RESULT_DTYPE)
+        self._check(self.L.hc_score_pairs(self._ctx, _ptr(pi), _ptr(pj), pi.shape[0], _ptr(out)), "hc_score_pairs")
+        return out
+
+    def tables(self):
+        eq = np.zeros((127, 127), np.float64)
+        un = np.zeros((127, 127), np.float64)
+        self._check(self.L.hc_get_tables(self._ctx, _ptr(eq), _ptr(un)), "hc_get_tables")
+        return eq, un
+
+
+def pack_only(batch: ReadBatch) -> PackedBatch:
+    """hc_pack without a device (host C++ packing only)."""
+    return PackedBatch(batch)
+
+
+def device_count() -> int:
+    return int(load_library().hc_device_count())

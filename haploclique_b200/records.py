@@ -209,6 +209,32 @@ class ReadBatch:
     def select(self, idx: Iterable[int]) -> "ReadBatch":
         return ReadBatch.from_records([self.record(int(i)) for i in idx])
 
+    def permute(self, order: np.ndarray) -> "ReadBatch":
+        """Vectorised re-ordering / sub-setting of reads (new read k = old read order[k])."""
+        order = np.asarray(order, np.int64)
+        b = ReadBatch(order.shape[0])
+        for f in ("single_end", "is_clique", "ncov", "cov_first", "cov_last"):
+            setattr(b, f, getattr(self, f)[order].copy())
+        segs = np.stack([2 * order, 2 * order + 1], axis=1).reshape(-1)
+        b.seg_start, b.seg_end = self.seg_start[segs].copy(), self.seg_end[segs].copy()
+        b.cig_len, b.seq_len = self.cig_len[segs].copy(), self.seq_len[segs].copy()
+        b.cig_off = (np.cumsum(b.cig_len, dtype=np.int64) - b.cig_len).astype(np.int64)
+        b.seq_off = (np.cumsum(b.seq_len, dtype=np.int64) - b.seq_len).astype(np.int64)
+
+        def gather(src, old_off, lens, new_off):
+            tot = int(lens.sum())
+            if tot == 0:
+                return np.zeros(0, src.dtype)
+            idx = np.arange(tot, dtype=np.int64) + np.repeat(old_off - new_off, lens)
+            return src[idx]
+
+        b.cig = gather(self.cig, self.cig_off[segs], b.cig_len, b.cig_off)
+        b.seq = gather(self.seq, self.seq_off[segs], b.seq_len, b.seq_off)
+        b.qual = gather(self.qual, self.seq_off[segs], b.seq_len, b.seq_off)
+        if self.names is not None:
+            b.names = [self.names[int(i)] for i in order]
+        return b
+
     # -- (de)serialisation for committed fixtures --------------------------------------------------
     _FIELDS = ("single_end", "is_clique", "ncov", "cov_first", "cov_last", "seg_start", "seg_end",
                "cig_off", "cig_len", "seq_off", "seq_len", "cig", "seq", "qual")

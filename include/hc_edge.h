@@ -1,0 +1,197 @@
+/* hc_edge.h -- C ABI of libhcgpu.so: B200 (sm_100a) read-pair edge scoring.
+ *
+ * Drop-in boundary for ONE path of cbg-ethz/haploclique: the edge decision
+ *     bool EdgeCalculator::edgeBetween(const AlignmentRecord&, const AlignmentRecord&) const
+ * (reference: src/EdgeCalculator.h:29) as implemented by NewEdgeCalculator
+ * (src/NewEdgeCalculator.cpp:1247-1376), evaluated for a whole batch of position-sorted reads at once.
+ * Plain pointers and sizes only; no C++/torch types. All functions return HC_OK (0) or a negative
+ * HC_E_* code; hc_last_error() gives the text. There is no CPU scoring path behind this API: without
+ * a CUDA device every scoring call fails with HC_E_CUDA.
+ *
+ * Call sequence (INTEGRATION.md shows the reference-side binding):
+ *     hc_create(&params, &ctx)            <- NewEdgeCalculator::NewEdgeCalculator (src/NewEdgeCalculator.cpp:77-90)
+ *     hc_pack(&reads, &packed)            <- AlignmentRecord getters (src/AlignmentRecord.cpp:1703-1811)
+ *     hc_upload(ctx, packed)
+ *     hc_score_band(ctx, ...) / hc_score_pairs(ctx, ...)   <- the edgeBetween calls of
+ *                                            CLEVER::addAlignment (src/CLEVER.cpp:218-232) and
+ *                                            BronKerbosch::addAlignment (src/BronKerbosch.cpp:286)
+ *     hc_packed_free(packed); hc_destroy(ctx)
+ */
+#ifndef HC_EDGE_H_
+#define HC_EDGE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HC_ABI_VERSION 1
+
+enum {
+    HC_OK = 0,
+    HC_E_INVALID = -1,   /* bad argument / malformed read (unknown CIGAR op, quality outside 33..126, ...) */
+    HC_E_CUDA = -2,      /* no device, or a CUDA call failed */
+    HC_E_NOMEM = -3,
+    HC_E_STATE = -4      /* call out of sequence (e.g. scoring before hc_upload) */
+};
+
+/* Constructor arguments of NewEdgeCalculator that the scorer reads (src/NewEdgeCalculator.h:58).
+ * Q and frameshift_merge are stored but unused by the reference's scorer and are not taken here. */
+typedef struct {
+    double edge_quasi_cutoff_cliques;   /* EDGE_QUASI_CUTOFF        (default 0.99) */
+    double edge_quasi_cutoff_mixed;     /* EDGE_QUASI_CUTOFF_MIXED  (default 0.97) */
+    double edge_quasi_cutoff_single;    /* EDGE_QUASI_CUTOFF_SINGLE (default 0.95) */
+    double min_overlap_cliques;         /* MIN_OVERLAP_CLIQUES      (default 0.9)  */
+    double min_overlap_single;          /* MIN_OVERLAP_SINGLE       (default 0.6)  */
+    int32_t no_prob0;                   /* NOPROB0 */
+    int32_t simpson_len;                /* maxPosition+1; 0 = no allele-frequency file */
+    const double* simpson;              /* dense SIMPSON_MAP, 0.0 = position absent (src/NewEdgeCalculator.cpp:85-88) */
+    int32_t device;                     /* CUDA device ordinal */
+    int32_t reserved;
+    double ambiguity_rel_tol;           /* pairs with |score-cutoff| <= tol*|cutoff| are also listed (0 -> 1e-12) */
+} hc_params;
+
+/* A batch of reads in arrival (position-sorted) order, as the AlignmentRecord fields the scorer reads
+ * (src/AlignmentRecord.h:54-77). Segment s (0/1) of read r is row 2*r+s of the per-segment arrays. */
+typedef struct {
+    int32_t n;
+    const uint8_t* single_end;          /* [n]  AlignmentRecord::single_end */
+    const uint8_t* is_clique;           /* [n]  name contains "Clique" (src/NewEdgeCalculator.cpp:1111) */
+    const int32_t* ncov;                /* [n]  cov_pos.size() */
+    const int32_t* cov_first;           /* [n]  cov_pos.front().ref */
+    const int32_t* cov_last;            /* [n]  cov_pos.back().ref */
+    const int32_t* seg_start;           /* [2n] start1/start2, 1-based inclusive */
+    const int32_t* seg_end;             /* [2n] end1/end2 */
+    const int64_t* cig_off;             /* [2n] offset of the segment's unrolled CIGAR in cig[] */
+    const int32_t* cig_len;             /* [2n] 0 for the absent 2nd segment of a single-end read */
+    const int64_t* seq_off;             /* [2n] offset of bases/qualities in seq[]/qual[] */
+    const int32_t* seq_len;             /* [2n] */
+    const uint8_t* cig;                 /* unrolled CIGAR chars, M I D S H only */
+    const uint8_t* seq;                 /* bases; anything but ACGT counts as N (src/ShortDnaSequence.cpp:37-50) */
+    const uint8_t* qual;                /* ASCII Phred+33, 33..126 */
+} hc_reads;
+
+/* Packed per-read header, 64 bytes, the unit the kernels load.
+ * raw[]/ext[] follow the order {start1,end1,start2,end2}; ext = clip-extended interval
+ * (start - leading S/H count, end + trailing S/H count: src/NewEdgeCalculator.cpp:413-421). */
+typedef struct {
+    int32_t raw[4];
+    int32_t ext[4];
+    uint32_t ops_off[2];                /* first op record of each segment in hc_packed.ops */
+    int32_t n_ops[2];                   /* unrolled CIGAR length per segment */
+    uint32_t ncov_flags;                /* bits 0..29 ncov, bit 30 single_end, bit 31 is_clique */
+    int32_t cov_first;
+    int32_t cov_last;
+    uint16_t has_ins[2];                /* segment holds at least one I op */
+} hc_read_hdr;
+
+#define HC_FLAG_SINGLE_END 0x40000000u
+#define HC_FLAG_IS_CLIQUE 0x80000000u
+
+/* One 16-bit record per unrolled CIGAR op:
+ *   bits 0..6  quality code (dense re-numbering of the quality chars present, see qual_chars[])
+ *   bits 7..9  base code    A=0 C=1 G=2 T=3 N=4   (0 for D/H ops, which carry no base)
+ *   bits 10..12 op          M=0 I=1 D=2 S=3 H=4 */
+#define HC_OP_SHIFT 10
+#define HC_BASE_SHIFT 7
+enum { HC_OP_M = 0, HC_OP_I = 1, HC_OP_D = 2, HC_OP_S = 3, HC_OP_H = 4 };
+
+typedef struct {
+    int32_t n_reads;
+    int32_t n_qual_codes;               /* K <= 94 */
+    uint8_t qual_chars[128];            /* code -> quality char */
+    const hc_read_hdr* hdr;             /* [n_reads] */
+    const uint16_t* ops;                /* [n_ops_total (+ padding)] */
+    int64_t n_ops_total;
+    int32_t max_ops_per_read;           /* max over reads of n_ops[0]+n_ops[1] */
+    int32_t reserved;
+    void* owner;                        /* library-private */
+} hc_packed;
+
+/* Per-pair result of hc_score_pairs (the values edgeBetween computes on its way to the bool). */
+enum { HC_ST_REJECT_COV = 0, HC_ST_REJECT_LAYOUT = 1, HC_ST_WALKED = 2, HC_ST_UNDEFINED = 3 };
+typedef struct {
+    int32_t status;                     /* HC_ST_*; UNDEFINED = the reference would read out of bounds here */
+    int32_t edge;
+    int32_t gap;                        /* checkGapsCigar returned true (src/NewEdgeCalculator.cpp:1367) */
+    int32_t cc, tc;
+    int32_t ambiguous;                  /* |score-cutoff| within ambiguity_rel_tol */
+    double probM, prob0;
+    double score;                       /* prob*potence (:1139); NaN when not reached */
+} hc_pair_result;
+
+typedef struct {
+    int32_t i, j;                       /* ap1 = read i (later arrival), ap2 = read j */
+    int32_t cc, tc;
+    double probM, prob0;
+    double score, cutoff;
+} hc_ambiguous;
+
+/* Totals of one hc_score_band call. */
+typedef struct {
+    int64_t pairs_total;                /* ordered pairs i>j looked at (inside the band) */
+    int64_t pairs_scored;               /* passed the covered-interval reject (src/NewEdgeCalculator.cpp:1252) */
+    int64_t pairs_walked;               /* also passed the layout rejects (:1268-1365) */
+    int64_t edges;
+    int64_t sum_cc, sum_tc;             /* column steps */
+    int64_t undefined;
+    int64_t ambiguous;                  /* number found (may exceed the capacity given) */
+    float kernel_ms;                    /* device time of the scoring kernel, CUDA events on its stream */
+    int32_t launches;
+} hc_band_stats;
+
+typedef struct hc_ctx hc_ctx;
+
+int hc_abi_version(void);
+int hc_device_count(void);
+const char* hc_last_error(const hc_ctx* ctx);   /* ctx may be NULL: error of the last failed hc_create/hc_pack */
+
+int hc_create(const hc_params* params, hc_ctx** out);
+void hc_destroy(hc_ctx* ctx);
+
+/* Host-side packing (C++, no GPU needed): validates, re-codes qualities, builds headers and op records.
+ * The output buffers are page-locked when a CUDA device is present (faster hc_upload), plain otherwise. */
+int hc_pack(const hc_reads* reads, hc_packed** out);
+void hc_packed_free(hc_packed* p);
+
+/* Copies a packed batch to the device (replaces the previous one). */
+int hc_upload(hc_ctx* ctx, const hc_packed* p);
+
+/* Band layout for rows [row_begin,row_end): row i holds bits for columns j in [col0[i], i), col0 a
+ * multiple of 32, chosen so that every j < col0[i] fails the covered-interval reject against i.
+ * word_off[k] (k = i-row_begin, row_end-row_begin+1 entries) = first 32-bit word of row i in the
+ * adjacency buffer. Returns the total number of words through *n_words. */
+int hc_band_layout(hc_ctx* ctx, int32_t row_begin, int32_t row_end, int32_t* col0, int64_t* word_off,
+                   int64_t* n_words);
+
+/* Scores every ordered pair (i, j<i) of rows [row_begin,row_end) that lies in the band and writes the
+ * adjacency bits (bit (j-col0[i]) of row i = edgeBetween(read i, read j)) to host memory `adj`
+ * (n_words words, see hc_band_layout; may be NULL to keep the result on the device only).
+ * amb/amb_cap: optional list of pairs whose score is within the tolerance of the threshold. */
+int hc_score_band(hc_ctx* ctx, int32_t row_begin, int32_t row_end, uint32_t* adj, int64_t n_words,
+                  hc_ambiguous* amb, int32_t amb_cap, hc_band_stats* stats);
+
+/* Scores an explicit list of ordered pairs (ap1 = pi[k], ap2 = pj[k]), full detail per pair. */
+int hc_score_pairs(hc_ctx* ctx, const int32_t* pi, const int32_t* pj, int64_t npairs, hc_pair_result* out);
+
+/* Replaces the scalar scoring parameters (cutoffs, min overlaps, no_prob0, tolerance) of a live context;
+ * the allele-frequency map and the device stay as given to hc_create. Mirrors
+ * EdgeCalculator::setOverlapCliques (src/EdgeCalculator.h:35). */
+int hc_set_params(hc_ctx* ctx, const hc_params* params);
+
+/* Evicts the device L2 by overwriting a scratch buffer larger than it (benchmark hygiene between timed
+ * iterations); asynchronous on the context's stream. */
+int hc_l2_flush(hc_ctx* ctx);
+
+/* Page-locked host memory for the adjacency / input buffers (plain cudaHostAlloc / cudaFreeHost). */
+void* hc_host_alloc(int64_t bytes);
+void hc_host_free(void* p);
+
+/* The two 127x127 match-probability tables the context uploaded (row-major [q1][q2], doubles). */
+int hc_get_tables(const hc_ctx* ctx, double* eq127x127, double* uneq127x127);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HC_EDGE_H_ */

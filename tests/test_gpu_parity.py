@@ -1,0 +1,139 @@
+"""GPU: the CUDA path (through the C ABI) against the oracle on the same inputs, and against the golden digests
+of the unmodified reference. Bit-exact on status/gap/cc/tc/probM/prob0; the edge decision may differ only on
+pairs the device itself reports as within 1e-12 (relative) of the threshold."""
+import numpy as np
+import pytest
+
+from haploclique_b200 import edge, synth
+from oracle import pyoracle
+from tests import common
+
+pytestmark = pytest.mark.gpu
+
+
+def _calc(params, max_position):
+    kw = common.calc_kwargs(params, max_position)
+    return edge.NewEdgeCalculator(**kw)
+
+
+@pytest.mark.parametrize("label", sorted(common.DATASETS))
+def test_pairs_match_oracle_and_golden(golden, label):
+    g = golden[label]
+    b = common.load_batch(common.DATASETS[label])
+    calc = _calc(g["params"], g["max_position"])
+    calc.upload(b)
+    pi, pj = common.tri_pairs(b.n)
+    dev = calc.score_pairs(pi, pj)
+    orc = pyoracle.Oracle(b, **common.calc_kwargs(g["params"], g["max_position"])).pairs(pi, pj)
+    differing = common.assert_pairs_equal(dev, orc, label)
+    h_edge, h_detail = common.pair_digests(dev["status"], dev["edge"], dev["gap"], dev["cc"], dev["tc"],
+                                           dev["probM"], dev["prob0"])
+    assert h_detail == g["sha256_detail"]
+    if differing == 0:
+        assert h_edge == g["sha256_edges"] and int(dev["edge"].sum()) == g["edges"]
+
+
+@pytest.mark.parametrize("label", ["hiv50_default", "arabis_weak_noprob0", "superreads_arabis_it1"])
+def test_band_adjacency_matches_oracle(golden, label):
+    g = golden[label]
+    b = common.load_batch(common.DATASETS[label])
+    calc = _calc(g["params"], g["max_position"])
+    adj = calc.scoreBatch(b)
+    edges, e = pyoracle.Oracle(b, **common.calc_kwargs(g["params"], g["max_position"])).all_pairs(detail=False)
+    pi, pj = common.tri_pairs(b.n)
+    ai, aj = adj.edges()
+    assert adj.stats["ambiguous"] == 0
+    assert adj.count() == edges == g["edges"]
+    assert (ai == pi[e == 1]).all() and (aj == pj[e == 1]).all()
+    assert adj.stats["edges"] == edges
+    assert adj.stats["pairs_scored"] == g["prefilter_pass"] + int(0) or adj.stats["pairs_walked"] == g["prefilter_pass"]
+    assert adj.stats["pairs_walked"] == g["prefilter_pass"]
+    assert adj.stats["sum_cc"] >= g["sum_cc"] and adj.stats["undefined"] == 0
+    # spot-check the lookup the clique finders would do
+    rng = np.random.default_rng(0)
+    for k in rng.integers(0, pi.shape[0], 200):
+        assert adj.edge(int(pi[k]), int(pj[k])) == bool(e[k])
+
+
+def test_reference_unit_expectations_through_edgeBetween(golden):
+    b = common.load_batch("unit_fixtures.npz")
+    recs = b.records()
+    calc = edge.NewEdgeCalculator(0.9, 0.99, 0.9, False, {}, 0.95, 0.6, 0.97, 20000, False)   # unit2.cpp:23-34 order
+    for name, case in golden["unit2"].items():
+        assert calc.edgeBetween(recs[case["ap1"]], recs[case["ap2"]]) == case["expected"], name
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_zoo_all_layouts_both_orders(seed):
+    b = synth.zoo(140, seed=seed)
+    kw = dict(noProb0=bool(seed % 2), edge_quasi_cutoff_single=0.8, edge_quasi_cutoff_mixed=0.85,
+              edge_quasi_cutoff=0.9, overlap=0.3, overlap_single=0.2, maxPosition=b.max_position())
+    pi, pj = common.tri_pairs(b.n)
+    pi, pj = np.concatenate([pi, pj]), np.concatenate([pj, pi])        # also ap1 = the EARLIER read
+    calc = edge.NewEdgeCalculator(**kw)
+    calc.upload(b)
+    dev = calc.score_pairs(pi, pj)
+    orc = pyoracle.Oracle(b, **kw).pairs(pi, pj)
+    common.assert_pairs_equal(dev, orc, "zoo%d" % seed)
+    assert set(np.unique(orc["layout"])) >= {100, 200, 300, 400}
+
+
+@pytest.mark.parametrize("noprob0", [False, True])
+def test_synthetic_quasispecies_with_allele_frequencies(noprob0):
+    b = synth.quasispecies(600, genome_len=1800, seed=11, indel_err=2e-3, clip_frac=0.1)
+    rng = np.random.default_rng(5)
+    simpson = {int(p): float(np.log10(rng.uniform(0.3, 1.0))) for p in rng.choice(np.arange(1, 1800), 900, replace=False)}
+    kw = dict(noProb0=noprob0, simpson_map=simpson, maxPosition=max(b.max_position(), max(simpson)), edge_quasi_cutoff_single=0.9)
+    calc = edge.NewEdgeCalculator(**kw)
+    calc.upload(b)
+    pi, pj = common.tri_pairs(b.n)
+    dev = calc.score_pairs(pi, pj)
+    orc = pyoracle.Oracle(b, **kw).pairs(pi, pj)
+    common.assert_pairs_equal(dev, orc, "simpson")
+    adj = calc.score_band()
+    assert adj.count() == int(orc["edge"].sum())
+
+
+def test_long_overlap_underflow_is_reproduced():
+    # 6000-column identical low-quality reads: the fp64 product underflows to 0 -> log10 = -inf -> no edge,
+    # which a log-domain sum would get wrong (SURVEY.md 7 "hard parts")
+    from haploclique_b200.records import AlignmentRecord, ReadBatch
+    n = 6000
+    rng = np.random.default_rng(3)
+    seq = bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), n))
+    a = AlignmentRecord("Clique_1", True, 1, n, b"M" * n, seq, bytes([33 + 3]) * n)
+    c = AlignmentRecord("Clique_2", True, 1, n, b"M" * n, seq, bytes([33 + 3]) * n)
+    b = ReadBatch.from_records([a, c])
+    kw = dict(edge_quasi_cutoff=0.1, overlap=0.5, noProb0=True, maxPosition=n)
+    calc = edge.NewEdgeCalculator(**kw)
+    calc.upload(b)
+    dev = calc.score_pairs([1], [0])
+    orc = pyoracle.Oracle(b, **kw).pairs([1], [0])
+    common.assert_pairs_equal(dev, orc, "underflow")
+    assert dev["probM"][0] == 0.0 and dev["edge"][0] == 0 and dev["cc"][0] == n
+
+
+def test_empty_ragged_and_tiny_batches():
+    from haploclique_b200.records import ReadBatch
+    b = common.load_batch("unit_fixtures.npz")
+    calc = edge.NewEdgeCalculator(maxPosition=20000)
+    for sel in ([], [3], [0, 0], list(range(10))):
+        sub = b.select(sel) if sel else ReadBatch.from_records([])
+        adj = calc.scoreBatch(sub)
+        edges, _ = pyoracle.Oracle(sub, maxPosition=20000).all_pairs(detail=False) if sub.n else (0, None)
+        assert adj.count() == edges
+    with pytest.raises(edge.HcError):
+        calc.upload(b.select([0]))
+        calc.score_pairs([5], [0])
+
+
+def test_setOverlapCliques_changes_the_decision():
+    b = common.load_batch("superreads_arabis_it2.npz")
+    kw = dict(common.WEAK, noProb0=True, maxPosition=b.max_position())
+    calc = edge.NewEdgeCalculator(**kw)
+    e0 = calc.scoreBatch(b).count()
+    calc.setOverlapCliques(0.99)
+    e1 = calc.score_band().count()
+    orc_kw = dict(kw, overlap=0.99)
+    edges, _ = pyoracle.Oracle(b, **orc_kw).all_pairs(detail=False)
+    assert e1 == edges and e1 <= e0
