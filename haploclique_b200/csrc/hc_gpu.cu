@@ -58,43 +58,45 @@ struct Phase { uint8_t op, x, y, a, b; };
 #define MAXPH 12
 enum { PROG_PP0 = 0, PROG_PS0 = 12, PROG_SP0 = 14, N_PROGS = 16 };
 
-__constant__ Phase c_prog[N_PROGS][MAXPH] = {
-    // paired x paired, checkGapsPaired branches 2..13 (src/NewEdgeCalculator.cpp)
-    /* :444 */ {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), P_OVL(1, 0, Be1),
-                P_TLT(0, 1, Bs2), P_SEAT(1, 1), P_OVL2(1, 1, xBe2, xAe2), P_FIN(xBe2, xAe2), P_END},
-    /* :482 */ {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1),
-                P_OVL2(1, 0, xBe1, xAe2), P_FIN(xBe1, xAe2), P_END},
-    /* :513 */ {P_START(xBs1), P_TLT(1, 0, xAs2), P_OVL(1, 0, Be1), P_TLT(0, 1, Bs2), P_SEAT(1, 1),
-                P_OVL2(1, 1, xBe2, xAe2), P_FIN(xBe2, xAe2), P_END},
-    /* :543 */ {P_START(xAs2), P_TLT(0, 1, xBs1), P_OVL(1, 0, Be1), P_TLT(0, 1, Bs2), P_SEAT(1, 1),
-                P_OVL2(1, 1, xAe2, xBe2), P_FIN(xAe2, xBe2), P_END},
-    /* :574 */ {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), P_OVL(0, 1, Ae1),
-                P_TLT(1, 1, As2), P_SEAT(0, 1), P_OVL2(1, 1, xBe2, xAe2), P_FIN(xBe2, xAe2), P_END},
-    /* :613 */ {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1),
-                P_OVLQX(0, 1, xAe1, xBe2), P_FIN(xAe1, xBe2), P_END},
-    /* :646 */ {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), P_OVL(1, 0, Be1),
-                P_TLT(0, 1, Bs2), P_SEAT(1, 1), P_OVL2(1, 1, xAe2, xBe2), P_FIN(xAe2, xBe2), P_END},
-    /* :684 */ {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1),
-                P_OVL2(1, 0, xBe1, xAe2), P_FIN(xBe1, xAe2), P_END},
-    /* :714 */ {P_START(xAs1), P_TLT(0, 0, xBs2), P_OVL(0, 1, Ae1), P_TLT(1, 1, As2), P_SEAT(0, 1),
-                P_OVL2(1, 1, xAe2, xBe2), P_FIN(xAe2, xBe2), P_END},
-    /* :744 */ {P_START(xBs2), P_TLT(1, 1, xAs1), P_OVL(0, 1, Ae1), P_TLT(1, 1, As2), P_SEAT(0, 1),
-                P_OVL2(1, 1, xAe2, xBe2), P_FIN(xAe2, xBe2), P_END},
-    /* :774 */ {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), P_OVL(0, 1, Ae1),
-                P_TLT(1, 1, As2), P_SEAT(0, 1), P_OVL2(1, 1, xBe2, xAe2), P_FIN(xBe2, xAe2), P_END},
-    /* :813 */ {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1),
-                P_OVL2(0, 1, xAe1, xBe2), P_FIN(xAe1, xBe2), P_END},
-    // ap1 paired x ap2 single-end, checkGapsMixed (:893, :922)
-    {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), P_OVL2(1, 0, xAe2, xBe1),
-     P_FIN(xAe2, xBe1), P_END},
-    {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), P_OVL2(1, 0, xAe2, xBe1),
-     P_FIN(xAe2, xBe1), P_END},
-    // ap1 single-end x ap2 paired, checkGapsMixed (:993, :1025)
-    {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), P_OVL2(0, 1, xBe2, xAe1),
-     P_FIN(xBe2, xAe1), P_END},
-    {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), P_OVL2(0, 1, xBe2, xAe1),
-     P_FIN(xBe2, xAe1), P_END},
-};
+// Linear phase programs. Order: checkGapsPaired branches 2..13 (:444 :482 :513 :543 :574 :613 :646 :684 :714 :744 :774 :813),
+// then ap1 paired x ap2 single-end (checkGapsMixed :893, :922), then ap1 single-end x ap2 paired (:993, :1025).
+#define HC_PROG_TABLE { \
+    /* :444 */ {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), P_OVL(1, 0, Be1), \
+                P_TLT(0, 1, Bs2), P_SEAT(1, 1), P_OVL2(1, 1, xBe2, xAe2), P_FIN(xBe2, xAe2), P_END}, \
+    /* :482 */ {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), \
+                P_OVL2(1, 0, xBe1, xAe2), P_FIN(xBe1, xAe2), P_END}, \
+    /* :513 */ {P_START(xBs1), P_TLT(1, 0, xAs2), P_OVL(1, 0, Be1), P_TLT(0, 1, Bs2), P_SEAT(1, 1), \
+                P_OVL2(1, 1, xBe2, xAe2), P_FIN(xBe2, xAe2), P_END}, \
+    /* :543 */ {P_START(xAs2), P_TLT(0, 1, xBs1), P_OVL(1, 0, Be1), P_TLT(0, 1, Bs2), P_SEAT(1, 1), \
+                P_OVL2(1, 1, xAe2, xBe2), P_FIN(xAe2, xBe2), P_END}, \
+    /* :574 */ {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), P_OVL(0, 1, Ae1), \
+                P_TLT(1, 1, As2), P_SEAT(0, 1), P_OVL2(1, 1, xBe2, xAe2), P_FIN(xBe2, xAe2), P_END}, \
+    /* :613 */ {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), \
+                P_OVLQX(0, 1, xAe1, xBe2), P_FIN(xAe1, xBe2), P_END}, \
+    /* :646 */ {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), P_OVL(1, 0, Be1), \
+                P_TLT(0, 1, Bs2), P_SEAT(1, 1), P_OVL2(1, 1, xAe2, xBe2), P_FIN(xAe2, xBe2), P_END}, \
+    /* :684 */ {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), \
+                P_OVL2(1, 0, xBe1, xAe2), P_FIN(xBe1, xAe2), P_END}, \
+    /* :714 */ {P_START(xAs1), P_TLT(0, 0, xBs2), P_OVL(0, 1, Ae1), P_TLT(1, 1, As2), P_SEAT(0, 1), \
+                P_OVL2(1, 1, xAe2, xBe2), P_FIN(xAe2, xBe2), P_END}, \
+    /* :744 */ {P_START(xBs2), P_TLT(1, 1, xAs1), P_OVL(0, 1, Ae1), P_TLT(1, 1, As2), P_SEAT(0, 1), \
+                P_OVL2(1, 1, xAe2, xBe2), P_FIN(xAe2, xBe2), P_END}, \
+    /* :774 */ {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), P_OVL(0, 1, Ae1), \
+                P_TLT(1, 1, As2), P_SEAT(0, 1), P_OVL2(1, 1, xBe2, xAe2), P_FIN(xBe2, xAe2), P_END}, \
+    /* :813 */ {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), \
+                P_OVL2(0, 1, xAe1, xBe2), P_FIN(xAe1, xBe2), P_END}, \
+    {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), P_OVL2(1, 0, xAe2, xBe1), \
+     P_FIN(xAe2, xBe1), P_END}, \
+    {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Ae1), P_TLT(1, 0, As2), P_SEAT(0, 1), P_OVL2(1, 0, xAe2, xBe1), \
+     P_FIN(xAe2, xBe1), P_END}, \
+    {P_START(xAs1), P_TLT(0, 0, xBs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), P_OVL2(0, 1, xBe2, xAe1), \
+     P_FIN(xBe2, xAe1), P_END}, \
+    {P_START(xBs1), P_TLT(1, 0, xAs1), P_OVL(0, 0, Be1), P_TLT(0, 0, Bs2), P_SEAT(1, 1), P_OVL2(0, 1, xBe2, xAe1), \
+     P_FIN(xBe2, xAe1), P_END}, \
+}
+__constant__ Phase c_prog[N_PROGS][MAXPH] = HC_PROG_TABLE;
+static const Phase h_prog[N_PROGS][MAXPH] = HC_PROG_TABLE;
+
 
 // ---- scoring parameters on the device ----------------------------------------------------------------
 struct DevParams {
@@ -188,7 +190,7 @@ __device__ __forceinline__ bool ovl_loop(const DevParams& P, WalkState& w, const
                 if (cq >= A.n) { w.undefined = true; return false; }
                 sa = A.ops[cq];
             }
-            const int idx = (int)(sa & 127u) * P.K + (int)(rb & 127u) + ((((sa ^ rb) >> HC_BASE_SHIFT) & 7u) ? P.KK : 0);
+            const int idx = (int)((sa >> HC_QUAL_SHIFT) & 127u) * P.K + (int)((rb >> HC_QUAL_SHIFT) & 127u) + ((((sa ^ rb) >> HC_BASE_SHIFT) & 7u) ? P.KK : 0);
             w.probM = __dmul_rn(w.probM, __ldg(P.table + idx));                // computeProbM (:122-131)
             w.cc++;
             if (oa == HC_OP_M) w.ref++;
@@ -455,6 +457,8 @@ __global__ void __launch_bounds__(256) score_band_kernel(DevParams P, const hc_r
     }
 }
 
+#include "hc_tile.cuh"
+
 }  // namespace
 
 // ======================================= host side of the C ABI =======================================
@@ -483,6 +487,14 @@ struct hc_ctx {
     int32_t* d_pi = nullptr; int32_t* d_pj = nullptr; hc_pair_result* d_res = nullptr; size_t pairs_cap = 0;
     std::vector<int32_t> lay_col0; std::vector<long long> lay_off; int lay_begin = -1, lay_end = -1;
     void* d_flush = nullptr; size_t flush_bytes = 0;
+    // tiled band kernel (hc_tile.cuh)
+    uint32_t* d_aux = nullptr; uint16_t* d_col2op = nullptr; uint32_t* d_tprog = nullptr;
+    int4* d_items = nullptr; size_t items_cap = 0; int* d_item_counter = nullptr;
+    hc_pair_result* d_detail = nullptr; size_t detail_cap = 0;
+    int kernel_mode = HC_KERNEL_AUTO;
+    int last_kernel = 0;
+    size_t smem_optin = 0;
+    std::vector<int4> items; int items_begin = -1, items_end = -1;
     std::string err;
 };
 
@@ -551,6 +563,99 @@ int compute_layout(hc_ctx* c, int row_begin, int row_end) {
     return HC_OK;
 }
 
+// Slotted programs for the tiled kernel: the overlap phases of every program sit in slots 3, 7 and 11, the O(1)
+// phases in front of them, the closing FIN / tail in slot 12 (hc_tile.cuh).
+void build_tile_programs(std::vector<uint32_t>& out) {
+    using namespace tile;
+    out.assign((size_t)TP_COUNT * TP_WORDS, 0u);
+    for (int k = 0; k < N_PROGS; ++k) {
+        uint32_t* pg = &out[(size_t)k * TP_WORDS];
+        int slot = 0, pre = 0;
+        for (int t = 0; t < MAXPH && h_prog[k][t].op != PH_END; ++t) {
+            const Phase ph = h_prog[k][t];
+            switch (ph.op) {
+                case PH_START: pg[slot * 4 + pre++] = TILE_MOP(M_START, 0, 0, ph.a, 0); break;
+                case PH_TAIL_LT: pg[slot * 4 + pre++] = TILE_MOP(M_TLT, ph.x, ph.y, ph.a, 0); break;
+                case PH_SEAT: pg[slot * 4 + pre++] = TILE_MOP(M_SEAT, ph.x, ph.y, 0, 0); break;
+                case PH_OVL: pg[slot * 4 + 3] = TILE_MOP(M_OVL, ph.x, ph.y, ph.a, 0); slot++; pre = 0; break;
+                case PH_OVL2: pg[slot * 4 + 3] = TILE_MOP(M_OVL2, ph.x, ph.y, ph.a, ph.b); slot++; pre = 0; break;
+                case PH_OVL2_QX: pg[slot * 4 + 3] = TILE_MOP(M_OVLQX, ph.x, ph.y, ph.a, ph.b); slot++; pre = 0; break;
+                case PH_FIN: pg[SLOT_FINAL] = TILE_MOP(M_FIN, 0, 0, ph.a, ph.b); break;
+                default: break;
+            }
+            if (pre > 3 || slot > 3) abort();          // a program that does not fit the slot template
+        }
+    }
+    const int single[3][2] = {{0, 0}, {1, 0}, {0, 1}};   // checkGapsSingle(segment of ap1, segment of ap2)
+    for (int k = 0; k < 3; ++k) {
+        uint32_t* pg = &out[(size_t)(TP_SINGLE00 + k) * TP_WORDS];
+        pg[0] = TILE_MOP(M_SPRE, single[k][0], single[k][1], 0, 0);
+        pg[SLOT_OVL0] = TILE_MOP(M_SOVL, single[k][0], single[k][1], 0, 0);
+        pg[SLOT_FINAL] = TILE_MOP(M_SPOST, single[k][0], single[k][1], 0, 0);
+    }
+    uint32_t* two = &out[(size_t)TP_TWO_SINGLES * TP_WORDS];   // :436-440: segments 1/1 then segments 2/2
+    two[0] = TILE_MOP(M_SPRE, 0, 0, 0, 0);
+    two[SLOT_OVL0] = TILE_MOP(M_SOVL, 0, 0, 0, 0);
+    two[4] = TILE_MOP(M_SPOST, 0, 0, 0, 0);
+    two[5] = TILE_MOP(M_SPRE, 1, 1, 0, 0);
+    two[SLOT_OVL1] = TILE_MOP(M_SOVL, 1, 1, 0, 0);
+    two[SLOT_FINAL] = TILE_MOP(M_SPOST, 1, 1, 0, 0);
+}
+
+struct TileGeom { int maxw, abuf_bytes; size_t smem; };
+
+TileGeom tile_geometry(const hc_ctx* c) {
+    TileGeom g;
+    g.maxw = (c->max_ops + 1) / 2 + 4;
+    g.abuf_bytes = ((c->max_ops * 2 + 15) & ~15) + 32;
+    size_t o = 0;
+    o += ((size_t)2 * c->K * c->K * 8 + 15) & ~(size_t)15;
+    o += (size_t)tile::TP_COUNT * tile::TP_WORDS * 4;
+    o += 16 * 32 * 4;
+    o += (size_t)g.maxw * 128;
+    o += (size_t)tile::kWarps * 2 * (64 + g.abuf_bytes);
+    o += tile::kWarps * 2 * 8;
+    o += 8 * 8;
+    o += 16;
+    g.smem = o;
+    return g;
+}
+
+// The tiled kernel needs: no allele-frequency map (prob0 comes from the ladder), and a column tile that fits.
+bool tile_eligible(const hc_ctx* c) {
+    if (c->d_simpson != nullptr) return false;
+    return tile_geometry(c).smem <= c->smem_optin;
+}
+
+// Work items of the tiled kernel for rows [row_begin,row_end): (column block, chunk of rows whose band reaches it).
+void build_items(hc_ctx* c, int row_begin, int row_end, int n_ctas) {
+    if (c->items_begin == row_begin && c->items_end == row_end) return;
+    c->items.clear();
+    const int nrows = row_end - row_begin;
+    if (nrows > 0) {
+        std::vector<int32_t> smin(nrows);                   // suffix minimum of col0: monotone, so "rows that reach block jb" is a prefix
+        int32_t run = INT32_MAX;
+        for (int k = nrows - 1; k >= 0; --k) { run = std::min(run, c->lay_col0[k]); smin[k] = run; }
+        const int jb_lo = smin[0] / 32, jb_hi = (row_end - 2) / 32;
+        std::vector<int> first, last;
+        long long total = 0;
+        for (int jb = jb_lo; jb <= jb_hi; ++jb) {
+            const int f = std::max(row_begin, jb * 32 + 1);
+            const int l = row_begin + (int)(std::upper_bound(smin.begin(), smin.end(), jb * 32) - smin.begin()) - 1;
+            first.push_back(f); last.push_back(l);
+            if (l >= f) total += l - f + 1;
+        }
+        long long chunk = (total + (long long)n_ctas * 16 - 1) / ((long long)n_ctas * 16);
+        chunk = std::max<long long>(32, std::min<long long>(chunk, 4096));
+        for (int jb = jb_lo; jb <= jb_hi; ++jb) {
+            const int f = first[jb - jb_lo], l = last[jb - jb_lo];
+            for (long long r = f; r <= l; r += chunk) c->items.push_back(make_int4(jb, (int)r, (int)std::min<long long>(r + chunk, (long long)l + 1), 0));
+        }
+    }
+    c->items_begin = row_begin;
+    c->items_end = row_end;
+}
+
 }  // namespace
 
 extern "C" {
@@ -594,6 +699,14 @@ int hc_create(const hc_params* params, hc_ctx** out) {
     cudaDeviceProp prop;
     if ((e = cudaGetDeviceProperties(&prop, c->device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
     c->sm_count = prop.multiProcessorCount;
+    c->smem_optin = prop.sharedMemPerBlockOptin;
+    {
+        std::vector<uint32_t> tp;
+        build_tile_programs(tp);
+        if ((e = cudaMalloc((void**)&c->d_tprog, tp.size() * sizeof(uint32_t))) != cudaSuccess) return fail("cudaMalloc", e);
+        if ((e = cudaMemcpy(c->d_tprog, tp.data(), tp.size() * sizeof(uint32_t), cudaMemcpyHostToDevice)) != cudaSuccess) return fail("cudaMemcpy", e);
+        if ((e = cudaMalloc((void**)&c->d_item_counter, sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
+    }
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
     if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
@@ -613,6 +726,8 @@ void hc_destroy(hc_ctx* c) {
     cudaFree(c->d_hdr); cudaFree(c->d_ops); cudaFree(c->d_table); cudaFree(c->d_simpson); cudaFree(c->d_ladder);
     cudaFree(c->d_col0); cudaFree(c->d_word_off); cudaFree(c->d_adj); cudaFree(c->d_stats); cudaFree(c->d_amb);
     cudaFree(c->d_pi); cudaFree(c->d_pj); cudaFree(c->d_res); cudaFree(c->d_flush);
+    cudaFree(c->d_aux); cudaFree(c->d_col2op); cudaFree(c->d_tprog); cudaFree(c->d_items); cudaFree(c->d_item_counter);
+    cudaFree(c->d_detail);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -657,8 +772,9 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     if (!c || !p) return HC_E_INVALID;
     CU_TRY(c, cudaSetDevice(c->device));
     CU_TRY(c, cudaStreamSynchronize(c->stream));
-    cudaFree(c->d_hdr); cudaFree(c->d_ops); cudaFree(c->d_table); cudaFree(c->d_ladder);
-    c->d_hdr = nullptr; c->d_ops = nullptr; c->d_table = nullptr; c->d_ladder = nullptr;
+    cudaFree(c->d_hdr); cudaFree(c->d_ops); cudaFree(c->d_table); cudaFree(c->d_ladder); cudaFree(c->d_aux); cudaFree(c->d_col2op);
+    c->d_hdr = nullptr; c->d_ops = nullptr; c->d_table = nullptr; c->d_ladder = nullptr; c->d_aux = nullptr; c->d_col2op = nullptr;
+    c->items_begin = c->items_end = -1;
     c->n_reads = p->n_reads;
     c->K = std::max(p->n_qual_codes, 1);
     c->max_ops = p->max_ops_per_read;
@@ -684,6 +800,13 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     hc::build_prob0_ladder(ladder, c->ladder_len - 1);
     CU_TRY(c, cudaMalloc((void**)&c->d_ladder, ladder.size() * sizeof(double)));
     CU_TRY(c, cudaMemcpyAsync(c->d_ladder, ladder.data(), ladder.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    // prefix counts of the segments that are not "clips, plain M, clips" (the tiled kernel's O(1) tails)
+    CU_TRY(c, cudaMalloc((void**)&c->d_aux, ((size_t)p->n_ops_total + 2 * (size_t)p->n_reads + 64) * sizeof(uint32_t)));
+    CU_TRY(c, cudaMalloc((void**)&c->d_col2op, ((size_t)p->n_ops_total + 64) * sizeof(uint16_t)));
+    if (p->n_reads > 0) {
+        tile::build_aux_kernel<<<(2 * p->n_reads + 127) / 128, 128, 0, c->stream>>>(c->d_hdr, c->d_ops, p->n_reads, c->d_aux, c->d_col2op);
+        CU_TRY(c, cudaGetLastError());
+    }
     c->cov_first.resize(p->n_reads);
     c->cov_last_pmax.resize(p->n_reads);
     int run = INT32_MIN;
@@ -708,8 +831,8 @@ int hc_band_layout(hc_ctx* c, int32_t row_begin, int32_t row_end, int32_t* col0,
     return HC_OK;
 }
 
-int hc_score_band(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32_t* adj, int64_t n_words, hc_ambiguous* amb,
-                  int32_t amb_cap, hc_band_stats* stats) {
+static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32_t* adj, int64_t n_words, hc_ambiguous* amb,
+                           int32_t amb_cap, hc_band_stats* stats, hc_pair_result* detail) {
     if (!c) return HC_E_INVALID;
     if (!c->d_hdr) { c->err = "hc_score_band: no batch uploaded"; return HC_E_STATE; }
     if (row_begin < 0 || row_end < row_begin || row_end > c->n_reads) { c->err = "hc_score_band: bad row range"; return HC_E_INVALID; }
@@ -717,12 +840,21 @@ int hc_score_band(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32_t* adj, 
     compute_layout(c, row_begin, row_end);
     const int nrows = row_end - row_begin;
     const long long total = c->lay_off[nrows];
-    if (adj && n_words < total) { c->err = "hc_score_band: adjacency buffer smaller than hc_band_layout's n_words"; return HC_E_INVALID; }
+    if ((adj || detail) && n_words < total) { c->err = "hc_score_band: output buffer smaller than hc_band_layout's n_words"; return HC_E_INVALID; }
+    const bool can_tile = tile_eligible(c);
+    if (c->kernel_mode == HC_KERNEL_TILED && !can_tile) {
+        c->err = "hc_score_band: the tiled kernel was requested but this batch / parameter set is not eligible "
+                 "(allele-frequency map set, or the column tile does not fit shared memory)";
+        return HC_E_STATE;
+    }
+    const bool use_tile = can_tile && c->kernel_mode != HC_KERNEL_GENERIC;
+    if (detail && !use_tile) { c->err = "hc_score_band_detail: only the tiled kernel writes per-slot detail; use hc_score_pairs"; return HC_E_STATE; }
     int rc;
     size_t cap2 = c->rows_cap;
     if ((rc = grow(c, c->d_col0, c->rows_cap, (size_t)nrows + 1)) != HC_OK) return rc;
     if ((rc = grow(c, c->d_word_off, cap2, (size_t)nrows + 1)) != HC_OK) return rc;
     if ((rc = grow(c, c->d_adj, c->adj_cap, (size_t)std::max<long long>(total, 1))) != HC_OK) return rc;
+    if (detail && (rc = grow(c, c->d_detail, c->detail_cap, (size_t)std::max<long long>(total, 1) * 32)) != HC_OK) return rc;
     if (amb_cap > c->amb_cap) {
         cudaFree(c->d_amb); c->d_amb = nullptr; c->amb_cap = 0;
         CU_TRY(c, cudaMalloc((void**)&c->d_amb, (size_t)amb_cap * sizeof(hc_ambiguous)));
@@ -732,21 +864,58 @@ int hc_score_band(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32_t* adj, 
     CU_TRY(c, cudaMemcpyAsync(c->d_word_off, c->lay_off.data(), sizeof(long long) * ((size_t)nrows + 1), cudaMemcpyHostToDevice, c->stream));
     CU_TRY(c, cudaMemsetAsync(c->d_stats, 0, sizeof(BandStatsDev), c->stream));
     int launches = 0;
-    CU_TRY(c, cudaEventRecord(c->ev0, c->stream));
-    if (total > 0) {
-        const int threads = 256;
-        const long long want = (total + (threads / 32) - 1) / (threads / 32);
-        const int blocks = (int)std::min<long long>(want, (long long)c->sm_count * 8);
-        score_band_kernel<<<blocks, threads, 0, c->stream>>>(dev_params(c), c->d_hdr, c->d_ops, row_begin, nrows, c->d_col0,
-                                                             c->d_word_off, total, c->d_adj, c->d_stats,
-                                                             amb ? c->d_amb : nullptr, amb ? amb_cap : 0);
-        CU_TRY(c, cudaGetLastError());
-        launches = 1;
+    c->last_kernel = 0;
+    if (use_tile && total > 0) {
+        const TileGeom g = tile_geometry(c);
+        CU_TRY(c, cudaFuncSetAttribute(tile::score_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
+        int per_sm = 0;
+        CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile::score_tile_kernel, tile::kThreads, g.smem));
+        if (per_sm < 1) { c->err = "hc_score_band: tiled kernel does not fit on an SM"; return HC_E_CUDA; }
+        const int n_ctas = c->sm_count * per_sm;
+        build_items(c, row_begin, row_end, n_ctas);
+        const size_t n_items = c->items.size();
+        if ((rc = grow(c, c->d_items, c->items_cap, std::max<size_t>(n_items, 1))) != HC_OK) return rc;
+        CU_TRY(c, cudaMemcpyAsync(c->d_items, c->items.data(), sizeof(int4) * n_items, cudaMemcpyHostToDevice, c->stream));
+        CU_TRY(c, cudaMemsetAsync(c->d_item_counter, 0, sizeof(int), c->stream));
+        // words of rows whose band holds no scored column block stay zero
+        CU_TRY(c, cudaMemsetAsync(c->d_adj, 0, (size_t)total * sizeof(uint32_t), c->stream));
+        if (detail) CU_TRY(c, cudaMemsetAsync(c->d_detail, 0, (size_t)total * 32 * sizeof(hc_pair_result), c->stream));
+        tile::Args a{};
+        a.P = dev_params(c);
+        a.hdr = c->d_hdr; a.ops = c->d_ops; a.aux = c->d_aux; a.col2op = c->d_col2op; a.prog = c->d_tprog;
+        a.n_reads = c->n_reads; a.row_begin = row_begin; a.col0 = c->d_col0; a.word_off = c->d_word_off;
+        a.items = c->d_items; a.n_items = (int)n_items; a.item_counter = c->d_item_counter;
+        a.adj = c->d_adj; a.stats = c->d_stats; a.amb = amb ? c->d_amb : nullptr; a.amb_cap = amb ? amb_cap : 0;
+        a.detail = detail ? c->d_detail : nullptr;
+        a.maxw = g.maxw; a.abuf_bytes = g.abuf_bytes;
+        CU_TRY(c, cudaEventRecord(c->ev0, c->stream));
+        if (n_items > 0) {
+            const int blocks = (int)std::min<size_t>(n_items, (size_t)n_ctas);
+            tile::score_tile_kernel<<<blocks, tile::kThreads, g.smem, c->stream>>>(a);
+            CU_TRY(c, cudaGetLastError());
+            launches = 1;
+            c->last_kernel = HC_KERNEL_TILED;
+        }
+        CU_TRY(c, cudaEventRecord(c->ev1, c->stream));
+    } else {
+        CU_TRY(c, cudaEventRecord(c->ev0, c->stream));
+        if (total > 0) {
+            const int threads = 256;
+            const long long want = (total + (threads / 32) - 1) / (threads / 32);
+            const int blocks = (int)std::min<long long>(want, (long long)c->sm_count * 8);
+            score_band_kernel<<<blocks, threads, 0, c->stream>>>(dev_params(c), c->d_hdr, c->d_ops, row_begin, nrows, c->d_col0,
+                                                                 c->d_word_off, total, c->d_adj, c->d_stats,
+                                                                 amb ? c->d_amb : nullptr, amb ? amb_cap : 0);
+            CU_TRY(c, cudaGetLastError());
+            launches = 1;
+            c->last_kernel = HC_KERNEL_GENERIC;
+        }
+        CU_TRY(c, cudaEventRecord(c->ev1, c->stream));
     }
-    CU_TRY(c, cudaEventRecord(c->ev1, c->stream));
     BandStatsDev hs{};
     CU_TRY(c, cudaMemcpyAsync(&hs, c->d_stats, sizeof(hs), cudaMemcpyDeviceToHost, c->stream));
     if (adj && total > 0) CU_TRY(c, cudaMemcpyAsync(adj, c->d_adj, (size_t)total * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    if (detail && total > 0) CU_TRY(c, cudaMemcpyAsync(detail, c->d_detail, (size_t)total * 32 * sizeof(hc_pair_result), cudaMemcpyDeviceToHost, c->stream));
     CU_TRY(c, cudaStreamSynchronize(c->stream));
     if (amb && amb_cap > 0 && hs.ambiguous > 0) {
         const size_t k = (size_t)std::min<unsigned long long>(hs.ambiguous, (unsigned long long)amb_cap);
@@ -764,6 +933,25 @@ int hc_score_band(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32_t* adj, 
     }
     return HC_OK;
 }
+
+int hc_score_band(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32_t* adj, int64_t n_words, hc_ambiguous* amb,
+                  int32_t amb_cap, hc_band_stats* stats) {
+    return score_band_impl(c, row_begin, row_end, adj, n_words, amb, amb_cap, stats, nullptr);
+}
+
+int hc_score_band_detail(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32_t* adj, hc_pair_result* detail, int64_t n_words,
+                         hc_band_stats* stats) {
+    if (!detail) { if (c) c->err = "hc_score_band_detail: null detail buffer"; return HC_E_INVALID; }
+    return score_band_impl(c, row_begin, row_end, adj, n_words, nullptr, 0, stats, detail);
+}
+
+int hc_set_kernel(hc_ctx* c, int32_t mode) {
+    if (!c || mode < HC_KERNEL_AUTO || mode > HC_KERNEL_TILED) return HC_E_INVALID;
+    c->kernel_mode = mode;
+    return HC_OK;
+}
+
+int hc_last_kernel(const hc_ctx* c) { return c ? c->last_kernel : 0; }
 
 int hc_score_pairs(hc_ctx* c, const int32_t* pi, const int32_t* pj, int64_t npairs, hc_pair_result* out) {
     if (!c || npairs < 0 || (npairs > 0 && (!pi || !pj || !out))) return HC_E_INVALID;

@@ -128,6 +128,7 @@ int hc_pack(const hc_reads* rd, hc_packed** out) {
     p->owner = own;
 
     // pass 1: which quality chars occur -> dense codes; total op count
+    // Every read's op stream starts on a 16-byte boundary (8 records) so that one TMA bulk copy moves it
     bool seen[256] = {false};
     int64_t total_ops = 0;
     for (int r = 0; r < n; ++r) {
@@ -136,8 +137,14 @@ int hc_pack(const hc_reads* rd, hc_packed** out) {
             const int k = 2 * r + s;
             const uint8_t* q = rd->qual + rd->seq_off[k];
             for (int t = 0; t < rd->seq_len[k]; ++t) seen[q[t]] = true;
+            if (rd->cig_len[k] < 0 || rd->cig_len[k] > 65534) {
+                hc::set_global_error("hc_pack: a segment's unrolled CIGAR is longer than 65534 ops");
+                hc_packed_free(p);
+                return HC_E_INVALID;
+            }
             total_ops += rd->cig_len[k];
         }
+        total_ops = (total_ops + 7) & ~int64_t(7);
     }
     int code_of[256];
     int K = 0;
@@ -165,7 +172,7 @@ int hc_pack(const hc_reads* rd, hc_packed** out) {
     }
     hc_read_hdr* hdr_out = static_cast<hc_read_hdr*>(own->hdr.p);
     uint16_t* ops_out = static_cast<uint16_t*>(own->ops.p);
-    std::memset(ops_out + total_ops, 0, sizeof(uint16_t) * 64);
+    std::memset(ops_out, 0, sizeof(uint16_t) * (static_cast<size_t>(total_ops) + 64));
 
     // pass 2: headers and op records
     int64_t w = 0;
@@ -195,7 +202,7 @@ int hc_pack(const hc_reads* rd, hc_packed** out) {
             h.ops_off[s] = static_cast<uint32_t>(w);
             h.n_ops[s] = nc;
             int qi = 0;
-            bool ins = false;
+            bool ins = false, plain = true;      // plain: only M between the leading and the trailing clip run
             for (int t = 0; t < nc; ++t) {
                 const int op = op_code(cg[t]);
                 if (op < 0) {
@@ -211,16 +218,19 @@ int hc_pack(const hc_reads* rd, hc_packed** out) {
                         hc_packed_free(p);
                         return HC_E_INVALID;
                     }
-                    rec |= static_cast<uint16_t>(base_code(sq[qi]) << HC_BASE_SHIFT) | static_cast<uint16_t>(code_of[ql[qi]]);
+                    rec |= static_cast<uint16_t>(base_code(sq[qi]) << HC_BASE_SHIFT) | static_cast<uint16_t>(code_of[ql[qi]] << HC_QUAL_SHIFT);
                     ++qi;
                 }
                 ins |= (op == HC_OP_I);
+                if (t >= lead && t < nc - trail && op != HC_OP_M) plain = false;
                 ops_out[static_cast<size_t>(w++)] = rec;
             }
-            h.has_ins[s] = ins ? 1 : 0;
+            if (lead + trail > nc) plain = false;             // a segment made of clips only
+            h.seg_flags[s] = static_cast<uint16_t>((ins ? HC_SEG_HAS_INS : 0) | (plain ? 0 : HC_SEG_NOT_PLAIN));
             read_ops += nc;
         }
         if (single) h.ops_off[1] = static_cast<uint32_t>(w);
+        w = (w + 7) & ~int64_t(7);
         if (read_ops > max_ops) max_ops = read_ops;
     }
     p->n_reads = n;

@@ -1,0 +1,550 @@
+// hc_tile.cuh -- the tiled band kernel (included by hc_gpu.cu after DevParams / op_action / BandStatsDev).
+//
+// Work shape. The adjacency band is cut into column blocks of 32 earlier reads ("j-block" = one 32-bit
+// adjacency word per row). A CTA takes one work item = (j-block, chunk of rows). The 32 column reads' op
+// streams are staged in shared memory once per item, transposed so that 32-bit word w of lane l sits at
+// tile[w*32+l] (bank == lane for any cursor position: conflict-free per-lane streaming). Each warp then takes
+// rows i from a shared counter; the row read's header and op stream arrive in the warp's own double buffer by
+// TMA bulk copies (cp.async.bulk + mbarrier) issued one row ahead. Lane l of the warp decides the pair
+// (ap1 = row read i, ap2 = column read 32*jb+l), so ap1's records are a shared-memory broadcast, the 32 edge
+// bits come out of one ballot, and the two match tables are read from shared memory.
+//
+// Walk. The reference's layouts (src/NewEdgeCalculator.cpp:269-1061) are phase programs as in the v1 kernel, but
+// re-slotted so that every program has its lock-step ("overlap") loops in the same three slots: the warp runs
+// three overlap loops in which all 32 lanes iterate together; the phases between them are O(1) per lane:
+//   * a tail (noOverlapCheckgap run, :234-267) only counts M/I ops and moves a cursor, so it is evaluated from
+//     per-segment prefix counts (arithmetic for segments that are plain M between their clips, two small
+//     lookups otherwise) instead of a loop; prob0 is then ladder[tc] (tc sequential additions of log10(0.25)),
+//     which is why this kernel is used only when no allele-frequency map is set;
+//   * the overlap loop multiplies probM by one table entry per shared column with __dmul_rn in increasing
+//     column order -- bit-identical to the reference's running product -- two columns per iteration while both
+//     reads show M (the common case), one generic step otherwise (clips, indels, the :629 cursor quirk).
+#pragma once
+
+namespace tile {
+
+enum : uint32_t { M_NOP = 0, M_START, M_TLT, M_SEAT, M_OVL, M_OVL2, M_OVLQX, M_FIN, M_SPRE, M_SOVL, M_SPOST };
+enum { TP_WORDS = 16, TP_SINGLE00 = 16, TP_SINGLE10 = 17, TP_SINGLE01 = 18, TP_TWO_SINGLES = 19, TP_NOP = 20, TP_COUNT = 21 };
+enum { SLOT_OVL0 = 3, SLOT_OVL1 = 7, SLOT_OVL2 = 11, SLOT_FINAL = 12 };
+#define TILE_MOP(op, x, y, a, b) ((uint32_t)(op) | ((uint32_t)(x) << 4) | ((uint32_t)(y) << 5) | ((uint32_t)(a) << 6) | ((uint32_t)(b) << 10))
+
+constexpr int kWarps = 16;
+constexpr int kThreads = kWarps * 32;
+constexpr unsigned FULL = 0xffffffffu;
+
+struct Args {
+    DevParams P;
+    const hc_read_hdr* hdr;
+    const uint16_t* ops;
+    const uint32_t* aux;        // per segment, n_ops+1 entries at ops_off[s] + 2*read + s: (non-I ops before c) << 16 | (M/I ops before c)
+    const uint16_t* col2op;     // per segment at ops_off[s]: op index of the k-th non-I op
+    const uint32_t* prog;       // [TP_COUNT][TP_WORDS] slotted programs
+    int n_reads, row_begin;
+    const int32_t* col0;        // per row (row - row_begin)
+    const long long* word_off;
+    const int4* items;          // {j-block, first row, end row, 0}
+    int n_items;
+    int* item_counter;
+    uint32_t* adj;
+    BandStatsDev* stats;
+    hc_ambiguous* amb;
+    int amb_cap;
+    hc_pair_result* detail;     // optional: one record per band slot (word*32 + lane)
+    int maxw;                   // 32-bit words per lane in the column tile (incl. read-ahead slack)
+    int abuf_bytes;             // bytes of one row op buffer (multiple of 16, incl. slack)
+};
+
+struct RowInfo { unsigned ops_off; int n_ops; int col0; long long word_off; };
+
+// ---- mbarrier / TMA bulk copy (1D) -----------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    for (unsigned spins = 0;; ++spins) {
+        uint32_t ok;
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n" : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+        if (ok) return;
+        if (spins > (1u << 24)) __trap();           // a bulk copy that never lands must fail loudly, not hang the GPU
+    }
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// ---- header access: A = the row read (16 ints, linear), B = the lane's column read (field f at hB[f*32]) -----
+// fields: 0-3 raw{s1,e1,s2,e2}  4-7 ext  8-9 ops_off  10-11 n_ops  12 ncov_flags  13 cov_first  14 cov_last  15 seg_flags
+__device__ __forceinline__ int bound(const int* hA, const int* hB, int id) {
+    const int f = ((id >> 3) << 2) | (id & 3);
+    return (id & 4) ? hB[f * 32] : hA[f];
+}
+
+struct Lane {
+    int ref, cc, tc;
+    double probM;
+    unsigned long long curs;   // four 16-bit CIGAR cursors, index side*2+seg
+    bool gap, undef;
+};
+
+__device__ __forceinline__ int get_cur(const Lane& L, int side, int seg) { return (int)((L.curs >> (16 * (side * 2 + seg))) & 0xffffull); }
+__device__ __forceinline__ void set_cur(Lane& L, int side, int seg, int c) {
+    const int sh = 16 * (side * 2 + seg);
+    L.curs = (L.curs & ~(0xffffull << sh)) | ((unsigned long long)(unsigned)c << sh);
+}
+
+// A run of noOverlapCheckgap steps on (side, seg) up to the exclusive column `limit`, in O(1).
+__device__ __forceinline__ void tail(const Args& a, const int* hA, const int* hB, int rA, int rB, int side, int seg, int limit, Lane& L) {
+    const int ncols = limit - L.ref;
+    if (ncols <= 0) return;
+    const int* h = side ? hB : hA;
+    const int st = side ? 32 : 1;
+    const int n = h[(10 + seg) * st];
+    const int c0 = get_cur(L, side, seg);
+    if (c0 >= n) { L.undef = true; return; }
+    const unsigned fl = ((unsigned)h[15 * st] >> (16 * seg)) & 0xffffu;
+    int c_end, dtc;
+    if (fl == 0) {                                   // clips, plain M, clips
+        c_end = c0 + ncols;
+        if (c_end > n) { L.undef = true; return; }
+        const int lead = h[(2 * seg) * st] - h[(4 + 2 * seg) * st];
+        const int trail = h[(5 + 2 * seg) * st] - h[(1 + 2 * seg) * st];
+        const int nm = n - lead - trail;
+        dtc = min(max(c_end - lead, 0), nm) - min(max(c0 - lead, 0), nm);
+    } else {
+        const unsigned off = (unsigned)h[(8 + seg) * st];
+        const uint32_t* ax = a.aux + (size_t)off + 2u * (unsigned)(side ? rB : rA) + seg;
+        const uint32_t x0 = __ldg(ax + c0), xn = __ldg(ax + n);
+        const int k0 = (int)(x0 >> 16), ktot = (int)(xn >> 16);
+        if (k0 + ncols > ktot) { L.undef = true; return; }
+        c_end = (int)__ldg(a.col2op + (size_t)off + k0 + ncols - 1) + 1;
+        dtc = (int)(__ldg(ax + c_end) & 0xffffu) - (int)(x0 & 0xffffu);
+    }
+    L.tc += dtc;
+    L.ref = limit;
+    set_cur(L, side, seg, c_end);
+}
+
+// One of the cheap (non-loop) micro-ops. `shape` carries checkGapsSingle's case between SPRE/SOVL/SPOST.
+__device__ __forceinline__ void cheap(const Args& a, const int* hA, const int* hB, int rA, int rB, uint32_t m, Lane& L, int& shape) {
+    const uint32_t op = m & 15u;
+    if (op == M_NOP || L.gap || L.undef) return;
+    const int x = (m >> 4) & 1, y = (m >> 5) & 1, ia = (m >> 6) & 15, ib = (m >> 10) & 15;
+    switch (op) {
+        case M_START: L.ref = bound(hA, hB, ia); break;
+        case M_TLT: tail(a, hA, hB, rA, rB, x, y, bound(hA, hB, ia), L); break;
+        case M_SEAT: {
+            const int* h = x ? hB : hA;
+            const int st = x ? 32 : 1;
+            set_cur(L, x, y, get_cur(L, x, y) + h[(2 * y) * st] - h[(4 + 2 * y) * st]);
+            break;
+        }
+        case M_FIN: {
+            int which = -1;
+            if (L.ref - 1 == bound(hA, hB, ia)) which = ib;
+            else if (L.ref - 1 == bound(hA, hB, ib)) which = ia;
+            if (which >= 0) tail(a, hA, hB, rA, rB, (which >> 2) & 1, (which >> 1) & 1, bound(hA, hB, which) + 1, L);
+            break;
+        }
+        case M_SPRE: {                               // checkGapsSingle (:269-395): shape, fresh cursors, leading tail
+            const int xs1 = hA[4 + 2 * x], xe1 = hA[5 + 2 * x], xs2 = hB[(4 + 2 * y) * 32], xe2 = hB[(5 + 2 * y) * 32];
+            if (xs1 <= xs2 && xe1 <= xe2) shape = 0;
+            else if (xs1 <= xs2 && xe1 >= xe2) shape = 1;
+            else if (xs1 >= xs2 && xe1 <= xe2) shape = 2;
+            else shape = 3;
+            set_cur(L, 0, x, 0);
+            set_cur(L, 1, y, 0);
+            if (shape < 2) { L.ref = xs1; tail(a, hA, hB, rA, rB, 0, x, xs2, L); }
+            else { L.ref = xs2; tail(a, hA, hB, rA, rB, 1, y, xs1, L); }
+            break;
+        }
+        case M_SPOST: {
+            if (shape == 0 || shape == 2) tail(a, hA, hB, rA, rB, 1, y, hB[(5 + 2 * y) * 32] + 1, L);
+            else tail(a, hA, hB, rA, rB, 0, x, hA[5 + 2 * x] + 1, L);
+            break;
+        }
+        default: break;
+    }
+}
+
+__device__ __forceinline__ bool consumes_q(uint32_t op) { return op == HC_OP_M || op == HC_OP_I || op == HC_OP_S; }
+
+// The lock-step loop of one slot, all 32 lanes together (lanes without an overlap phase in this slot idle).
+__device__ __forceinline__ void overlap(const Args& a, const int* hA, const int* hB, const uint16_t* opsA, const uint32_t* opsB,
+                                        const unsigned char* Tb, uint32_t m, Lane& L, int shape) {
+    const uint32_t op = m & 15u;
+    bool more = (op == M_OVL || op == M_OVL2 || op == M_OVLQX || op == M_SOVL) && !L.gap && !L.undef;
+    const int sa = (m >> 4) & 1, sb = (m >> 5) & 1;
+    const bool qx = op == M_OVLQX;
+    int hi = 0;
+    if (more) {
+        if (op == M_SOVL) hi = (shape == 0 || shape == 2) ? hA[5 + 2 * sa] : hB[(5 + 2 * sb) * 32];
+        else {
+            hi = bound(hA, hB, (m >> 6) & 15);
+            if (op != M_OVL) hi = min(hi, bound(hA, hB, (m >> 10) & 15));
+        }
+    }
+    const int nA = hA[10 + sa], nB = hB[(10 + sb) * 32];
+    const int aoff = sa ? hA[10] : 0, boff = sb ? hB[10 * 32] : 0;
+    int ca = get_cur(L, 0, sa), cb = get_cur(L, 1, sb);
+    int cq = 0;
+    if (more && qx) { while (cq < nA && !consumes_q(opsA[aoff + cq] >> HC_OP_SHIFT)) cq++; }
+    const uint32_t K = (uint32_t)a.P.K, KK8 = (uint32_t)a.P.KK * 8u;
+    const uint32_t* opsA32 = reinterpret_cast<const uint32_t*>(opsA);
+    int ref = L.ref, cc = L.cc;
+    double probM = L.probM;
+    for (;;) {
+        // -- two columns per iteration while both reads show M
+        if (more && !qx) {
+            const int run = min(min(hi - ref + 1, nA - ca), nB - cb);
+            if (run >= 2) {
+                const int ia = aoff + ca, ib = boff + cb;
+                const uint32_t* pa = opsA32 + (ia >> 1);
+                const uint32_t* pb = opsB + (ib >> 1) * 32;
+                const int sha = (ia & 1) * 16, shb = (ib & 1) * 16;
+                uint32_t a0 = pa[0], a1 = pa[1], b0 = pb[0], b1 = pb[32];
+                int done = 0;
+                do {
+                    const uint32_t a2 = __funnelshift_r(a0, a1, sha), b2 = __funnelshift_r(b0, b1, shb);
+                    a0 = a1; b0 = b1; pa += 1; pb += 32;
+                    a1 = pa[1]; b1 = pb[32];
+                    if ((a2 | b2) & 0x1C001C00u) break;
+                    const uint32_t x = a2 ^ b2;
+                    uint32_t o0 = (a2 & 0x3F8u) * K + (b2 & 0x3F8u);
+                    uint32_t o1 = ((a2 >> 16) & 0x3F8u) * K + ((b2 >> 16) & 0x3F8u);
+                    if (x & 0x00000007u) o0 += KK8;
+                    if (x & 0x00070000u) o1 += KK8;
+                    const double t0 = *reinterpret_cast<const double*>(Tb + o0);
+                    const double t1 = *reinterpret_cast<const double*>(Tb + o1);
+                    probM = __dmul_rn(probM, t0);
+                    probM = __dmul_rn(probM, t1);
+                    done += 2;
+                } while (done + 2 <= run);
+                ca += done; cb += done; ref += done; cc += done;
+            }
+        }
+        __syncwarp();
+        // -- one generic step (overlapCheckgap, :145-232)
+        if (more) {
+            if (ref > hi) more = false;
+            else if (ca >= nA || cb >= nB) { L.undef = true; more = false; }
+            else {
+                const uint32_t ra = opsA[aoff + ca];
+                const uint32_t wb = opsB[((boff + cb) >> 1) * 32];
+                const uint32_t rb = ((boff + cb) & 1) ? (wb >> 16) : (wb & 0xffffu);
+                const int oa = (int)(ra >> HC_OP_SHIFT), ob = (int)(rb >> HC_OP_SHIFT);
+                const int act = (oa | ob) == 0 ? ACT_SCORE : op_action(oa, ob);
+                if (act == ACT_SCORE) {
+                    uint32_t sq = ra;
+                    bool ok = true;
+                    if (qx) {
+                        if (cq >= nA) { L.undef = true; more = false; ok = false; }
+                        else sq = opsA[aoff + cq];
+                    }
+                    if (ok) {
+                        uint32_t o = (sq & 0x3F8u) * K + (rb & 0x3F8u);
+                        if ((sq ^ rb) & 7u) o += KK8;
+                        probM = __dmul_rn(probM, *reinterpret_cast<const double*>(Tb + o));
+                        cc++;
+                        if (oa == HC_OP_M) ref++;
+                        ca++; cb++;
+                        if (qx) { cq++; while (cq < nA && !consumes_q(opsA[aoff + cq] >> HC_OP_SHIFT)) cq++; }
+                    }
+                } else if (act == ACT_SKIP) {
+                    ref++; ca++; cb++;
+                    if (qx && consumes_q(oa)) { cq++; while (cq < nA && !consumes_q(opsA[aoff + cq] >> HC_OP_SHIFT)) cq++; }
+                } else if (act == ACT_ADV_A) {
+                    ca++;
+                    if (qx) { cq++; while (cq < nA && !consumes_q(opsA[aoff + cq] >> HC_OP_SHIFT)) cq++; }
+                } else if (act == ACT_ADV_B) {
+                    cb++;
+                } else {
+                    L.gap = true; more = false;
+                }
+            }
+        }
+        if (!__any_sync(FULL, more)) break;
+    }
+    L.ref = ref; L.cc = cc; L.probM = probM;
+    if (op == M_OVL || op == M_OVL2 || op == M_OVLQX || op == M_SOVL) { set_cur(L, 0, sa, ca); set_cur(L, 1, sb, cb); }
+}
+
+// checkGapsCigar dispatch (:1063-1074) + the layout choice of checkGapsPaired / checkGapsMixed -> program id.
+__device__ __forceinline__ int pick_program(const int* hA, const int* hB, bool se1, bool se2) {
+#define VA(f) hA[f]
+#define VB(f) hB[(f) * 32]
+    // raw: s1=0 e1=1 s2=2 e2=3; ext: +4
+    if (se1 && se2) return TP_SINGLE00;
+    if (!se1 && !se2) {
+        const int As1 = VA(0), Ae1 = VA(1), As2 = VA(2), Ae2 = VA(3), xAs1 = VA(4), xAs2 = VA(6);
+        const int Bs1 = VB(0), Be1 = VB(1), Bs2 = VB(2), Be2 = VB(3), xBs1 = VB(4), xBs2 = VB(6);
+        if (Ae1 < Bs2 && As2 > Be1) return TP_TWO_SINGLES;                                  // :436
+        if (xAs1 <= xBs1 && Ae1 >= Bs1 && As2 <= Be1 && Ae2 >= Bs2) return 0;
+        if (xAs1 <= xBs1 && Ae1 >= Bs1 && As2 <= Be1 && Ae2 < Bs2) return 1;
+        if (xBs1 <= xAs2 && Ae1 < Bs1 && As2 <= Be1 && Ae2 >= Bs2) return 2;
+        if (xAs2 <= xBs1 && Ae1 < Bs1 && As2 <= Be1 && Ae2 >= Bs2) return 3;
+        if (xAs1 <= xBs1 && As1 <= Be1 && Ae1 >= Bs2 && As2 <= Be2) return 4;
+        if (xAs1 <= xBs1 && As2 > Be2 && Ae1 >= Bs2 && As1 <= Be1) return 5;
+        if (xBs1 <= xAs1 && Ae1 >= Bs1 && As2 <= Be1 && Ae2 >= Bs2) return 6;
+        if (xBs1 <= xAs1 && Ae1 >= Bs1 && As2 <= Be1 && Ae2 < Bs2) return 7;
+        if (xAs1 <= xBs2 && As1 > Be1 && Ae1 >= Bs2 && As2 <= Be2) return 8;
+        if (xBs2 <= xAs1 && Be1 < As1 && Ae1 >= Bs2 && As2 <= Be2) return 9;
+        if (xBs1 <= xAs1 && As1 <= Be1 && Ae1 >= Bs2 && As2 <= Be2) return 10;
+        if (xBs1 <= xAs1 && As2 > Be2 && As1 <= Be1 && Ae1 >= Bs2) return 11;
+        return TP_NOP;                               // no layout matches: cc stays 0 (:841-844 under NDEBUG)
+    }
+    if (se2) {                                       // ap1 paired, ap2 single-end (:850-954)
+        if (VB(1) < VA(2)) return TP_SINGLE00;
+        if (VB(0) > VA(1)) return TP_SINGLE10;
+        return PROG_PS0 + (VB(4) <= VA(4) ? 0 : 1);
+    }
+    if (VA(1) < VB(2)) return TP_SINGLE00;           // ap1 single-end, ap2 paired (:955-1056)
+    if (VA(0) > VB(1)) return TP_SINGLE01;
+    return PROG_SP0 + (VA(4) <= VB(4) ? 0 : 1);
+#undef VA
+#undef VB
+}
+
+__device__ __forceinline__ bool tile_layout_reject(const int* hA, const int* hB, bool se1, bool se2) {
+    const int As1 = hA[0], Ae1 = hA[1], As2 = hA[2], Ae2 = hA[3];
+    const int Bs1 = hB[0], Be1 = hB[32], Bs2 = hB[64], Be2 = hB[96];
+    if (se1 && se2) return Ae1 < Bs1 || Be1 < As1;
+    if (!se1 && !se2)
+        return (Ae1 < Bs1 && Ae2 < Bs2) || (Be1 < As1 && Be2 < As2) || (Be1 < As2 && Ae2 < Bs2) || (Ae1 < Bs2 && Be2 < As2) ||
+               (Be1 < As1 && Ae1 < Bs2) || (Ae1 < Bs1 && Be1 < As2);
+    if (se1) return Ae1 < Bs1 || (Be1 < As1 && Ae1 < Bs2) || Be2 < As1;
+    return Ae2 < Bs1 || (Ae1 < Bs1 && Be1 < As2) || Be1 < As1;
+}
+
+__global__ void __launch_bounds__(kThreads, 2) score_tile_kernel(const Args a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int K = a.P.K;
+    // ---- shared memory carve-up (every piece a multiple of 16 bytes)
+    size_t o = 0;
+    double* Tsm = reinterpret_cast<double*>(smem + o);            o += ((size_t)2 * K * K * 8 + 15) & ~(size_t)15;
+    uint32_t* progsm = reinterpret_cast<uint32_t*>(smem + o);     o += TP_COUNT * TP_WORDS * 4;
+    int* hBsm = reinterpret_cast<int*>(smem + o);                 o += 16 * 32 * 4;
+    uint32_t* tileB = reinterpret_cast<uint32_t*>(smem + o);      o += (size_t)a.maxw * 128;
+    unsigned char* rowbuf = smem + o;                             o += (size_t)kWarps * 2 * (64 + a.abuf_bytes);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + o);       o += kWarps * 2 * 8;
+    unsigned long long* cstat = reinterpret_cast<unsigned long long*>(smem + o); o += 8 * 8;
+    int* ctl = reinterpret_cast<int*>(smem + o);
+
+    for (int k = tid; k < 2 * K * K; k += kThreads) Tsm[k] = a.P.table[k];
+    for (int k = tid; k < TP_COUNT * TP_WORDS; k += kThreads) progsm[k] = a.prog[k];
+    if (tid < 8) cstat[tid] = 0ull;
+    if (lane == 0) {
+        mbar_init(&bars[warp * 2 + 0], 1);
+        mbar_init(&bars[warp * 2 + 1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        fence_proxy_async();
+    }
+    const int bufstride = 64 + a.abuf_bytes;
+    unsigned char* const mybuf0 = rowbuf + (size_t)(warp * 2) * bufstride;
+    uint32_t parity = 0;       // bit k = phase parity of this warp's barrier k
+    const unsigned char* Tb = reinterpret_cast<const unsigned char*>(Tsm);
+    const int* hB = hBsm + lane;
+    const uint32_t* opsB = tileB + lane;
+
+    auto load_info = [&](int row, int r1) {
+        RowInfo ri;
+        ri.ops_off = 0; ri.n_ops = 0; ri.col0 = 0; ri.word_off = 0;
+        if (row < r1) {
+            const int4 h2 = __ldg(reinterpret_cast<const int4*>(a.hdr + row) + 2);
+            ri.ops_off = (unsigned)h2.x; ri.n_ops = h2.z + h2.w;
+            ri.col0 = __ldg(a.col0 + (row - a.row_begin));
+            ri.word_off = __ldg(a.word_off + (row - a.row_begin));
+        }
+        return ri;
+    };
+    auto issue = [&](int k, int row, const RowInfo& ri) {       // lane 0 only
+        const uint32_t ob = ((uint32_t)ri.n_ops * 2u + 15u) & ~15u;
+        uint64_t* bar = &bars[warp * 2 + k];
+        fence_proxy_async();
+        mbar_expect_tx(bar, 64u + ob);
+        bulk_g2s(mybuf0 + k * bufstride, a.hdr + row, 64u, bar);
+        if (ob) bulk_g2s(mybuf0 + k * bufstride + 64, a.ops + ri.ops_off, ob, bar);
+    };
+
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) ctl[0] = atomicAdd(a.item_counter, 1);
+        __syncthreads();
+        const int item = ctl[0];
+        if (item >= a.n_items) break;
+        const int4 it = a.items[item];
+        const int jb = it.x, r0 = it.y, r1 = it.z;
+        const int j0 = jb * 32;
+        // ---- stage the 32 column reads: headers transposed, op streams interleaved word-wise
+        for (int k = tid; k < 16 * 32; k += kThreads) {
+            const int l = k & 31, f = k >> 5;
+            const int j = j0 + l;
+            hBsm[f * 32 + l] = j < a.n_reads ? __ldg(reinterpret_cast<const int*>(a.hdr + j) + f) : 0;
+        }
+        {
+            const int l = tid & 31;
+            const int j = j0 + l;
+            if (j < a.n_reads) {
+                const int4 h2 = __ldg(reinterpret_cast<const int4*>(a.hdr + j) + 2);
+                const int nchunk = (h2.z + h2.w + 7) >> 3;
+                const uint4* src = reinterpret_cast<const uint4*>(a.ops + (unsigned)h2.x);
+                for (int c = tid >> 5; c < nchunk; c += kWarps) {
+                    const uint4 v = __ldg(src + c);
+                    uint32_t* d = tileB + (size_t)(4 * c) * 32 + l;
+                    d[0] = v.x; d[32] = v.y; d[64] = v.z; d[96] = v.w;
+                }
+            }
+        }
+        if (tid == 0) ctl[1] = r0;
+        __syncthreads();
+
+        // ---- rows: two grabbed ahead, the next row's bytes in flight while this one is walked
+        auto grab = [&]() {
+            int r = 0;
+            if (lane == 0) r = atomicAdd(&ctl[1], 1);
+            return __shfl_sync(FULL, r, 0);
+        };
+        int rowA = grab(), rowB = grab();
+        RowInfo infA = load_info(rowA, r1), infB = load_info(rowB, r1);
+        int kb = 0;
+        if (rowA < r1 && lane == 0) issue(0, rowA, infA);
+        while (rowA < r1) {
+            if (rowB < r1 && lane == 0) issue(kb ^ 1, rowB, infB);
+            const int rowC = grab();
+            const RowInfo infC = load_info(rowC, r1);
+            mbar_wait(&bars[warp * 2 + kb], (parity >> kb) & 1u);
+            parity ^= 1u << kb;
+            const int* hA = reinterpret_cast<const int*>(mybuf0 + kb * bufstride);
+            const uint16_t* opsA = reinterpret_cast<const uint16_t*>(mybuf0 + kb * bufstride + 64);
+            const int i = rowA;
+            if (infA.col0 <= j0) {                                  // the row's band reaches this column block
+                const long long wd = infA.word_off + ((j0 - infA.col0) >> 5);
+                const int j = j0 + lane;
+                const bool active = j < i;
+                int status = HC_ST_REJECT_COV;
+                int pid = TP_NOP;
+                const unsigned fa = (unsigned)hA[12], fb = (unsigned)hB[12 * 32];
+                const bool se1 = fa & HC_FLAG_SINGLE_END, se2 = fb & HC_FLAG_SINGLE_END;
+                if (active && !(hA[14] < hB[13 * 32] || hB[14 * 32] < hA[13])) {        // :1252
+                    if (tile_layout_reject(hA, hB, se1, se2)) status = HC_ST_REJECT_LAYOUT;
+                    else { status = HC_ST_WALKED; pid = pick_program(hA, hB, se1, se2); }
+                }
+                Lane L;
+                L.ref = 0; L.cc = 0; L.tc = 0; L.probM = 1.0; L.curs = 0ull; L.gap = false; L.undef = false;
+                int shape = 0;
+                const uint32_t* pg = progsm + pid * TP_WORDS;
+#pragma unroll 1
+                for (int s = 0; s < 3; ++s) {
+                    cheap(a, hA, hB, i, j, pg[s * 4 + 0], L, shape);
+                    cheap(a, hA, hB, i, j, pg[s * 4 + 1], L, shape);
+                    cheap(a, hA, hB, i, j, pg[s * 4 + 2], L, shape);
+                    __syncwarp();
+                    const uint32_t mo = pg[s * 4 + 3];
+                    if (__any_sync(FULL, (mo & 15u) != M_NOP)) overlap(a, hA, hB, opsA, opsB, Tb, mo, L, shape);
+                }
+                cheap(a, hA, hB, i, j, pg[SLOT_FINAL], L, shape);
+                __syncwarp();
+                // ---- similarityCriterion (:1107-1141)
+                double prob0 = 0.0, score = __longlong_as_double(0x7ff8000000000000ll), cutoff = 0.0;
+                bool edge = false, ambiguous = false;
+                if (status == HC_ST_WALKED) {
+                    if (!L.undef) {
+                        if (L.tc >= a.P.ladder_len) L.undef = true;
+                        else prob0 = __ldg(a.P.ladder + L.tc);
+                    }
+                    if (L.undef) status = HC_ST_UNDEFINED;
+                    else if (!L.gap && L.cc != 0) {
+                        const bool cl1 = fa & HC_FLAG_IS_CLIQUE, cl2 = fb & HC_FLAG_IS_CLIQUE;
+                        const int sel = (cl1 && cl2) ? 0 : ((cl1 || cl2) ? 1 : 2);
+                        cutoff = a.P.log_cutoff[sel];
+                        const double min_overlap = a.P.min_overlap[(cl1 && cl2) ? 0 : 1];
+                        const unsigned smaller = min(fa & 0x3fffffffu, fb & 0x3fffffffu);
+                        if (!((double)L.cc <= __dmul_rn(min_overlap, (double)smaller))) {
+                            double prob, potence;
+                            if (a.P.no_prob0) { prob = log10(L.probM); potence = __ddiv_rn(1.0, (double)L.cc); }
+                            else { prob = __dadd_rn(log10(L.probM), prob0); potence = __ddiv_rn(1.0, (double)(L.cc + L.tc)); }
+                            score = __dmul_rn(prob, potence);
+                            edge = score >= cutoff;
+                            ambiguous = fabs(score - cutoff) <= a.P.amb_tol * fabs(cutoff);
+                        }
+                    }
+                }
+                const unsigned bits = __ballot_sync(FULL, edge);
+                if (lane == 0) a.adj[wd] = bits;
+                if (a.detail != nullptr && active) {
+                    hc_pair_result r;
+                    r.status = status; r.edge = edge; r.gap = L.gap; r.cc = L.cc; r.tc = L.tc; r.ambiguous = ambiguous;
+                    r.probM = L.probM; r.prob0 = prob0; r.score = score;
+                    a.detail[wd * 32 + lane] = r;
+                }
+                if (ambiguous) {
+                    const unsigned long long slot = atomicAdd(&a.stats->ambiguous, 1ull);
+                    if (a.amb != nullptr && slot < (unsigned long long)a.amb_cap) {
+                        hc_ambiguous am;
+                        am.i = i; am.j = j; am.cc = L.cc; am.tc = L.tc; am.probM = L.probM; am.prob0 = prob0;
+                        am.score = score; am.cutoff = cutoff;
+                        a.amb[slot] = am;
+                    }
+                }
+                const bool walked = status == HC_ST_WALKED;
+                const unsigned n_total = __popc(__ballot_sync(FULL, active));
+                const unsigned n_scored = __popc(__ballot_sync(FULL, active && status != HC_ST_REJECT_COV));
+                const unsigned n_walked = __popc(__ballot_sync(FULL, walked));
+                const unsigned n_undef = __popc(__ballot_sync(FULL, status == HC_ST_UNDEFINED));
+                const unsigned s_cc = __reduce_add_sync(FULL, walked ? (unsigned)L.cc : 0u);
+                const unsigned s_tc = __reduce_add_sync(FULL, walked ? (unsigned)L.tc : 0u);
+                if (lane == 0) {
+                    atomicAdd(&cstat[0], (unsigned long long)n_total);
+                    atomicAdd(&cstat[1], (unsigned long long)n_scored);
+                    atomicAdd(&cstat[2], (unsigned long long)n_walked);
+                    atomicAdd(&cstat[3], (unsigned long long)__popc(bits));
+                    atomicAdd(&cstat[4], (unsigned long long)s_cc);
+                    atomicAdd(&cstat[5], (unsigned long long)s_tc);
+                    atomicAdd(&cstat[6], (unsigned long long)n_undef);
+                }
+            }
+            __syncwarp();
+            rowA = rowB; infA = infB; rowB = rowC; infB = infC; kb ^= 1;
+        }
+    }
+    __syncthreads();
+    if (tid < 7 && cstat[tid] != 0ull) {
+        unsigned long long* dst = &a.stats->pairs_total;
+        atomicAdd(dst + tid, cstat[tid]);
+    }
+}
+
+// ---- per-segment prefix counts for segments that are not "clips, plain M, clips" ---------------------------
+__global__ void build_aux_kernel(const hc_read_hdr* __restrict__ hdr, const uint16_t* __restrict__ ops, int n_reads,
+                                 uint32_t* __restrict__ aux, uint16_t* __restrict__ col2op) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= 2 * n_reads) return;
+    const int r = t >> 1, s = t & 1;
+    const hc_read_hdr h = hdr[r];
+    if (h.seg_flags[s] == 0 || h.n_ops[s] == 0) return;
+    const unsigned off = h.ops_off[s];
+    uint32_t* ax = aux + (size_t)off + 2u * (unsigned)r + s;
+    uint32_t mi = 0, ni = 0;
+    for (int c = 0; c < h.n_ops[s]; ++c) {
+        ax[c] = (ni << 16) | mi;
+        const int op = ops[off + c] >> HC_OP_SHIFT;
+        if (op == HC_OP_M || op == HC_OP_I) mi++;
+        if (op != HC_OP_I) { col2op[(size_t)off + ni] = (uint16_t)c; ni++; }
+    }
+    ax[h.n_ops[s]] = (ni << 16) | mi;
+}
+
+}  // namespace tile

@@ -19,6 +19,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libhcgpu.so")
 
 HC_OK = 0
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_TILED = 0, 1, 2
 ST_REJECT_COV, ST_REJECT_LAYOUT, ST_WALKED, ST_UNDEFINED = 0, 1, 2, 3
 
 
@@ -60,7 +61,7 @@ AMBIGUOUS_DTYPE = np.dtype([("i", np.int32), ("j", np.int32), ("cc", np.int32), 
                             ("cutoff", np.float64)], align=True)
 HDR_DTYPE = np.dtype([("raw", np.int32, 4), ("ext", np.int32, 4), ("ops_off", np.uint32, 2), ("n_ops", np.int32, 2),
                       ("ncov_flags", np.uint32), ("cov_first", np.int32), ("cov_last", np.int32),
-                      ("has_ins", np.uint16, 2)], align=True)
+                      ("seg_flags", np.uint16, 2)], align=True)
 
 _lib = None
 
@@ -88,6 +89,9 @@ def load_library():
         L.hc_score_band.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32,
                                     C.c_void_p]
         L.hc_score_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+        L.hc_score_band_detail.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+        L.hc_set_kernel.argtypes = [C.c_void_p, C.c_int32]
+        L.hc_last_kernel.argtypes = [C.c_void_p]
         L.hc_get_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         assert C.sizeof(_BandStats) == 72 and HDR_DTYPE.itemsize == 64
         _lib = L
@@ -151,8 +155,16 @@ class PackedBatch:
         return np.frombuffer(buf, dtype=HDR_DTYPE).copy()
 
     def ops(self) -> np.ndarray:
+        """The op records of all reads back to back (the per-read alignment padding removed)."""
+        if self.c.n_ops_total == 0:
+            return np.zeros(0, np.uint16)
         buf = (C.c_uint16 * self.c.n_ops_total).from_address(self.c.ops)
-        return np.frombuffer(buf, dtype=np.uint16).copy()
+        raw = np.frombuffer(buf, dtype=np.uint16)
+        h = self.headers()
+        off = h["ops_off"][:, 0].astype(np.int64)
+        cnt = h["n_ops"].sum(axis=1).astype(np.int64)
+        idx = np.repeat(off - (np.cumsum(cnt) - cnt), cnt) + np.arange(int(cnt.sum()), dtype=np.int64)
+        return raw[idx].copy()
 
     def __del__(self):
         try:
@@ -326,6 +338,35 @@ class NewEdgeCalculator(EdgeCalculator):
         stats = {k: getattr(st, k) for k, _ in _BandStats._fields_}
         words = out[:nw] if fetch else np.zeros(0, np.uint32)
         return Adjacency(row_begin, row_end, col0, off, words, stats, amb[:min(int(st.ambiguous), amb_cap)].copy())
+
+    def set_kernel(self, mode: int) -> None:
+        """KERNEL_AUTO / KERNEL_GENERIC / KERNEL_TILED (include/hc_edge.h: hc_set_kernel)."""
+        self._check(self.L.hc_set_kernel(self._ctx, mode), "hc_set_kernel")
+
+    def last_kernel(self) -> int:
+        return int(self.L.hc_last_kernel(self._ctx))
+
+    def score_band_detail(self, row_begin: int = 0, row_end: Optional[int] = None):
+        """Tiled kernel with per-slot detail: returns (Adjacency, pi, pj, detail) where detail[k] holds the
+        values of the ordered pair (pi[k], pj[k]) -- every band slot with j < i, row-major."""
+        row_end = self._packed.n_reads if row_end is None else row_end
+        col0, off, nw = self.band_layout(row_begin, row_end)
+        words = np.zeros(max(nw, 1), np.uint32)
+        det = np.zeros(max(nw, 1) * 32, PAIR_RESULT_DTYPE)
+        st = _BandStats()
+        self._check(self.L.hc_score_band_detail(self._ctx, row_begin, row_end, _ptr(words), _ptr(det), nw, C.byref(st)),
+                    "hc_score_band_detail")
+        stats = {k: getattr(st, k) for k, _ in _BandStats._fields_}
+        adj = Adjacency(row_begin, row_end, col0, off, words[:nw], stats, np.zeros(0, AMBIGUOUS_DTYPE))
+        nrows = row_end - row_begin
+        wcount = np.diff(off).astype(np.int64)
+        row_of_word = np.repeat(np.arange(nrows, dtype=np.int64), wcount)
+        slot = np.arange(nw * 32, dtype=np.int64)
+        w = slot >> 5
+        i = row_begin + row_of_word[w]
+        j = col0[row_of_word[w]].astype(np.int64) + (w - off[row_of_word[w]]) * 32 + (slot & 31)
+        keep = j < i
+        return adj, i[keep].astype(np.int32), j[keep].astype(np.int32), det[:nw * 32][keep]
 
     def scoreBatch(self, reads) -> Adjacency:
         """One call per clique-finder iteration: pack, upload, score the whole band, fetch the adjacency."""

@@ -78,23 +78,29 @@ typedef struct {
 typedef struct {
     int32_t raw[4];
     int32_t ext[4];
-    uint32_t ops_off[2];                /* first op record of each segment in hc_packed.ops */
+    uint32_t ops_off[2];                /* first op record of each segment in hc_packed.ops; a read's two segments are
+                                           contiguous and ops_off[0] is a multiple of 8 (16-byte aligned stream) */
     int32_t n_ops[2];                   /* unrolled CIGAR length per segment */
     uint32_t ncov_flags;                /* bits 0..29 ncov, bit 30 single_end, bit 31 is_clique */
     int32_t cov_first;
     int32_t cov_last;
-    uint16_t has_ins[2];                /* segment holds at least one I op */
+    uint16_t seg_flags[2];              /* HC_SEG_* per segment */
 } hc_read_hdr;
+
+#define HC_SEG_HAS_INS 1u               /* segment holds at least one I op */
+#define HC_SEG_NOT_PLAIN 2u             /* some op between the leading and trailing clip runs is not M */
 
 #define HC_FLAG_SINGLE_END 0x40000000u
 #define HC_FLAG_IS_CLIQUE 0x80000000u
 
 /* One 16-bit record per unrolled CIGAR op:
- *   bits 0..6  quality code (dense re-numbering of the quality chars present, see qual_chars[])
- *   bits 7..9  base code    A=0 C=1 G=2 T=3 N=4   (0 for D/H ops, which carry no base)
+ *   bits 0..2  base code    A=0 C=1 G=2 T=3 N=4   (0 for D/H ops, which carry no base)
+ *   bits 3..9  quality code (dense re-numbering of the quality chars present, see qual_chars[]);
+ *              record & 0x3F8 is the byte offset of the code's column in a row of doubles
  *   bits 10..12 op          M=0 I=1 D=2 S=3 H=4 */
 #define HC_OP_SHIFT 10
-#define HC_BASE_SHIFT 7
+#define HC_BASE_SHIFT 0
+#define HC_QUAL_SHIFT 3
 enum { HC_OP_M = 0, HC_OP_I = 1, HC_OP_D = 2, HC_OP_S = 3, HC_OP_H = 4 };
 
 typedef struct {
@@ -102,8 +108,8 @@ typedef struct {
     int32_t n_qual_codes;               /* K <= 94 */
     uint8_t qual_chars[128];            /* code -> quality char */
     const hc_read_hdr* hdr;             /* [n_reads] */
-    const uint16_t* ops;                /* [n_ops_total (+ padding)] */
-    int64_t n_ops_total;
+    const uint16_t* ops;                /* [n_ops_total (+ 64 records of padding)] */
+    int64_t n_ops_total;                /* records in ops[], including the per-read alignment padding */
     int32_t max_ops_per_read;           /* max over reads of n_ops[0]+n_ops[1] */
     int32_t reserved;
     void* owner;                        /* library-private */
@@ -171,6 +177,20 @@ int hc_band_layout(hc_ctx* ctx, int32_t row_begin, int32_t row_end, int32_t* col
  * amb/amb_cap: optional list of pairs whose score is within the tolerance of the threshold. */
 int hc_score_band(hc_ctx* ctx, int32_t row_begin, int32_t row_end, uint32_t* adj, int64_t n_words,
                   hc_ambiguous* amb, int32_t amb_cap, hc_band_stats* stats);
+
+/* Same pass, but additionally returns the per-pair values (status, gap, cc, tc, probM, prob0, score) of every
+ * band slot: detail[w*32 + b] belongs to bit b of adjacency word w (slots with j >= i stay zeroed). Only the
+ * tiled kernel produces this (parity testing of that kernel); HC_E_STATE otherwise. n_words as in hc_score_band. */
+int hc_score_band_detail(hc_ctx* ctx, int32_t row_begin, int32_t row_end, uint32_t* adj, hc_pair_result* detail,
+                         int64_t n_words, hc_band_stats* stats);
+
+/* Which band kernel hc_score_band uses. AUTO: the tiled kernel (shared-memory column tiles, TMA-fed rows) when
+ * the batch is eligible -- no allele-frequency map and the longest read fits a tile -- else the generic
+ * one-lane-per-pair walker. GENERIC / TILED force one; TILED fails with HC_E_STATE when not eligible.
+ * Both produce identical results. hc_last_kernel: the kernel the last hc_score_band call launched (0 = none). */
+enum { HC_KERNEL_AUTO = 0, HC_KERNEL_GENERIC = 1, HC_KERNEL_TILED = 2 };
+int hc_set_kernel(hc_ctx* ctx, int32_t mode);
+int hc_last_kernel(const hc_ctx* ctx);
 
 /* Scores an explicit list of ordered pairs (ap1 = pi[k], ap2 = pj[k]), full detail per pair. */
 int hc_score_pairs(hc_ctx* ctx, const int32_t* pi, const int32_t* pj, int64_t npairs, hc_pair_result* out);

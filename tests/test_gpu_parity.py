@@ -137,3 +137,81 @@ def test_setOverlapCliques_changes_the_decision():
     orc_kw = dict(kw, overlap=0.99)
     edges, _ = pyoracle.Oracle(b, **orc_kw).all_pairs(detail=False)
     assert e1 == edges and e1 <= e0
+
+
+# ---- the tiled band kernel (shared-memory column tiles, TMA-fed rows): every band slot against the oracle ----
+def _tiled_detail_vs_oracle(b, kw, label):
+    calc = edge.NewEdgeCalculator(**kw)
+    calc.upload(b)
+    calc.set_kernel(edge.KERNEL_TILED)
+    adj, pi, pj, det = calc.score_band_detail()
+    assert calc.last_kernel() == edge.KERNEL_TILED or b.n < 2
+    O = pyoracle.Oracle(b, **kw)
+    orc = O.pairs(pi, pj)
+    common.assert_pairs_equal(det, orc, label)
+    # the adjacency words say the same as the per-slot detail, and nothing outside the band is an edge
+    edges, e = O.all_pairs(detail=False)
+    ai, aj = adj.edges()
+    ti, tj = common.tri_pairs(b.n)
+    differing = int(((det["edge"] != orc["edge"]) & (orc["status"] != 3)).sum())
+    if differing == 0:
+        assert adj.count() == edges
+        assert (ai == ti[e == 1]).all() and (aj == tj[e == 1]).all()
+    assert adj.stats["pairs_total"] == pi.shape[0]
+    assert adj.stats["pairs_walked"] == int((orc["status"] == 2).sum())
+    assert adj.stats["sum_cc"] == int(orc["cc"][orc["status"] == 2].sum())
+    assert adj.stats["sum_tc"] == int(orc["tc"][orc["status"] == 2].sum())
+    # same answer from the generic kernel
+    calc.set_kernel(edge.KERNEL_GENERIC)
+    adj2 = calc.score_band()
+    assert calc.last_kernel() == edge.KERNEL_GENERIC or b.n < 2
+    assert (adj2.words == adj.words).all()
+    return det, orc
+
+
+@pytest.mark.parametrize("label", sorted(common.DATASETS))
+def test_tiled_kernel_matches_oracle_on_golden_sets(golden, label):
+    g = golden[label]
+    b = common.load_batch(common.DATASETS[label])
+    kw = common.calc_kwargs(g["params"], g["max_position"])
+    calc = edge.NewEdgeCalculator(**kw)
+    calc.upload(b)
+    adj = calc.score_band()
+    if calc.last_kernel() != edge.KERNEL_TILED:
+        pytest.skip("batch not eligible for the tiled kernel (longest read does not fit a shared-memory tile)")
+    _tiled_detail_vs_oracle(b, kw, label)
+    assert adj.count() == g["edges"]
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_tiled_kernel_zoo(seed):
+    b = synth.zoo(200, seed=100 + seed)
+    kw = dict(noProb0=bool(seed % 2), edge_quasi_cutoff_single=0.8, edge_quasi_cutoff_mixed=0.85,
+              edge_quasi_cutoff=0.9, overlap=0.3, overlap_single=0.2, maxPosition=b.max_position())
+    det, orc = _tiled_detail_vs_oracle(b, kw, "tiled-zoo%d" % seed)
+    assert set(np.unique(orc["layout"])) >= {100, 200, 300, 400}
+
+
+def test_tiled_kernel_quasispecies_with_indels_and_clips():
+    b = synth.quasispecies(1500, genome_len=2500, seed=21, indel_err=3e-3, clip_frac=0.15)
+    kw = dict(noProb0=True, maxPosition=b.max_position(), edge_quasi_cutoff_single=0.9)
+    det, orc = _tiled_detail_vs_oracle(b, kw, "tiled-quasi")
+    assert int(orc["edge"].sum()) > 1000 and int(orc["gap"].sum()) > 100
+    kw["noProb0"] = False
+    _tiled_detail_vs_oracle(b, kw, "tiled-quasi-prob0")
+
+
+def test_tiled_kernel_row_windows_concatenate():
+    # sharding by row windows (what N>1 ranks do): the windows' words are the full run's words
+    b = synth.quasispecies(900, genome_len=2000, seed=5)
+    kw = dict(noProb0=True, maxPosition=b.max_position())
+    calc = edge.NewEdgeCalculator(**kw)
+    calc.upload(b)
+    calc.set_kernel(edge.KERNEL_TILED)
+    full = calc.score_band()
+    parts = [calc.score_band(r0, r1) for r0, r1 in ((0, 301), (301, 650), (650, 900))]
+    assert sum(p.count() for p in parts) == full.count()
+    fi, fj = full.edges()
+    pi_ = np.concatenate([p.edges()[0] for p in parts])
+    pj_ = np.concatenate([p.edges()[1] for p in parts])
+    assert (fi == pi_).all() and (fj == pj_).all()

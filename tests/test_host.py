@@ -46,7 +46,7 @@ def _python_pack(b: ReadBatch, qual_chars: bytes):
             for c in cig:
                 rec = opc[int(c)] << 10
                 if int(c) in (ord("M"), ord("I"), ord("S")):
-                    rec |= (bc.get(int(seq[qi]), 4) << 7) | code[int(ql[qi])]
+                    rec |= bc.get(int(seq[qi]), 4) | (code[int(ql[qi])] << 3)
                     qi += 1
                 out.append(rec)
     return np.array(out, np.uint16)
@@ -56,7 +56,7 @@ def _python_pack(b: ReadBatch, qual_chars: bytes):
 def test_pack_matches_python_restatement(fixture):
     b = common.load_batch(fixture)
     pk = edge.pack_only(b)
-    assert pk.n_reads == b.n and pk.n_ops_total == int(b.cig_len.sum())
+    assert pk.n_reads == b.n and pk.n_ops_total >= int(b.cig_len.sum())
     qc = bytes(pk.c.qual_chars[:pk.c.n_qual_codes])
     assert qc == bytes(sorted(set(b.qual.tolist())))
     assert (pk.ops() == _python_pack(b, qc)).all()
@@ -70,7 +70,10 @@ def test_pack_matches_python_restatement(fixture):
         lead = len(cig) - len(cig.lstrip(b"SH"))
         trail = len(cig) - len(cig.rstrip(b"SH"))
         assert h["ext"][r, 0] == b.seg_start[2 * r] - lead and h["ext"][r, 1] == b.seg_end[2 * r] + trail
-        assert h["has_ins"][r, 0] == (1 if b"I" in cig else 0)
+        assert (h["seg_flags"][r, 0] & 1) == (1 if b"I" in cig else 0)
+        core = cig[lead:len(cig) - trail]
+        assert ((h["seg_flags"][r, 0] >> 1) & 1) == (0 if core == b"M" * len(core) else 1)
+        assert h["ops_off"][r, 0] % 8 == 0 and h["ops_off"][r, 1] == h["ops_off"][r, 0] + h["n_ops"][r, 0]
 
 
 def test_pack_rejects_malformed_reads():
