@@ -152,7 +152,7 @@ __device__ __forceinline__ bool consumes_query(int op) { return op == HC_OP_M ||
 __device__ __forceinline__ void tail_loop(const DevParams& P, WalkState& w, const Seg s, int& c, int limit) {
     while (w.ref < limit) {
         if (c >= s.n) { w.undefined = true; return; }
-        const int op = s.ops[c] >> HC_OP_SHIFT;
+        const int op = (int)HC_REC_OP((unsigned)s.ops[c]);
         if (op == HC_OP_M || op == HC_OP_I) {
             w.tc++;
             if (P.simpson != nullptr) {                                        // computeProb0 (:133-143)
@@ -177,31 +177,31 @@ __device__ __forceinline__ bool ovl_loop(const DevParams& P, WalkState& w, const
                                          int hi) {
     int cq = 0;   // QX only: op index in A of the base the reference's stray query cursor points at
     if (QX) {
-        while (cq < A.n && !consumes_query(A.ops[cq] >> HC_OP_SHIFT)) cq++;
+        while (cq < A.n && !consumes_query((int)HC_REC_OP((unsigned)A.ops[cq]))) cq++;
     }
     while (w.ref <= hi) {
         if (ca >= A.n || cb >= B.n) { w.undefined = true; return false; }
         const unsigned ra = A.ops[ca], rb = B.ops[cb];
-        const int oa = ra >> HC_OP_SHIFT, ob = rb >> HC_OP_SHIFT;
-        const int act = ((ra | rb) >> HC_OP_SHIFT) == 0 ? ACT_SCORE : op_action(oa, ob);
+        const int oa = (int)HC_REC_OP(ra), ob = (int)HC_REC_OP(rb);
+        const int act = (oa | ob) == 0 ? ACT_SCORE : op_action(oa, ob);
         if (act == ACT_SCORE) {
             unsigned sa = ra;
             if (QX) {
                 if (cq >= A.n) { w.undefined = true; return false; }
                 sa = A.ops[cq];
             }
-            const int idx = (int)((sa >> HC_QUAL_SHIFT) & 127u) * P.K + (int)((rb >> HC_QUAL_SHIFT) & 127u) + ((((sa ^ rb) >> HC_BASE_SHIFT) & 7u) ? P.KK : 0);
+            const int idx = (int)HC_REC_QUAL(sa) * P.K + (int)HC_REC_QUAL(rb) + (HC_REC_BASE(sa ^ rb) ? P.KK : 0);
             w.probM = __dmul_rn(w.probM, __ldg(P.table + idx));                // computeProbM (:122-131)
             w.cc++;
             if (oa == HC_OP_M) w.ref++;
             ca++; cb++;
-            if (QX) { cq++; while (cq < A.n && !consumes_query(A.ops[cq] >> HC_OP_SHIFT)) cq++; }
+            if (QX) { cq++; while (cq < A.n && !consumes_query((int)HC_REC_OP((unsigned)A.ops[cq]))) cq++; }
         } else if (act == ACT_SKIP) {
             w.ref++; ca++; cb++;
-            if (QX && consumes_query(oa)) { cq++; while (cq < A.n && !consumes_query(A.ops[cq] >> HC_OP_SHIFT)) cq++; }
+            if (QX && consumes_query(oa)) { cq++; while (cq < A.n && !consumes_query((int)HC_REC_OP((unsigned)A.ops[cq]))) cq++; }
         } else if (act == ACT_ADV_A) {
             ca++;
-            if (QX) { cq++; while (cq < A.n && !consumes_query(A.ops[cq] >> HC_OP_SHIFT)) cq++; }
+            if (QX) { cq++; while (cq < A.n && !consumes_query((int)HC_REC_OP((unsigned)A.ops[cq]))) cq++; }
         } else if (act == ACT_ADV_B) {
             cb++;
         } else {

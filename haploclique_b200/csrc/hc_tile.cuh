@@ -200,38 +200,57 @@ __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int*
     const int aoff = sa ? hA[10] : 0, boff = sb ? hB[10 * 32] : 0;
     int ca = get_cur(L, 0, sa), cb = get_cur(L, 1, sb);
     int cq = 0;
-    if (more && qx) { while (cq < nA && !consumes_q(opsA[aoff + cq] >> HC_OP_SHIFT)) cq++; }
-    const uint32_t K = (uint32_t)a.P.K, KK8 = (uint32_t)a.P.KK * 8u;
+    if (more && qx) { while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
+    const uint32_t K8 = (uint32_t)a.P.K * 8u;
+    const uint32_t teq = smem_u32(Tb), tun = teq + (uint32_t)a.P.KK * 8u;   // shared-space addresses of the two tables
     const uint32_t* opsA32 = reinterpret_cast<const uint32_t*>(opsA);
     int ref = L.ref, cc = L.cc;
     double probM = L.probM;
+    // probM *= T[neq][qa][qb]; the address is formed on the FMA pipe (two IMADs), the select is the only ALU op
+#define TILE_MUL(QA, QB, NEQ)                                                             \
+    do {                                                                                  \
+        const uint32_t ad__ = (QB) * 8u + ((QA) * K8 + ((NEQ) ? tun : teq));              \
+        double t__;                                                                       \
+        asm("ld.shared.f64 %0, [%1];" : "=d"(t__) : "r"(ad__));                           \
+        probM = __dmul_rn(probM, t__);                                                    \
+    } while (0)
+#define TILE_MUL2(AW, BW)                                                                 \
+    do {                                                                                  \
+        const uint32_t x__ = (AW) ^ (BW);                                                 \
+        TILE_MUL(__byte_perm((AW), 0, 0x4441), __byte_perm((BW), 0, 0x4441), (x__ & 0x7u) != 0u);       \
+        TILE_MUL((AW) >> 24, (BW) >> 24, (x__ & 0x70000u) != 0u);                         \
+    } while (0)
     for (;;) {
-        // -- two columns per iteration while both reads show M
+        // -- four (then two) columns per iteration while both reads show M
         if (more && !qx) {
             const int run = min(min(hi - ref + 1, nA - ca), nB - cb);
             if (run >= 2) {
                 const int ia = aoff + ca, ib = boff + cb;
                 const uint32_t* pa = opsA32 + (ia >> 1);
                 const uint32_t* pb = opsB + (ib >> 1) * 32;
-                const int sha = (ia & 1) * 16, shb = (ib & 1) * 16;
-                uint32_t a0 = pa[0], a1 = pa[1], b0 = pb[0], b1 = pb[32];
+                int sha = (ia & 1) * 16, shb = (ib & 1) * 16;
+                asm volatile("" : "+r"(sha), "+r"(shb));          // keep the two shift amounts in registers
+                uint32_t a0 = pa[0], a1 = pa[1], a2 = pa[2];
+                uint32_t b0 = pb[0], b1 = pb[32], b2 = pb[64];
                 int done = 0;
-                do {
-                    const uint32_t a2 = __funnelshift_r(a0, a1, sha), b2 = __funnelshift_r(b0, b1, shb);
-                    a0 = a1; b0 = b1; pa += 1; pb += 32;
-                    a1 = pa[1]; b1 = pb[32];
-                    if ((a2 | b2) & 0x1C001C00u) break;
-                    const uint32_t x = a2 ^ b2;
-                    uint32_t o0 = (a2 & 0x3F8u) * K + (b2 & 0x3F8u);
-                    uint32_t o1 = ((a2 >> 16) & 0x3F8u) * K + ((b2 >> 16) & 0x3F8u);
-                    if (x & 0x00000007u) o0 += KK8;
-                    if (x & 0x00070000u) o1 += KK8;
-                    const double t0 = *reinterpret_cast<const double*>(Tb + o0);
-                    const double t1 = *reinterpret_cast<const double*>(Tb + o1);
-                    probM = __dmul_rn(probM, t0);
-                    probM = __dmul_rn(probM, t1);
-                    done += 2;
-                } while (done + 2 <= run);
+                while (done + 4 <= run) {
+                    const uint32_t A01 = __funnelshift_r(a0, a1, sha), A23 = __funnelshift_r(a1, a2, sha);
+                    const uint32_t B01 = __funnelshift_r(b0, b1, shb), B23 = __funnelshift_r(b1, b2, shb);
+                    if ((A01 | B01 | A23 | B23) & 0x00380038u) break;
+                    pa += 2; pb += 64;
+                    a0 = a2; b0 = b2;
+                    a1 = pa[1]; a2 = pa[2]; b1 = pb[32]; b2 = pb[64];
+                    TILE_MUL2(A01, B01);
+                    TILE_MUL2(A23, B23);
+                    done += 4;
+                }
+                if (done + 2 <= run) {
+                    const uint32_t A01 = __funnelshift_r(a0, a1, sha), B01 = __funnelshift_r(b0, b1, shb);
+                    if (!((A01 | B01) & 0x00380038u)) {
+                        TILE_MUL2(A01, B01);
+                        done += 2;
+                    }
+                }
                 ca += done; cb += done; ref += done; cc += done;
             }
         }
@@ -244,7 +263,7 @@ __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int*
                 const uint32_t ra = opsA[aoff + ca];
                 const uint32_t wb = opsB[((boff + cb) >> 1) * 32];
                 const uint32_t rb = ((boff + cb) & 1) ? (wb >> 16) : (wb & 0xffffu);
-                const int oa = (int)(ra >> HC_OP_SHIFT), ob = (int)(rb >> HC_OP_SHIFT);
+                const int oa = (int)HC_REC_OP(ra), ob = (int)HC_REC_OP(rb);
                 const int act = (oa | ob) == 0 ? ACT_SCORE : op_action(oa, ob);
                 if (act == ACT_SCORE) {
                     uint32_t sq = ra;
@@ -254,20 +273,18 @@ __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int*
                         else sq = opsA[aoff + cq];
                     }
                     if (ok) {
-                        uint32_t o = (sq & 0x3F8u) * K + (rb & 0x3F8u);
-                        if ((sq ^ rb) & 7u) o += KK8;
-                        probM = __dmul_rn(probM, *reinterpret_cast<const double*>(Tb + o));
+                        TILE_MUL(HC_REC_QUAL(sq), HC_REC_QUAL(rb), HC_REC_BASE(sq ^ rb) != 0u);
                         cc++;
                         if (oa == HC_OP_M) ref++;
                         ca++; cb++;
-                        if (qx) { cq++; while (cq < nA && !consumes_q(opsA[aoff + cq] >> HC_OP_SHIFT)) cq++; }
+                        if (qx) { cq++; while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
                     }
                 } else if (act == ACT_SKIP) {
                     ref++; ca++; cb++;
-                    if (qx && consumes_q(oa)) { cq++; while (cq < nA && !consumes_q(opsA[aoff + cq] >> HC_OP_SHIFT)) cq++; }
+                    if (qx && consumes_q(oa)) { cq++; while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
                 } else if (act == ACT_ADV_A) {
                     ca++;
-                    if (qx) { cq++; while (cq < nA && !consumes_q(opsA[aoff + cq] >> HC_OP_SHIFT)) cq++; }
+                    if (qx) { cq++; while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
                 } else if (act == ACT_ADV_B) {
                     cb++;
                 } else {
@@ -277,6 +294,8 @@ __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int*
         }
         if (!__any_sync(FULL, more)) break;
     }
+#undef TILE_MUL2
+#undef TILE_MUL
     L.ref = ref; L.cc = cc; L.probM = probM;
     if (op == M_OVL || op == M_OVL2 || op == M_OVLQX || op == M_SOVL) { set_cur(L, 0, sa, ca); set_cur(L, 1, sb, cb); }
 }
@@ -540,7 +559,7 @@ __global__ void build_aux_kernel(const hc_read_hdr* __restrict__ hdr, const uint
     uint32_t mi = 0, ni = 0;
     for (int c = 0; c < h.n_ops[s]; ++c) {
         ax[c] = (ni << 16) | mi;
-        const int op = ops[off + c] >> HC_OP_SHIFT;
+        const int op = (int)HC_REC_OP((unsigned)ops[off + c]);
         if (op == HC_OP_M || op == HC_OP_I) mi++;
         if (op != HC_OP_I) { col2op[(size_t)off + ni] = (uint16_t)c; ni++; }
     }

@@ -95,12 +95,15 @@ typedef struct {
 
 /* One 16-bit record per unrolled CIGAR op:
  *   bits 0..2  base code    A=0 C=1 G=2 T=3 N=4   (0 for D/H ops, which carry no base)
- *   bits 3..9  quality code (dense re-numbering of the quality chars present, see qual_chars[]);
- *              record & 0x3F8 is the byte offset of the code's column in a row of doubles
- *   bits 10..12 op          M=0 I=1 D=2 S=3 H=4 */
-#define HC_OP_SHIFT 10
+ *   bits 3..5  op           M=0 I=1 D=2 S=3 H=4
+ *   bits 8..14 quality code (dense re-numbering of the quality chars present, see qual_chars[]): the high
+ *              byte, so a byte extract yields the table index without masking */
+#define HC_OP_SHIFT 3
 #define HC_BASE_SHIFT 0
-#define HC_QUAL_SHIFT 3
+#define HC_QUAL_SHIFT 8
+#define HC_REC_OP(r) (((r) >> HC_OP_SHIFT) & 7u)
+#define HC_REC_BASE(r) ((r) & 7u)
+#define HC_REC_QUAL(r) (((r) >> HC_QUAL_SHIFT) & 127u)
 enum { HC_OP_M = 0, HC_OP_I = 1, HC_OP_D = 2, HC_OP_S = 3, HC_OP_H = 4 };
 
 typedef struct {

@@ -44,9 +44,9 @@ def _python_pack(b: ReadBatch, qual_chars: bytes):
             ql = b.qual[b.seq_off[k]:b.seq_off[k] + b.seq_len[k]]
             qi = 0
             for c in cig:
-                rec = opc[int(c)] << 10
+                rec = opc[int(c)] << 3
                 if int(c) in (ord("M"), ord("I"), ord("S")):
-                    rec |= bc.get(int(seq[qi]), 4) | (code[int(ql[qi])] << 3)
+                    rec |= bc.get(int(seq[qi]), 4) | (code[int(ql[qi])] << 8)
                     qi += 1
                 out.append(rec)
     return np.array(out, np.uint16)
