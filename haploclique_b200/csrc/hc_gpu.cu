@@ -494,7 +494,9 @@ struct hc_ctx {
     int kernel_mode = HC_KERNEL_AUTO;
     int last_kernel = 0;
     size_t smem_optin = 0;
-    std::vector<int4> items; int items_begin = -1, items_end = -1;
+    std::vector<int4> items; std::vector<int32_t> colidx; int items_begin = -1, items_end = -1;
+    int32_t* d_colidx = nullptr; size_t colidx_cap = 0;
+    std::vector<int32_t> cov_last, cov_first_smin; std::vector<uint8_t> is_single;
     std::string err;
 };
 
@@ -627,30 +629,63 @@ bool tile_eligible(const hc_ctx* c) {
     return tile_geometry(c).smem <= c->smem_optin;
 }
 
-// Work items of the tiled kernel for rows [row_begin,row_end): (column block, chunk of rows whose band reaches it).
+// Work items of the tiled kernel for rows [row_begin,row_end).
+// Columns (the earlier reads j) are taken in windows of W consecutive reads; inside a window they are sorted by
+// (single/paired, last covered position) and cut into blocks of 32. For a later row read i the length of the
+// lock-step loop against j depends on min(end_i, end_j) but not on j's start (j starts first), so the 32 lanes of
+// a block run loops of nearly the same length; and a block stops being scheduled at the first row that starts
+// behind the block's furthest end, so lanes are not spent on the reference's first reject (:1252).
+// An item = (block, chunk of rows that can reach it).
 void build_items(hc_ctx* c, int row_begin, int row_end, int n_ctas) {
     if (c->items_begin == row_begin && c->items_end == row_end) return;
     c->items.clear();
+    c->colidx.clear();
     const int nrows = row_end - row_begin;
-    if (nrows > 0) {
-        std::vector<int32_t> smin(nrows);                   // suffix minimum of col0: monotone, so "rows that reach block jb" is a prefix
-        int32_t run = INT32_MAX;
-        for (int k = nrows - 1; k >= 0; --k) { run = std::min(run, c->lay_col0[k]); smin[k] = run; }
-        const int jb_lo = smin[0] / 32, jb_hi = (row_end - 2) / 32;
-        std::vector<int> first, last;
+    if (nrows > 0 && row_end >= 2) {
+        int32_t jlo = INT32_MAX;
+        long long band = 0;
+        for (int k = 0; k < nrows; ++k) { jlo = std::min(jlo, c->lay_col0[k]); band += (row_begin + k) - c->lay_col0[k]; }
+        const int jhi = row_end - 1;                                   // columns [jlo, jhi)
+        int W = (int)(band / nrows / 16);
+        W = std::max(32, std::min(1024, (W + 16) / 32 * 32));
+        std::vector<int32_t> order;
+        struct Blk { int first_j; int maxend; };
+        std::vector<Blk> blks;
+        for (int w0 = jlo; w0 < jhi; w0 += W) {
+            const int w1 = std::min(w0 + W, jhi);
+            order.resize(w1 - w0);
+            for (int j = w0; j < w1; ++j) order[j - w0] = j;
+            std::sort(order.begin(), order.end(), [&](int x, int y) {
+                const int tx = c->is_single[x] ? 0 : 1, ty = c->is_single[y] ? 0 : 1;
+                if (tx != ty) return tx < ty;
+                if (c->cov_last[x] != c->cov_last[y]) return c->cov_last[x] < c->cov_last[y];
+                return x < y;
+            });
+            for (size_t p = 0; p < order.size(); p += 32) {
+                Blk b{INT32_MAX, INT32_MIN};
+                for (size_t q = p; q < p + 32; ++q) {
+                    const int j = q < order.size() ? order[q] : -1;
+                    c->colidx.push_back(j);
+                    if (j >= 0) { b.first_j = std::min(b.first_j, j); b.maxend = std::max(b.maxend, c->cov_last[j]); }
+                }
+                blks.push_back(b);
+            }
+        }
+        // rows that can reach a block: i > first_j and cov_first[i] <= maxend; cov_first_smin is the suffix minimum of
+        // cov_first (monotone), so the admissible rows are a prefix
+        std::vector<int> first(blks.size()), last(blks.size());
         long long total = 0;
-        for (int jb = jb_lo; jb <= jb_hi; ++jb) {
-            const int f = std::max(row_begin, jb * 32 + 1);
-            const int l = row_begin + (int)(std::upper_bound(smin.begin(), smin.end(), jb * 32) - smin.begin()) - 1;
-            first.push_back(f); last.push_back(l);
-            if (l >= f) total += l - f + 1;
+        for (size_t b = 0; b < blks.size(); ++b) {
+            first[b] = std::max(row_begin, blks[b].first_j + 1);
+            last[b] = std::min(row_end, (int)(std::upper_bound(c->cov_first_smin.begin(), c->cov_first_smin.end(), blks[b].maxend) -
+                                              c->cov_first_smin.begin())) - 1;
+            if (last[b] >= first[b]) total += last[b] - first[b] + 1;
         }
         long long chunk = (total + (long long)n_ctas * 16 - 1) / ((long long)n_ctas * 16);
         chunk = std::max<long long>(32, std::min<long long>(chunk, 4096));
-        for (int jb = jb_lo; jb <= jb_hi; ++jb) {
-            const int f = first[jb - jb_lo], l = last[jb - jb_lo];
-            for (long long r = f; r <= l; r += chunk) c->items.push_back(make_int4(jb, (int)r, (int)std::min<long long>(r + chunk, (long long)l + 1), 0));
-        }
+        for (size_t b = 0; b < blks.size(); ++b)
+            for (long long r = first[b]; r <= last[b]; r += chunk)
+                c->items.push_back(make_int4((int)b, (int)r, (int)std::min<long long>(r + chunk, (long long)last[b] + 1), 0));
     }
     c->items_begin = row_begin;
     c->items_end = row_end;
@@ -727,7 +762,7 @@ void hc_destroy(hc_ctx* c) {
     cudaFree(c->d_col0); cudaFree(c->d_word_off); cudaFree(c->d_adj); cudaFree(c->d_stats); cudaFree(c->d_amb);
     cudaFree(c->d_pi); cudaFree(c->d_pj); cudaFree(c->d_res); cudaFree(c->d_flush);
     cudaFree(c->d_aux); cudaFree(c->d_col2op); cudaFree(c->d_tprog); cudaFree(c->d_items); cudaFree(c->d_item_counter);
-    cudaFree(c->d_detail);
+    cudaFree(c->d_detail); cudaFree(c->d_colidx);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -809,12 +844,19 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     }
     c->cov_first.resize(p->n_reads);
     c->cov_last_pmax.resize(p->n_reads);
+    c->cov_last.resize(p->n_reads);
+    c->is_single.resize(p->n_reads);
+    c->cov_first_smin.resize(p->n_reads);
     int run = INT32_MIN;
     for (int r = 0; r < p->n_reads; ++r) {
         c->cov_first[r] = p->hdr[r].cov_first;
+        c->cov_last[r] = p->hdr[r].cov_last;
+        c->is_single[r] = (p->hdr[r].ncov_flags & HC_FLAG_SINGLE_END) ? 1 : 0;
         run = std::max(run, p->hdr[r].cov_last);
         c->cov_last_pmax[r] = run;
     }
+    int smin = INT32_MAX;
+    for (int r = p->n_reads - 1; r >= 0; --r) { smin = std::min(smin, c->cov_first[r]); c->cov_first_smin[r] = smin; }
     CU_TRY(c, cudaStreamSynchronize(c->stream));
     return HC_OK;
 }
@@ -876,6 +918,8 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
         const size_t n_items = c->items.size();
         if ((rc = grow(c, c->d_items, c->items_cap, std::max<size_t>(n_items, 1))) != HC_OK) return rc;
         CU_TRY(c, cudaMemcpyAsync(c->d_items, c->items.data(), sizeof(int4) * n_items, cudaMemcpyHostToDevice, c->stream));
+        if ((rc = grow(c, c->d_colidx, c->colidx_cap, std::max<size_t>(c->colidx.size(), 32))) != HC_OK) return rc;
+        CU_TRY(c, cudaMemcpyAsync(c->d_colidx, c->colidx.data(), sizeof(int32_t) * c->colidx.size(), cudaMemcpyHostToDevice, c->stream));
         CU_TRY(c, cudaMemsetAsync(c->d_item_counter, 0, sizeof(int), c->stream));
         // words of rows whose band holds no scored column block stay zero
         CU_TRY(c, cudaMemsetAsync(c->d_adj, 0, (size_t)total * sizeof(uint32_t), c->stream));
@@ -884,7 +928,7 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
         a.P = dev_params(c);
         a.hdr = c->d_hdr; a.ops = c->d_ops; a.aux = c->d_aux; a.col2op = c->d_col2op; a.prog = c->d_tprog;
         a.n_reads = c->n_reads; a.row_begin = row_begin; a.col0 = c->d_col0; a.word_off = c->d_word_off;
-        a.items = c->d_items; a.n_items = (int)n_items; a.item_counter = c->d_item_counter;
+        a.colidx = c->d_colidx; a.items = c->d_items; a.n_items = (int)n_items; a.item_counter = c->d_item_counter;
         a.adj = c->d_adj; a.stats = c->d_stats; a.amb = amb ? c->d_amb : nullptr; a.amb_cap = amb ? amb_cap : 0;
         a.detail = detail ? c->d_detail : nullptr;
         a.maxw = g.maxw; a.abuf_bytes = g.abuf_bytes;

@@ -42,7 +42,8 @@ struct Args {
     int n_reads, row_begin;
     const int32_t* col0;        // per row (row - row_begin)
     const long long* word_off;
-    const int4* items;          // {j-block, first row, end row, 0}
+    const int32_t* colidx;      // column blocks: 32 read indices per block (-1 = empty slot), see build_items()
+    const int4* items;          // {column block, first row, end row, 0}
     int n_items;
     int* item_counter;
     uint32_t* adj;
@@ -405,18 +406,15 @@ __global__ void __launch_bounds__(kThreads, 2) score_tile_kernel(const Args a) {
         const int item = ctl[0];
         if (item >= a.n_items) break;
         const int4 it = a.items[item];
-        const int jb = it.x, r0 = it.y, r1 = it.z;
-        const int j0 = jb * 32;
+        const int blk = it.x, r0 = it.y, r1 = it.z;
+        const int jmine = __ldg(a.colidx + (size_t)blk * 32 + lane);       // this lane's column read (every warp agrees)
         // ---- stage the 32 column reads: headers transposed, op streams interleaved word-wise
-        for (int k = tid; k < 16 * 32; k += kThreads) {
-            const int l = k & 31, f = k >> 5;
-            const int j = j0 + l;
-            hBsm[f * 32 + l] = j < a.n_reads ? __ldg(reinterpret_cast<const int*>(a.hdr + j) + f) : 0;
-        }
+        static_assert(kThreads == 16 * 32, "one thread per (header field, lane)");
+        hBsm[warp * 32 + lane] = jmine >= 0 ? __ldg(reinterpret_cast<const int*>(a.hdr + jmine) + warp) : 0;
         {
-            const int l = tid & 31;
-            const int j = j0 + l;
-            if (j < a.n_reads) {
+            const int l = lane;
+            const int j = jmine;
+            if (j >= 0) {
                 const int4 h2 = __ldg(reinterpret_cast<const int4*>(a.hdr + j) + 2);
                 const int nchunk = (h2.z + h2.w + 7) >> 3;
                 const uint4* src = reinterpret_cast<const uint4*>(a.ops + (unsigned)h2.x);
@@ -449,15 +447,17 @@ __global__ void __launch_bounds__(kThreads, 2) score_tile_kernel(const Args a) {
             const int* hA = reinterpret_cast<const int*>(mybuf0 + kb * bufstride);
             const uint16_t* opsA = reinterpret_cast<const uint16_t*>(mybuf0 + kb * bufstride + 64);
             const int i = rowA;
-            if (infA.col0 <= j0) {                                  // the row's band reaches this column block
-                const long long wd = infA.word_off + ((j0 - infA.col0) >> 5);
-                const int j = j0 + lane;
-                const bool active = j < i;
+            const int j = jmine;
+            const bool active = j >= 0 && j < i;
+            const bool covers = active && !(hA[14] < hB[13 * 32] || hB[14 * 32] < hA[13]);        // :1252
+            const unsigned n_total = __popc(__ballot_sync(FULL, active));
+            if (__any_sync(FULL, covers)) {                         // some column read of the block reaches this row
+                const int rel = j - infA.col0;                      // column inside the row's band (>= 0 whenever covers)
                 int status = HC_ST_REJECT_COV;
                 int pid = TP_NOP;
                 const unsigned fa = (unsigned)hA[12], fb = (unsigned)hB[12 * 32];
                 const bool se1 = fa & HC_FLAG_SINGLE_END, se2 = fb & HC_FLAG_SINGLE_END;
-                if (active && !(hA[14] < hB[13 * 32] || hB[14 * 32] < hA[13])) {        // :1252
+                if (covers) {
                     if (tile_layout_reject(hA, hB, se1, se2)) status = HC_ST_REJECT_LAYOUT;
                     else { status = HC_ST_WALKED; pid = pick_program(hA, hB, se1, se2); }
                 }
@@ -502,12 +502,12 @@ __global__ void __launch_bounds__(kThreads, 2) score_tile_kernel(const Args a) {
                     }
                 }
                 const unsigned bits = __ballot_sync(FULL, edge);
-                if (lane == 0) a.adj[wd] = bits;
-                if (a.detail != nullptr && active) {
+                if (edge) atomicOr(&a.adj[infA.word_off + (rel >> 5)], 1u << (rel & 31));
+                if (a.detail != nullptr && active && rel >= 0) {
                     hc_pair_result r;
                     r.status = status; r.edge = edge; r.gap = L.gap; r.cc = L.cc; r.tc = L.tc; r.ambiguous = ambiguous;
                     r.probM = L.probM; r.prob0 = prob0; r.score = score;
-                    a.detail[wd * 32 + lane] = r;
+                    a.detail[infA.word_off * 32 + rel] = r;
                 }
                 if (ambiguous) {
                     const unsigned long long slot = atomicAdd(&a.stats->ambiguous, 1ull);
@@ -519,7 +519,6 @@ __global__ void __launch_bounds__(kThreads, 2) score_tile_kernel(const Args a) {
                     }
                 }
                 const bool walked = status == HC_ST_WALKED;
-                const unsigned n_total = __popc(__ballot_sync(FULL, active));
                 const unsigned n_scored = __popc(__ballot_sync(FULL, active && status != HC_ST_REJECT_COV));
                 const unsigned n_walked = __popc(__ballot_sync(FULL, walked));
                 const unsigned n_undef = __popc(__ballot_sync(FULL, status == HC_ST_UNDEFINED));
@@ -534,6 +533,8 @@ __global__ void __launch_bounds__(kThreads, 2) score_tile_kernel(const Args a) {
                     atomicAdd(&cstat[5], (unsigned long long)s_tc);
                     atomicAdd(&cstat[6], (unsigned long long)n_undef);
                 }
+            } else if (lane == 0 && n_total) {
+                atomicAdd(&cstat[0], (unsigned long long)n_total);
             }
             __syncwarp();
             rowA = rowB; infA = infB; rowB = rowC; infB = infC; kb ^= 1;

@@ -157,7 +157,7 @@ def _tiled_detail_vs_oracle(b, kw, label):
     if differing == 0:
         assert adj.count() == edges
         assert (ai == ti[e == 1]).all() and (aj == tj[e == 1]).all()
-    assert adj.stats["pairs_total"] == pi.shape[0]
+    assert adj.stats["pairs_total"] >= adj.stats["pairs_scored"] == int((orc["status"] >= 1).sum())
     assert adj.stats["pairs_walked"] == int((orc["status"] == 2).sum())
     assert adj.stats["sum_cc"] == int(orc["cc"][orc["status"] == 2].sum())
     assert adj.stats["sum_tc"] == int(orc["tc"][orc["status"] == 2].sum())
