@@ -28,7 +28,13 @@ enum { TP_WORDS = 16, TP_SINGLE00 = 16, TP_SINGLE10 = 17, TP_SINGLE01 = 18, TP_T
 enum { SLOT_OVL0 = 3, SLOT_OVL1 = 7, SLOT_OVL2 = 11, SLOT_FINAL = 12 };
 #define TILE_MOP(op, x, y, a, b) ((uint32_t)(op) | ((uint32_t)(x) << 4) | ((uint32_t)(y) << 5) | ((uint32_t)(a) << 6) | ((uint32_t)(b) << 10))
 
-constexpr int kWarps = 16;
+#ifndef HC_TILE_WARPS
+#define HC_TILE_WARPS 16
+#endif
+#ifndef HC_TILE_MINBLOCKS
+#define HC_TILE_MINBLOCKS 2
+#endif
+constexpr int kWarps = HC_TILE_WARPS;
 constexpr int kThreads = kWarps * 32;
 constexpr unsigned FULL = 0xffffffffu;
 
@@ -222,10 +228,10 @@ __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int*
         TILE_MUL((AW) >> 24, (BW) >> 24, (x__ & 0x70000u) != 0u);                         \
     } while (0)
     for (;;) {
-        // -- four (then two) columns per iteration while both reads show M
+        // -- four (then two, then one) columns per iteration while both reads show M
         if (more && !qx) {
             const int run = min(min(hi - ref + 1, nA - ca), nB - cb);
-            if (run >= 2) {
+            if (run >= 1) {
                 const int ia = aoff + ca, ib = boff + cb;
                 const uint32_t* pa = opsA32 + (ia >> 1);
                 const uint32_t* pb = opsB + (ib >> 1) * 32;
@@ -245,52 +251,57 @@ __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int*
                     TILE_MUL2(A23, B23);
                     done += 4;
                 }
-                if (done + 2 <= run) {
-                    const uint32_t A01 = __funnelshift_r(a0, a1, sha), B01 = __funnelshift_r(b0, b1, shb);
-                    if (!((A01 | B01) & 0x00380038u)) {
-                        TILE_MUL2(A01, B01);
-                        done += 2;
-                    }
+                uint32_t Aw = __funnelshift_r(a0, a1, sha), Bw = __funnelshift_r(b0, b1, shb);
+                if (done + 2 <= run && !((Aw | Bw) & 0x00380038u)) {
+                    TILE_MUL2(Aw, Bw);
+                    done += 2;
+                    Aw = __funnelshift_r(a1, a2, sha); Bw = __funnelshift_r(b1, b2, shb);
+                }
+                if (done + 1 <= run && !((Aw | Bw) & 0x38u)) {
+                    TILE_MUL(__byte_perm(Aw, 0, 0x4441), __byte_perm(Bw, 0, 0x4441), ((Aw ^ Bw) & 0x7u) != 0u);
+                    done += 1;
                 }
                 ca += done; cb += done; ref += done; cc += done;
             }
         }
         __syncwarp();
-        // -- one generic step (overlapCheckgap, :145-232)
-        if (more) {
-            if (ref > hi) more = false;
-            else if (ca >= nA || cb >= nB) { L.undef = true; more = false; }
-            else {
-                const uint32_t ra = opsA[aoff + ca];
-                const uint32_t wb = opsB[((boff + cb) >> 1) * 32];
-                const uint32_t rb = ((boff + cb) & 1) ? (wb >> 16) : (wb & 0xffffu);
-                const int oa = (int)HC_REC_OP(ra), ob = (int)HC_REC_OP(rb);
-                const int act = (oa | ob) == 0 ? ACT_SCORE : op_action(oa, ob);
-                if (act == ACT_SCORE) {
-                    uint32_t sq = ra;
-                    bool ok = true;
-                    if (qx) {
-                        if (cq >= nA) { L.undef = true; more = false; ok = false; }
-                        else sq = opsA[aoff + cq];
-                    }
-                    if (ok) {
-                        TILE_MUL(HC_REC_QUAL(sq), HC_REC_QUAL(rb), HC_REC_BASE(sq ^ rb) != 0u);
-                        cc++;
-                        if (oa == HC_OP_M) ref++;
-                        ca++; cb++;
-                        if (qx) { cq++; while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
-                    }
-                } else if (act == ACT_SKIP) {
-                    ref++; ca++; cb++;
-                    if (qx && consumes_q(oa)) { cq++; while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
-                } else if (act == ACT_ADV_A) {
-                    ca++;
-                    if (qx) { cq++; while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
-                } else if (act == ACT_ADV_B) {
-                    cb++;
-                } else {
-                    L.gap = true; more = false;
+        // -- generic steps (overlapCheckgap, :145-232) until both reads show M again or the phase ends
+        while (more) {
+            if (ref > hi) { more = false; break; }
+            if (ca >= nA || cb >= nB) { L.undef = true; more = false; break; }
+            const uint32_t ra = opsA[aoff + ca];
+            const uint32_t wb = opsB[((boff + cb) >> 1) * 32];
+            const uint32_t rb = ((boff + cb) & 1) ? (wb >> 16) : (wb & 0xffffu);
+            const int oa = (int)HC_REC_OP(ra), ob = (int)HC_REC_OP(rb);
+            const int act = (oa | ob) == 0 ? ACT_SCORE : op_action(oa, ob);
+            if (act == ACT_SCORE) {
+                uint32_t sq = ra;
+                if (qx) {
+                    if (cq >= nA) { L.undef = true; more = false; break; }
+                    sq = opsA[aoff + cq];
                 }
+                TILE_MUL(HC_REC_QUAL(sq), HC_REC_QUAL(rb), HC_REC_BASE(sq ^ rb) != 0u);
+                cc++;
+                if (oa == HC_OP_M) ref++;
+                ca++; cb++;
+                if (qx) { cq++; while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
+            } else if (act == ACT_SKIP) {
+                ref++; ca++; cb++;
+                if (qx && consumes_q(oa)) { cq++; while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
+            } else if (act == ACT_ADV_A) {
+                ca++;
+                if (qx) { cq++; while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
+            } else if (act == ACT_ADV_B) {
+                cb++;
+            } else {
+                L.gap = true; more = false; break;
+            }
+            // hand back to the fast loop as soon as the next column is M against M again
+            if (!qx && ref <= hi && ca < nA && cb < nB) {
+                const uint32_t na = opsA[aoff + ca];
+                const uint32_t nw = opsB[((boff + cb) >> 1) * 32];
+                const uint32_t nb = ((boff + cb) & 1) ? (nw >> 16) : (nw & 0xffffu);
+                if (((na | nb) & 0x38u) == 0u) break;
             }
         }
         if (!__any_sync(FULL, more)) break;
@@ -348,7 +359,7 @@ __device__ __forceinline__ bool tile_layout_reject(const int* hA, const int* hB,
     return Ae2 < Bs1 || (Ae1 < Bs1 && Be1 < As2) || Be1 < As1;
 }
 
-__global__ void __launch_bounds__(kThreads, 2) score_tile_kernel(const Args a) {
+__global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel(const Args a) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int K = a.P.K;
@@ -409,8 +420,8 @@ __global__ void __launch_bounds__(kThreads, 2) score_tile_kernel(const Args a) {
         const int blk = it.x, r0 = it.y, r1 = it.z;
         const int jmine = __ldg(a.colidx + (size_t)blk * 32 + lane);       // this lane's column read (every warp agrees)
         // ---- stage the 32 column reads: headers transposed, op streams interleaved word-wise
-        static_assert(kThreads == 16 * 32, "one thread per (header field, lane)");
-        hBsm[warp * 32 + lane] = jmine >= 0 ? __ldg(reinterpret_cast<const int*>(a.hdr + jmine) + warp) : 0;
+        static_assert(kWarps >= 16, "one thread per (header field, lane)");
+        if (warp < 16) hBsm[warp * 32 + lane] = jmine >= 0 ? __ldg(reinterpret_cast<const int*>(a.hdr + jmine) + warp) : 0;
         {
             const int l = lane;
             const int j = jmine;

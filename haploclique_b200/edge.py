@@ -92,6 +92,7 @@ def load_library():
         L.hc_score_band_detail.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
         L.hc_set_kernel.argtypes = [C.c_void_p, C.c_int32]
         L.hc_last_kernel.argtypes = [C.c_void_p]
+        L.hc_measure_peaks.argtypes = [C.c_int32, C.c_void_p, C.c_void_p]
         L.hc_get_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         assert C.sizeof(_BandStats) == 72 and HDR_DTYPE.itemsize == 64
         _lib = L
@@ -391,6 +392,16 @@ class NewEdgeCalculator(EdgeCalculator):
 def pack_only(batch: ReadBatch) -> PackedBatch:
     """hc_pack without a device (host C++ packing only)."""
     return PackedBatch(batch)
+
+
+def measure_peaks(device: int = 0):
+    """(shared-memory load GB/s, DMUL/s) of `device`, measured now by the library's probes."""
+    L = load_library()
+    a, b = C.c_double(0), C.c_double(0)
+    rc = L.hc_measure_peaks(device, C.byref(a), C.byref(b))
+    if rc != HC_OK:
+        raise HcError("hc_measure_peaks failed (%d): %s" % (rc, L.hc_last_error(None).decode()))
+    return a.value, b.value
 
 
 def device_count() -> int:

@@ -235,6 +235,29 @@ class ReadBatch:
             b.names = [self.names[int(i)] for i in order]
         return b
 
+    @staticmethod
+    def concat_sorted(parts: Sequence["ReadBatch"]) -> "ReadBatch":
+        """Concatenates batches and re-sorts the reads by start1 (stable), the order readBamFile hands to the finder."""
+        parts = [p for p in parts if p.n > 0]
+        if not parts:
+            return ReadBatch(0)
+        b = ReadBatch(sum(p.n for p in parts))
+        for f in ("single_end", "is_clique", "ncov", "cov_first", "cov_last", "seg_start", "seg_end", "cig_len", "seq_len",
+                  "cig", "seq", "qual"):
+            setattr(b, f, np.concatenate([getattr(p, f) for p in parts]))
+        co = so = 0
+        offs_c, offs_s = [], []
+        for p in parts:
+            offs_c.append(p.cig_off + co)
+            offs_s.append(p.seq_off + so)
+            co += int(p.cig.shape[0])
+            so += int(p.seq.shape[0])
+        b.cig_off, b.seq_off = np.concatenate(offs_c), np.concatenate(offs_s)
+        if all(p.names is not None for p in parts):
+            b.names = [nm for p in parts for nm in p.names]
+        order = np.argsort(b.seg_start[0::2], kind="stable")
+        return b.permute(order)
+
     # -- (de)serialisation for committed fixtures --------------------------------------------------
     _FIELDS = ("single_end", "is_clique", "ncov", "cov_first", "cov_last", "seg_start", "seg_end",
                "cig_off", "cig_len", "seq_off", "seq_len", "cig", "seq", "qual")

@@ -26,7 +26,9 @@ def quasispecies(n_frag: int, genome_len: int = 9719, read_len: int = 250, frag_
                  frag_sd: float = 60.0, frag_min: int = 260, frag_max: int = 800,
                  snv_rates=(0.01, 0.02, 0.03, 0.04, 0.05), hap_freq=(0.40, 0.25, 0.15, 0.12, 0.08),
                  indel_err: float = 1e-4, clip_frac: float = 0.01, n_frac: float = 5e-4,
-                 seed: int = 20261104) -> ReadBatch:
+                 seed: int = 20261104, frag_seed=None) -> ReadBatch:
+    """`seed` fixes the reference and the haplotypes; `frag_seed` (default: continue the same stream) the fragments,
+    their qualities and errors."""
     rng = np.random.default_rng(seed)
     G = int(genome_len)
     H = len(hap_freq)
@@ -45,6 +47,8 @@ def quasispecies(n_frag: int, genome_len: int = 9719, read_len: int = 250, frag_
             hap_ins_col[h] = int(rng.integers(G // 8, G - G // 8))
             hap_ins_len[h] = int(rng.integers(1, 4))
     hap_ins_bases = rng.integers(0, 4, (H, 3), dtype=np.uint8)
+    if frag_seed is not None:
+        rng = np.random.default_rng(frag_seed)
 
     # -- fragments -> segments -------------------------------------------------------------------------
     L = np.clip(np.rint(rng.normal(frag_mean, frag_sd, n_frag)), frag_min, min(frag_max, G)).astype(np.int64)
@@ -149,6 +153,28 @@ def quasispecies(n_frag: int, genome_len: int = 9719, read_len: int = 250, frag_
     if (order != np.arange(n)).any():
         b = b.permute(order)
     return b
+
+
+def quasispecies_sharded(n_frag: int, chunk: int = 50_000, start_window=None, seed: int = 20261104, **kw) -> ReadBatch:
+    """The same kind of read set generated in chunks of `chunk` fragments (chunk k uses seed+1000*k for its
+    fragments; the haplotypes come from `seed` and are shared), merged and sorted by start. `start_window` =
+    (lo, hi) keeps only reads with lo <= start1 < hi: every rank of a sharded run generates the same global
+    read set and keeps its own genome-position window plus the halo to its left, so memory stays bounded by
+    one chunk plus the kept reads."""
+    parts = []
+    k = 0
+    left = int(n_frag)
+    while left > 0:
+        n = min(chunk, left)
+        b = quasispecies(n, seed=seed, frag_seed=seed + 1000 * (k + 1), **kw)
+        if start_window is not None:
+            st = b.seg_start[0::2]
+            keep = np.nonzero((st >= start_window[0]) & (st < start_window[1]))[0]
+            b = b.permute(keep)
+        parts.append(b)
+        left -= n
+        k += 1
+    return ReadBatch.concat_sorted(parts)
 
 
 def zoo(n_reads: int, genome_len: int = 400, seed: int = 1, max_seg: int = 120, clique_frac: float = 0.3) -> ReadBatch:

@@ -211,6 +211,10 @@ int hc_l2_flush(hc_ctx* ctx);
 void* hc_host_alloc(int64_t bytes);
 void hc_host_free(void* p);
 
+/* On-chip peak probes for the roofline (bench.py): sustained shared-memory load bandwidth over all SMs (GB/s,
+ * conflict-free 128-bit loads) and fp64 multiply rate (DMUL/s, independent chains), measured on `device` now. */
+int hc_measure_peaks(int32_t device, double* lds_gbs, double* dmul_per_s);
+
 /* The two 127x127 match-probability tables the context uploaded (row-major [q1][q2], doubles). */
 int hc_get_tables(const hc_ctx* ctx, double* eq127x127, double* uneq127x127);
 
