@@ -58,7 +58,8 @@ def make_workload(name, n_frag, rank=0, world=1):
     n = kw.pop("n_frag")
     G = kw["genome_len"]
     if world == 1:
-        b = synth.quasispecies(n, **kw) if n <= 200_000 else synth.quasispecies_sharded(n, **kw)
+        # C2 is one draw; every other workload is the chunked draw, so that N=1 and N>1 see the same read set
+        b = synth.quasispecies(n, **kw) if name == "C2" else synth.quasispecies_sharded(n, **kw)
         return b, 0, dict(kw, n_frag=n)
     lo = 1 + (G * rank) // world
     hi = 1 + (G * (rank + 1)) // world if rank + 1 < world else G + 2 * HALO
@@ -185,6 +186,8 @@ def main():
         raise SystemExit("bench.py: no CUDA device; the scored path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"              # keep rank 0's stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     t0 = time.perf_counter()

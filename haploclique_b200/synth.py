@@ -205,7 +205,7 @@ def zoo(n_reads: int, genome_len: int = 400, seed: int = 1, max_seg: int = 120, 
         return start_ext + lead, start_ext + ncol - trail - 1, cig, seq, qual
 
     # a shared "true" sequence makes many pairs similar enough to pass the thresholds
-    truth = _BASES[rng.integers(0, 4, genome_len + 2 * max_seg + 64)]
+    truth = _BASES[rng.integers(0, 4, genome_len + 4 * max_seg + 64)]
     for r in range(n_reads):
         name = ("Clique_%d" % r) if rng.random() < clique_frac else ("read_%d" % r)
         s1 = int(rng.integers(1, genome_len)) // 4 * 4 + 1        # coarse grid -> many ties

@@ -1,0 +1,160 @@
+// GpuEdgeCalculator.cpp -- see GpuEdgeCalculator.h. Host C++ only; all scoring is behind the C ABI (hc_edge.h).
+#include "GpuEdgeCalculator.h"
+
+#include <cassert>
+#include <cstring>
+#include <stdexcept>
+
+struct GpuEdgeCalculator::Flat {
+    std::vector<uint8_t> single_end, is_clique, cig, seq, qual;
+    std::vector<int32_t> ncov, cov_first, cov_last, seg_start, seg_end, cig_len, seq_len;
+    std::vector<int64_t> cig_off, seq_off;
+    hc_reads view() const {
+        hc_reads r;
+        r.n = (int32_t)single_end.size();
+        r.single_end = single_end.data(); r.is_clique = is_clique.data();
+        r.ncov = ncov.data(); r.cov_first = cov_first.data(); r.cov_last = cov_last.data();
+        r.seg_start = seg_start.data(); r.seg_end = seg_end.data();
+        r.cig_off = cig_off.data(); r.cig_len = cig_len.data(); r.seq_off = seq_off.data(); r.seq_len = seq_len.data();
+        r.cig = cig.data(); r.seq = seq.data(); r.qual = qual.data();
+        return r;
+    }
+};
+
+// AlignmentRecord getters (src/AlignmentRecord.cpp:1703-1811) -> the SoA the packer reads. Only what
+// NewEdgeCalculator::edgeBetween touches: single_end, the "Clique" name test (src/NewEdgeCalculator.cpp:1111),
+// cov_pos size / first / last (:1127, :1252), start/end, unrolled CIGARs, bases, qualities.
+void GpuEdgeCalculator::flatten(const std::vector<const AlignmentRecord*>& reads, Flat& f) {
+    const size_t n = reads.size();
+    f.single_end.resize(n); f.is_clique.resize(n); f.ncov.resize(n); f.cov_first.resize(n); f.cov_last.resize(n);
+    f.seg_start.assign(2 * n, 0); f.seg_end.assign(2 * n, 0); f.cig_len.assign(2 * n, 0); f.seq_len.assign(2 * n, 0);
+    f.cig_off.assign(2 * n, 0); f.seq_off.assign(2 * n, 0);
+    f.cig.clear(); f.seq.clear(); f.qual.clear();
+    for (size_t r = 0; r < n; ++r) {
+        const AlignmentRecord& ar = *reads[r];
+        const bool single = ar.isSingleEnd();
+        f.single_end[r] = single ? 1 : 0;
+        f.is_clique[r] = ar.getName().find("Clique") != std::string::npos ? 1 : 0;
+        const std::vector<AlignmentRecord::mapValue>& cov = ar.getCovmap();
+        if (cov.empty()) throw std::runtime_error("GpuEdgeCalculator: read " + ar.getName() + " covers no reference position");
+        f.ncov[r] = (int32_t)cov.size();
+        f.cov_first[r] = cov.front().ref;
+        f.cov_last[r] = cov.back().ref;
+        for (int s = 0; s < (single ? 1 : 2); ++s) {
+            const std::vector<char>& cg = s ? ar.getCigar2Unrolled() : ar.getCigar1Unrolled();
+            const ShortDnaSequence& sq = s ? ar.getSequence2() : ar.getSequence1();
+            const std::string& bases = sq.toString();
+            const std::string& quals = sq.qualityString();
+            const size_t k = 2 * r + s;
+            f.seg_start[k] = s ? ar.getStart2() : ar.getStart1();
+            f.seg_end[k] = s ? ar.getEnd2() : ar.getEnd1();
+            f.cig_off[k] = (int64_t)f.cig.size();
+            f.cig_len[k] = (int32_t)cg.size();
+            f.seq_off[k] = (int64_t)f.seq.size();
+            f.seq_len[k] = (int32_t)bases.size();
+            f.cig.insert(f.cig.end(), cg.begin(), cg.end());
+            f.seq.insert(f.seq.end(), bases.begin(), bases.end());
+            f.qual.insert(f.qual.end(), quals.begin(), quals.end());
+        }
+        if (single) { f.cig_off[2 * r + 1] = (int64_t)f.cig.size(); f.seq_off[2 * r + 1] = (int64_t)f.seq.size(); }
+    }
+}
+
+void GpuEdgeCalculator::fail(const char* what, int rc) const {
+    throw std::runtime_error(std::string("GpuEdgeCalculator: ") + what + " failed (" + std::to_string(rc) + "): " +
+                             hc_last_error(ctx_));
+}
+
+GpuEdgeCalculator::GpuEdgeCalculator(double, double edge_quasi_cutoff, double overlap, bool, std::unordered_map<int, double>& simpson_map,
+                                     double edge_quasi_cutoff_single, double overlap_single, double edge_quasi_cutoff_mixed,
+                                     unsigned int maxPosition, bool noProb0, int device)
+    : ctx_(nullptr), resident_(nullptr), resident_dirty_(false) {
+    std::memset(&par_, 0, sizeof par_);
+    std::memset(&stats_, 0, sizeof stats_);
+    par_.edge_quasi_cutoff_cliques = edge_quasi_cutoff;
+    par_.edge_quasi_cutoff_mixed = edge_quasi_cutoff_mixed;
+    par_.edge_quasi_cutoff_single = edge_quasi_cutoff_single;
+    par_.min_overlap_cliques = overlap;
+    par_.min_overlap_single = overlap_single;
+    par_.no_prob0 = noProb0 ? 1 : 0;
+    par_.device = device;
+    if (!simpson_map.empty()) {                            // SIMPSON_MAP.resize(maxPosition+1) (src/NewEdgeCalculator.cpp:85-88)
+        simpson_.assign((size_t)maxPosition + 1, 0.0);
+        for (const auto& kv : simpson_map)
+            if (kv.first >= 0 && (size_t)kv.first < simpson_.size()) simpson_[kv.first] = kv.second;
+        par_.simpson = simpson_.data();
+        par_.simpson_len = (int32_t)simpson_.size();
+    }
+    const int rc = hc_create(&par_, &ctx_);
+    if (rc != HC_OK) throw std::runtime_error(std::string("GpuEdgeCalculator: hc_create failed: ") + hc_last_error(nullptr));
+}
+
+GpuEdgeCalculator::~GpuEdgeCalculator() {
+    hc_packed_free(resident_);
+    hc_destroy(ctx_);
+}
+
+void GpuEdgeCalculator::scoreBatch(const std::deque<AlignmentRecord*>& reads) {
+    std::vector<const AlignmentRecord*> v(reads.begin(), reads.end());
+    scoreBatch(v);
+}
+
+void GpuEdgeCalculator::scoreBatch(const std::vector<const AlignmentRecord*>& reads) {
+    index_.clear();
+    for (size_t k = 0; k < reads.size(); ++k) index_[reads[k]] = (int)k;
+    Flat f;
+    flatten(reads, f);
+    const hc_reads view = f.view();
+    hc_packed_free(resident_);
+    resident_ = nullptr;
+    int rc = hc_pack(&view, &resident_);
+    if (rc != HC_OK) throw std::runtime_error(std::string("GpuEdgeCalculator: hc_pack failed: ") + hc_last_error(nullptr));
+    if ((rc = hc_upload(ctx_, resident_)) != HC_OK) fail("hc_upload", rc);
+    resident_dirty_ = false;
+    const int n = (int)reads.size();
+    col0_.assign((size_t)std::max(n, 1), 0);
+    word_off_.assign((size_t)n + 1, 0);
+    int64_t n_words = 0;
+    if ((rc = hc_band_layout(ctx_, 0, n, col0_.data(), word_off_.data(), &n_words)) != HC_OK) fail("hc_band_layout", rc);
+    words_.assign((size_t)std::max<int64_t>(n_words, 1), 0u);
+    if ((rc = hc_score_band(ctx_, 0, n, words_.data(), n_words, nullptr, 0, &stats_)) != HC_OK) fail("hc_score_band", rc);
+}
+
+bool GpuEdgeCalculator::edgeBetween(const AlignmentRecord& ap1, const AlignmentRecord& ap2) const {
+    const auto it1 = index_.find(&ap1), it2 = index_.find(&ap2);
+    if (it1 != index_.end() && it2 != index_.end() && it2->second < it1->second) {
+        const int i = it1->second, j = it2->second;
+        if (j < col0_[i]) return false;                    // left of the band: the reference's first reject (:1252)
+        const int rel = j - col0_[i];
+        return (words_[(size_t)word_off_[i] + (rel >> 5)] >> (rel & 31)) & 1u;
+    }
+    // any other two records: a two-read batch, ap2 first (the earlier arrival), scored on the device
+    std::vector<const AlignmentRecord*> two;
+    two.push_back(&ap2);
+    two.push_back(&ap1);
+    Flat f;
+    flatten(two, f);
+    const hc_reads view = f.view();
+    hc_packed* pk = nullptr;
+    int rc = hc_pack(&view, &pk);
+    if (rc != HC_OK) throw std::runtime_error(std::string("GpuEdgeCalculator: hc_pack failed: ") + hc_last_error(nullptr));
+    rc = hc_upload(ctx_, pk);
+    hc_pair_result res;
+    const int32_t pi = 1, pj = 0;
+    if (rc == HC_OK) rc = hc_score_pairs(ctx_, &pi, &pj, 1, &res);
+    hc_packed_free(pk);
+    if (resident_ != nullptr) {                            // put the scored batch back for later pair queries
+        const int rc2 = hc_upload(ctx_, resident_);
+        if (rc2 != HC_OK) fail("hc_upload", rc2);
+    }
+    if (rc != HC_OK) fail("hc_score_pairs", rc);
+    return res.edge != 0;
+}
+
+void GpuEdgeCalculator::getPartnerLengthRange(const AlignmentRecord&, unsigned int*, unsigned int*) const { assert(false); }
+
+void GpuEdgeCalculator::setOverlapCliques(double d) {      // NewEdgeCalculator::setOverlapCliques (src/NewEdgeCalculator.cpp:1382)
+    par_.min_overlap_cliques = d;
+    const int rc = hc_set_params(ctx_, &par_);
+    if (rc != HC_OK) fail("hc_set_params", rc);
+}

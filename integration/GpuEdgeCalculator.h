@@ -1,0 +1,74 @@
+// GpuEdgeCalculator -- the reference-side binding of libhcgpu.so.
+//
+// A drop-in for the reference's NewEdgeCalculator behind its own plugin interface
+// (class EdgeCalculator, src/EdgeCalculator.h:24-37). Compiled INSIDE the reference tree (it includes the
+// reference's headers); nothing of the reference is copied here. Same constructor arguments as
+// NewEdgeCalculator (src/NewEdgeCalculator.h:58) plus the CUDA device ordinal.
+//
+// Use (INTEGRATION.md shows the four-line change to src/haploclique.cpp):
+//     GpuEdgeCalculator* calc = new GpuEdgeCalculator(Q, cutoff, overlap, fs_merge, simpson_map, cutoff_single,
+//                                                      overlap_single, cutoff_mixed, max_position, no_prob0);
+//     ... once per iteration, with the reads that will be handed to the clique finder, in that order:
+//     calc->scoreBatch(reads_of_this_iteration);
+//     ... CLEVER / BronKerbosch unchanged: their edgeBetween(new, old) calls are answered from the adjacency words.
+//
+// There is no CPU scoring path: every answer comes from the CUDA kernels; if the library cannot reach a device the
+// constructor throws std::runtime_error.
+#ifndef GPUEDGECALCULATOR_H_
+#define GPUEDGECALCULATOR_H_
+
+#include <deque>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "AlignmentRecord.h"
+#include "EdgeCalculator.h"
+
+extern "C" {
+#include "hc_edge.h"
+}
+
+class GpuEdgeCalculator : public EdgeCalculator {
+public:
+    GpuEdgeCalculator(double Q, double edge_quasi_cutoff, double overlap, bool frameshift_merge,
+                      std::unordered_map<int, double>& simpson_map, double edge_quasi_cutoff_single, double overlap_single,
+                      double edge_quasi_cutoff_mixed, unsigned int maxPosition, bool noProb0, int device = 0);
+    virtual ~GpuEdgeCalculator();
+
+    /** Packs the reads (arrival order = the order they will be added to the clique finder), uploads them and scores
+     *  the whole band on the GPU. After this, edgeBetween(a, b) for two reads of the batch is a bit lookup. */
+    void scoreBatch(const std::vector<const AlignmentRecord*>& reads);
+    void scoreBatch(const std::deque<AlignmentRecord*>& reads);
+
+    /** edgeBetween(new arrival, earlier arrival), as both clique finders call it (src/CLEVER.cpp:220,
+     *  src/BronKerbosch.cpp:286). Two records outside the scored batch (the reference's unit tests call it that way)
+     *  are packed as a two-read batch and scored on the GPU. */
+    virtual bool edgeBetween(const AlignmentRecord& ap1, const AlignmentRecord& ap2) const;
+    /** Not implemented by NewEdgeCalculator either (src/NewEdgeCalculator.cpp:1378-1380). */
+    virtual void getPartnerLengthRange(const AlignmentRecord& ap, unsigned int* min, unsigned int* max) const;
+    virtual void setOverlapCliques(double d);
+
+    long edges() const { return stats_.edges; }
+    long scoredPairs() const { return stats_.pairs_scored; }
+    long nearThresholdPairs() const { return stats_.ambiguous; }
+    double kernelMilliseconds() const { return stats_.kernel_ms; }
+
+private:
+    struct Flat;                                           // SoA staging of AlignmentRecord fields (hc_reads)
+    static void flatten(const std::vector<const AlignmentRecord*>& reads, Flat& f);
+    void fail(const char* what, int rc) const;
+
+    hc_params par_;
+    std::vector<double> simpson_;
+    hc_ctx* ctx_;
+    std::unordered_map<const AlignmentRecord*, int> index_;   // record -> arrival index in the scored batch
+    std::vector<int32_t> col0_;
+    std::vector<int64_t> word_off_;
+    std::vector<uint32_t> words_;
+    hc_band_stats stats_;
+    mutable hc_packed* resident_;                          // the scored batch (re-uploaded after an out-of-batch query)
+    mutable bool resident_dirty_;
+};
+
+#endif /* GPUEDGECALCULATOR_H_ */

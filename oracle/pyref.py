@@ -13,6 +13,9 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_HERE, "_ref", "libhcref.so")
+_LIB_GPU = os.path.join(_HERE, "_ref", "libhcref_gpu.so")   # + integration/GpuEdgeCalculator, linked with libhcgpu.so
+CLI_REF = os.path.join(_HERE, "_ref", "haploclique_ref")
+CLI_GPU = os.path.join(_HERE, "_ref", "haploclique_gpu")
 REFERENCE_ROOT = "/root/reference"
 
 
@@ -20,13 +23,40 @@ def available() -> bool:
     return os.path.exists(_LIB)
 
 
+def gpu_adapter_available() -> bool:
+    return os.path.exists(_LIB_GPU)
+
+
 def build() -> bool:
     if os.path.exists(os.path.join(REFERENCE_ROOT, "src", "NewEdgeCalculator.cpp")):
         subprocess.check_call(["make", "-s", "-j8", "-C", _HERE, "ref"])
+        if os.path.exists(os.path.join(_HERE, "..", "haploclique_b200", "libhcgpu.so")):
+            subprocess.check_call(["make", "-s", "-j8", "-C", _HERE, "gpu"])
     return available()
 
 
 _lib = None
+_lib_gpu = None
+
+
+def _declare(L):
+    L.hcref_new.restype = C.c_void_p
+    L.hcref_error.restype = C.c_char_p
+    L.hcref_score_all.restype = C.c_long
+    L.hcref_time_pairs.restype = C.c_double
+    L.hcref_max_position.restype = C.c_uint
+    return L
+
+
+def lib_gpu():
+    """libhcref_gpu.so: the same face plus hcref_iterate_gpu / hcref_edge_gpu (the reference's finders driven by the
+    product's GpuEdgeCalculator)."""
+    global _lib_gpu
+    if _lib_gpu is None:
+        if not gpu_adapter_available():
+            raise RuntimeError("oracle/_ref/libhcref_gpu.so missing: run `make -C oracle gpu` where /root/reference exists")
+        _lib_gpu = _declare(C.CDLL(_LIB_GPU))
+    return _lib_gpu
 
 
 def lib():
@@ -56,8 +86,8 @@ def _p(a):
 class Reference:
     """Holds reference AlignmentRecord objects and one NewEdgeCalculator."""
 
-    def __init__(self):
-        self.L = lib()
+    def __init__(self, gpu_adapter: bool = False):
+        self.L = lib_gpu() if gpu_adapter else lib()
         self.h = C.c_void_p(self.L.hcref_new())
 
     def __del__(self):
@@ -72,6 +102,13 @@ class Reference:
         if n < 0:
             raise RuntimeError(self.L.hcref_error(self.h).decode())
         return n
+
+    def bam_writer_open(self, path: str, ref_name: str, ref_len: int) -> None:
+        if self.L.hcref_bam_writer_open(self.h, path.encode(), ref_name.encode(), C.c_int(ref_len)) != 0:
+            raise RuntimeError(self.L.hcref_error(self.h).decode())
+
+    def bam_writer_close(self) -> None:
+        self.L.hcref_bam_writer_close(self.h)
 
     def restore_fixture(self, path: str) -> int:
         return self.L.hcref_restore_fixture(self.h, path.encode())
@@ -169,3 +206,21 @@ class Reference:
         n = self.L.hcref_iterate(self.h, C.c_int(int(use_bk)), C.c_int(int(filter_singletons)),
                                  C.c_double(significance), state, C.byref(sd), logfile.encode())
         return n, state[0], state[1], bool(state[2]), sd.value
+
+    def iterate_gpu(self, ct: int, stdev: float, use_bk=False, filter_singletons=False, significance=0.0, logfile=""):
+        """The same pass with GpuEdgeCalculator (integration/) plugged into the reference's finder; needs a CUDA device.
+        Returns (n_next, ct, edges counted by the finder, converged, stdev, edges in the GPU adjacency)."""
+        state = (C.c_int * 3)(ct, 0, 0)
+        sd = C.c_double(stdev)
+        ge = C.c_long(0)
+        n = self.L.hcref_iterate_gpu(self.h, C.c_int(int(use_bk)), C.c_int(int(filter_singletons)),
+                                     C.c_double(significance), state, C.byref(sd), logfile.encode(), C.byref(ge))
+        if n < 0:
+            raise RuntimeError("hcref_iterate_gpu failed (%d): %s" % (n, self.L.hcref_error(self.h).decode()))
+        return n, state[0], state[1], bool(state[2]), sd.value, int(ge.value)
+
+    def edge_gpu(self, i: int, j: int) -> bool:
+        r = self.L.hcref_edge_gpu(self.h, i, j)
+        if r < 0:
+            raise RuntimeError("hcref_edge_gpu failed: %s" % self.L.hcref_error(self.h).decode())
+        return bool(r)

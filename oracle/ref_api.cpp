@@ -13,6 +13,10 @@
 #include "haploclique.cpp"
 #undef main
 
+#ifdef HC_WITH_GPU_ADAPTER
+#include "GpuEdgeCalculator.h"          // integration/: the product's reference-side binding, tested through the reference's finders
+#endif
+
 #include <atomic>
 #include <chrono>
 #include <cstring>
@@ -33,7 +37,9 @@ struct RefCtx {
     size_t maxpos_done = 0;
     std::unordered_map<int, double> simpson;
     std::string err;
+    BamTools::BamWriter* writer = nullptr;   // optional: every alignment fed to hcref_add_alignment is also written here
     ~RefCtx() {
+        if (writer) { writer->Close(); delete writer; }
         for (auto* r : recs) delete r;
         for (auto& kv : open_mates) delete kv.second;
         delete calc;
@@ -129,6 +135,10 @@ int hcref_add_alignment(void* p, const char* name, int pos0, const char* cigar_u
     al.QueryBases.assign(bases, nq);
     al.Qualities.assign(quals, nq);
     al.Length = nq;
+    if (c->writer) {
+        al.RefID = 0; al.MateRefID = -1; al.MatePosition = -1; al.MapQuality = 60; al.AlignmentFlag = 0; al.InsertSize = 0; al.Bin = 0;
+        c->writer->SaveAlignment(al);
+    }
     bool valid = false;
     for (auto& op : al.CigarData) if (op.Type == 'M' && op.Length > 0) valid = true;
     if (!valid) return 0;
@@ -142,6 +152,24 @@ int hcref_add_alignment(void* p, const char* name, int pos0, const char* cigar_u
         c->names.push_back(al.Name);
     }
     return 1;
+}
+
+// Opens a BAM file (the reference's vendored BamWriter) that receives every alignment passed to hcref_add_alignment,
+// so that synthetic read sets can be fed to the unmodified CLI. One reference sequence `ref_name` of length ref_len.
+int hcref_bam_writer_open(void* p, const char* path, const char* ref_name, int ref_len) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    if (c->writer) { c->writer->Close(); delete c->writer; c->writer = nullptr; }
+    BamTools::RefVector refs;
+    refs.push_back(BamTools::RefData(ref_name, ref_len));
+    const std::string header = std::string("@HD\tVN:1.0\tSO:unsorted\n@SQ\tSN:") + ref_name + "\tLN:" + std::to_string(ref_len) + "\n";
+    c->writer = new BamTools::BamWriter();
+    if (!c->writer->Open(path, header, refs)) { c->err = "BamWriter::Open failed"; delete c->writer; c->writer = nullptr; return -1; }
+    return 0;
+}
+int hcref_bam_writer_close(void* p) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    if (c->writer) { c->writer->Close(); delete c->writer; c->writer = nullptr; }
+    return 0;
 }
 
 // End of readBamFile: leftovers appended, optional sort by interval start, max_position (:178-198).
@@ -310,29 +338,41 @@ double hcref_time_pairs(void* p, const int* pi, const int* pj, long npairs, int 
 // One pass of the CLI's main loop body (src/haploclique.cpp:349-372) with CLEVER or BronKerbosch:
 // consumes the current records, replaces them by the collector's position-sorted super-reads.
 // state[0]=ct (in/out), state[1]=edges (out), state[2]=converged (out); stdev in/out.
-int hcref_iterate(void* p, int use_bk, int filter_singletons, double significance, int* state, double* stdev,
-                  const char* logfile) {
-    RefCtx* c = static_cast<RefCtx*>(p);
+// One pass of the CLI main loop (src/haploclique.cpp:349-372) with the given calculator. When `gpu` is set, the reads
+// that survive the filter are first handed to GpuEdgeCalculator::scoreBatch (the driver hook of INTEGRATION.md).
+static int iterate_impl(RefCtx* c, EdgeCalculator& calc, int use_bk, int filter_singletons, double significance, int* state,
+                        double* stdev, const char* logfile, void* gpu) {
     int ct = state[0];
     std::vector<unsigned int> read_clique_counter(c->names.size());
     LogWriter* lw = (logfile && logfile[0]) ? new LogWriter(logfile, read_clique_counter) : nullptr;
     CliqueCollector collector(lw);
     CliqueFinder* finder;
-    if (use_bk) finder = new BronKerbosch(*c->calc, collector, lw);
-    else finder = new CLEVER(*c->calc, collector, lw, 0, 0, c->names.size(), filter_singletons != 0);
+    if (use_bk) finder = new BronKerbosch(calc, collector, lw);
+    else finder = new CLEVER(calc, collector, lw, 0, 0, c->names.size(), filter_singletons != 0);
     finder->initialize();
     if (lw) lw->initialize();
     int size = (int)c->recs.size();
     int edgecounter = 0;
     double sd = *stdev;
+    std::vector<AlignmentRecord*> kept;
     for (auto* r : c->recs) {
-        std::unique_ptr<AlignmentRecord> al(r);
-        bool drop = (ct == 1 && filter_singletons && al->getReadCount() <= 1) ||
-                    (ct > 1 && significance != 0.0 && al->getProbability() < 1.0 / size - significance * sd);
-        if (drop) continue;
-        finder->addAlignment(al, edgecounter);
+        bool drop = (ct == 1 && filter_singletons && r->getReadCount() <= 1) ||
+                    (ct > 1 && significance != 0.0 && r->getProbability() < 1.0 / size - significance * sd);
+        if (drop) delete r; else kept.push_back(r);
     }
     c->recs.clear();
+#ifdef HC_WITH_GPU_ADAPTER
+    if (gpu) {
+        std::vector<const AlignmentRecord*> v(kept.begin(), kept.end());
+        static_cast<GpuEdgeCalculator*>(gpu)->scoreBatch(v);
+    }
+#else
+    (void)gpu;
+#endif
+    for (auto* r : kept) {
+        std::unique_ptr<AlignmentRecord> al(r);
+        finder->addAlignment(al, edgecounter);
+    }
     finder->finish();
     std::deque<AlignmentRecord*>* next = collector.finish();
     if (lw) lw->finish();
@@ -345,6 +385,52 @@ int hcref_iterate(void* p, int use_bk, int filter_singletons, double significanc
     delete finder;
     delete lw;
     return (int)c->recs.size();
+}
+
+int hcref_iterate(void* p, int use_bk, int filter_singletons, double significance, int* state, double* stdev,
+                  const char* logfile) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    return iterate_impl(c, *c->calc, use_bk, filter_singletons, significance, state, stdev, logfile, nullptr);
+}
+
+// The same pass with the product's GpuEdgeCalculator plugged into the reference's finder. -1 = adapter not built
+// into this library, -2 = the adapter threw (no device, ...): message in hcref_error.
+int hcref_iterate_gpu(void* p, int use_bk, int filter_singletons, double significance, int* state, double* stdev,
+                      const char* logfile, long* gpu_edges) {
+#ifdef HC_WITH_GPU_ADAPTER
+    RefCtx* c = static_cast<RefCtx*>(p);
+    try {
+        GpuEdgeCalculator calc(c->Q, c->cut_cliques, c->ov_cliques, c->frameshift, c->simpson, c->cut_single, c->ov_single,
+                               c->cut_mixed, c->max_position, c->no_prob0);
+        const int n = iterate_impl(c, calc, use_bk, filter_singletons, significance, state, stdev, logfile, &calc);
+        if (gpu_edges) *gpu_edges = calc.edges();
+        return n;
+    } catch (const std::exception& e) {
+        c->err = e.what();
+        return -2;
+    }
+#else
+    (void)p; (void)use_bk; (void)filter_singletons; (void)significance; (void)state; (void)stdev; (void)logfile; (void)gpu_edges;
+    return -1;
+#endif
+}
+
+// edgeBetween through the adapter for two stored records (the reference's unit-test style call). -1 on error.
+int hcref_edge_gpu(void* p, int i, int j) {
+#ifdef HC_WITH_GPU_ADAPTER
+    RefCtx* c = static_cast<RefCtx*>(p);
+    try {
+        GpuEdgeCalculator calc(c->Q, c->cut_cliques, c->ov_cliques, c->frameshift, c->simpson, c->cut_single, c->ov_single,
+                               c->cut_mixed, c->max_position, c->no_prob0);
+        return calc.edgeBetween(*c->recs[i], *c->recs[j]) ? 1 : 0;
+    } catch (const std::exception& e) {
+        c->err = e.what();
+        return -1;
+    }
+#else
+    (void)p; (void)i; (void)j;
+    return -1;
+#endif
 }
 
 }  // extern "C"

@@ -1,0 +1,85 @@
+"""GPU: the reference-side binding (integration/GpuEdgeCalculator, compiled against the reference tree into
+oracle/_ref/libhcref_gpu.so and oracle/_ref/haploclique_gpu) driving the reference's own clique finders: whole-program
+parity -- same edges, same cliques, same super-reads, same FASTA as the unmodified reference on the same input."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from haploclique_b200 import synth
+from haploclique_b200.records import ReadBatch
+from oracle import pyref
+from tests import common
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(not pyref.gpu_adapter_available(), reason="oracle/_ref/libhcref_gpu.so not built")]
+
+
+def _same_batch(a: ReadBatch, b: ReadBatch):
+    assert a.n == b.n
+    for f in ReadBatch._FIELDS:
+        assert (getattr(a, f) == getattr(b, f)).all(), f
+    assert a.names == b.names
+
+
+@pytest.mark.parametrize("use_bk", [False, True])
+def test_clique_rounds_with_gpu_calculator_equal_the_reference(use_bk):
+    # the reference's cram test input (arabis, 1104 paired records) and parameters, all rounds until convergence
+    b = common.load_batch("arabis_records.npz")
+    params = dict(common.WEAK, noProb0=True)
+    ref, gpu = pyref.Reference(gpu_adapter=True), pyref.Reference(gpu_adapter=True)
+    for R in (ref, gpu):
+        R.add_batch(b)
+        R.set_params(**params)
+    ct_r = ct_g = 0
+    sd_r = sd_g = 1.0
+    rounds = []
+    for it in range(6):
+        n_r, ct_r, e_r, conv_r, sd_r = ref.iterate(ct_r, sd_r, use_bk=use_bk, filter_singletons=True, significance=4.0)
+        n_g, ct_g, e_g, conv_g, sd_g, adj_edges = gpu.iterate_gpu(ct_g, sd_g, use_bk=use_bk, filter_singletons=True, significance=4.0)
+        rounds.append((n_r, e_r))
+        assert (n_g, e_g, conv_g) == (n_r, e_r, conv_r), "round %d" % it
+        assert sd_g == sd_r
+        if not use_bk:
+            assert adj_edges == e_r                  # CLEVER asks about every earlier read: its count = the adjacency's
+        _same_batch(ref.to_batch(), gpu.to_batch())  # the next round's super-reads
+        if conv_r:
+            break
+    if not use_bk:
+        assert rounds[0] == (447, 153685) and rounds[1][1] == 48675     # 1104 -> 447 -> 42 -> 2
+
+
+def test_unit_expectations_through_the_adapter(golden):
+    b = common.load_batch("unit_fixtures.npz")
+    R = pyref.Reference(gpu_adapter=True)
+    R.add_batch(b)
+    R.set_params(maxPosition=20000)
+    for name, case in golden["unit2"].items():
+        assert R.edge_gpu(case["ap1"], case["ap2"]) == case["expected"] == R.edge(case["ap1"], case["ap2"]), name
+
+
+@pytest.mark.parametrize("finder", ["clever", "bronkerbosch"])
+def test_cli_fasta_identical(tmp_path, finder):
+    if not (os.path.exists(pyref.CLI_REF) and os.path.exists(pyref.CLI_GPU)):
+        pytest.skip("CLI binaries not built")
+    # a synthetic BAM written with the reference's vendored BamWriter, then both CLIs on it
+    q = synth.quasispecies(300, genome_len=1200, seed=9, indel_err=1e-3, clip_frac=0.05)
+    W = pyref.Reference()
+    bam = str(tmp_path / "reads.bam")
+    W.bam_writer_open(bam, "ref", 1300)
+    W.add_batch(q)
+    W.bam_writer_close()
+    # default cutoffs (the weak cram-test ones make CLEVER itself run for minutes on this input); 7 rounds, ~2 s on CPU
+    flags = ["--no_prob0", "--no_singletons", "--significance=4"]
+    outs = {}
+    for tag, exe in (("ref", pyref.CLI_REF), ("gpu", pyref.CLI_GPU)):
+        d = tmp_path / tag
+        d.mkdir()
+        cmd = [exe] + ([finder] if finder == "bronkerbosch" else []) + flags + [bam]
+        r = subprocess.run(cmd, cwd=str(d), capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-500:]
+        outs[tag] = (open(d / "quasispecies.fasta", "rb").read(),
+                     [ln for ln in r.stdout.splitlines() if "edges:" in ln or ln.startswith("final")])
+    assert outs["ref"][0] == outs["gpu"][0] and len(outs["ref"][0]) > 0
+    assert outs["ref"][1] == outs["gpu"][1]
