@@ -29,10 +29,10 @@ enum { SLOT_OVL0 = 3, SLOT_OVL1 = 7, SLOT_OVL2 = 11, SLOT_FINAL = 12 };
 #define TILE_MOP(op, x, y, a, b) ((uint32_t)(op) | ((uint32_t)(x) << 4) | ((uint32_t)(y) << 5) | ((uint32_t)(a) << 6) | ((uint32_t)(b) << 10))
 
 #ifndef HC_TILE_WARPS
-#define HC_TILE_WARPS 16
+#define HC_TILE_WARPS 24
 #endif
 #ifndef HC_TILE_MINBLOCKS
-#define HC_TILE_MINBLOCKS 2
+#define HC_TILE_MINBLOCKS 1
 #endif
 constexpr int kWarps = HC_TILE_WARPS;
 constexpr int kThreads = kWarps * 32;
@@ -377,6 +377,8 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
     for (int k = tid; k < 2 * K * K; k += kThreads) Tsm[k] = a.P.table[k];
     for (int k = tid; k < TP_COUNT * TP_WORDS; k += kThreads) progsm[k] = a.prog[k];
     if (tid < 8) cstat[tid] = 0ull;
+    unsigned a_total = 0, a_scored = 0, a_walked = 0, a_edges = 0, a_undef = 0;   // per-lane totals, reduced once at the end
+    unsigned long long a_cc = 0, a_tc = 0;
     if (lane == 0) {
         mbar_init(&bars[warp * 2 + 0], 1);
         mbar_init(&bars[warp * 2 + 1], 1);
@@ -461,7 +463,6 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
             const int j = jmine;
             const bool active = j >= 0 && j < i;
             const bool covers = active && !(hA[14] < hB[13 * 32] || hB[14 * 32] < hA[13]);        // :1252
-            const unsigned n_total = __popc(__ballot_sync(FULL, active));
             if (__any_sync(FULL, covers)) {                         // some column read of the block reaches this row
                 const int rel = j - infA.col0;                      // column inside the row's band (>= 0 whenever covers)
                 int status = HC_ST_REJECT_COV;
@@ -475,17 +476,26 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
                 Lane L;
                 L.ref = 0; L.cc = 0; L.tc = 0; L.probM = 1.0; L.curs = 0ull; L.gap = false; L.undef = false;
                 int shape = 0;
-                const uint32_t* pg = progsm + pid * TP_WORDS;
-#pragma unroll 1
-                for (int s = 0; s < 3; ++s) {
-                    cheap(a, hA, hB, i, j, pg[s * 4 + 0], L, shape);
-                    cheap(a, hA, hB, i, j, pg[s * 4 + 1], L, shape);
-                    cheap(a, hA, hB, i, j, pg[s * 4 + 2], L, shape);
+                if (__all_sync(FULL, pid == TP_SINGLE00 || pid == TP_NOP)) {
+                    // the common case, checkGapsSingle on segments 1/1 for every lane: straight-line code
+                    const bool mine = pid == TP_SINGLE00;
+                    if (mine) cheap(a, hA, hB, i, j, TILE_MOP(M_SPRE, 0, 0, 0, 0), L, shape);
                     __syncwarp();
-                    const uint32_t mo = pg[s * 4 + 3];
-                    if (__any_sync(FULL, (mo & 15u) != M_NOP)) overlap(a, hA, hB, opsA, opsB, Tb, mo, L, shape);
+                    overlap(a, hA, hB, opsA, opsB, Tb, mine ? TILE_MOP(M_SOVL, 0, 0, 0, 0) : 0u, L, shape);
+                    if (mine) cheap(a, hA, hB, i, j, TILE_MOP(M_SPOST, 0, 0, 0, 0), L, shape);
+                } else {
+                    const uint32_t* pg = progsm + pid * TP_WORDS;
+#pragma unroll 1
+                    for (int s = 0; s < 3; ++s) {
+                        cheap(a, hA, hB, i, j, pg[s * 4 + 0], L, shape);
+                        cheap(a, hA, hB, i, j, pg[s * 4 + 1], L, shape);
+                        cheap(a, hA, hB, i, j, pg[s * 4 + 2], L, shape);
+                        __syncwarp();
+                        const uint32_t mo = pg[s * 4 + 3];
+                        if (__any_sync(FULL, (mo & 15u) != M_NOP)) overlap(a, hA, hB, opsA, opsB, Tb, mo, L, shape);
+                    }
+                    cheap(a, hA, hB, i, j, pg[SLOT_FINAL], L, shape);
                 }
-                cheap(a, hA, hB, i, j, pg[SLOT_FINAL], L, shape);
                 __syncwarp();
                 // ---- similarityCriterion (:1107-1141)
                 double prob0 = 0.0, score = __longlong_as_double(0x7ff8000000000000ll), cutoff = 0.0;
@@ -512,7 +522,6 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
                         }
                     }
                 }
-                const unsigned bits = __ballot_sync(FULL, edge);
                 if (edge) atomicOr(&a.adj[infA.word_off + (rel >> 5)], 1u << (rel & 31));
                 if (a.detail != nullptr && active && rel >= 0) {
                     hc_pair_result r;
@@ -530,25 +539,24 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
                     }
                 }
                 const bool walked = status == HC_ST_WALKED;
-                const unsigned n_scored = __popc(__ballot_sync(FULL, active && status != HC_ST_REJECT_COV));
-                const unsigned n_walked = __popc(__ballot_sync(FULL, walked));
-                const unsigned n_undef = __popc(__ballot_sync(FULL, status == HC_ST_UNDEFINED));
-                const unsigned s_cc = __reduce_add_sync(FULL, walked ? (unsigned)L.cc : 0u);
-                const unsigned s_tc = __reduce_add_sync(FULL, walked ? (unsigned)L.tc : 0u);
-                if (lane == 0) {
-                    atomicAdd(&cstat[0], (unsigned long long)n_total);
-                    atomicAdd(&cstat[1], (unsigned long long)n_scored);
-                    atomicAdd(&cstat[2], (unsigned long long)n_walked);
-                    atomicAdd(&cstat[3], (unsigned long long)__popc(bits));
-                    atomicAdd(&cstat[4], (unsigned long long)s_cc);
-                    atomicAdd(&cstat[5], (unsigned long long)s_tc);
-                    atomicAdd(&cstat[6], (unsigned long long)n_undef);
-                }
-            } else if (lane == 0 && n_total) {
-                atomicAdd(&cstat[0], (unsigned long long)n_total);
+                a_scored += (active && status != HC_ST_REJECT_COV) ? 1u : 0u;
+                a_walked += walked ? 1u : 0u;
+                a_edges += edge ? 1u : 0u;
+                a_undef += status == HC_ST_UNDEFINED ? 1u : 0u;
+                if (walked) { a_cc += (unsigned)L.cc; a_tc += (unsigned)L.tc; }
             }
+            a_total += active ? 1u : 0u;
             __syncwarp();
             rowA = rowB; infA = infB; rowB = rowC; infB = infC; kb ^= 1;
+        }
+    }
+    {
+        const unsigned long long v[7] = {a_total, a_scored, a_walked, a_edges, a_cc, a_tc, a_undef};
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            unsigned long long x = v[k];
+            for (int d = 16; d > 0; d >>= 1) x += __shfl_down_sync(FULL, x, d);
+            if (lane == 0 && x) atomicAdd(&cstat[k], x);
         }
     }
     __syncthreads();
