@@ -148,7 +148,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="auto", choices=["auto", "C2", "C3", "C4"])
     ap.add_argument("--n-frag", type=int, default=0, help="override the fragment count (debugging only)")
-    ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "tiled"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "tiled", "tiled2"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -197,7 +197,7 @@ def main():
     max_position = cfg["genome_len"] + 2 * HALO
 
     calc = edge.NewEdgeCalculator(maxPosition=max_position, device=local_rank, **PARAMS)
-    calc.set_kernel({"auto": edge.KERNEL_AUTO, "generic": edge.KERNEL_GENERIC, "tiled": edge.KERNEL_TILED}[args.kernel])
+    calc.set_kernel({"auto": edge.KERNEL_AUTO, "generic": edge.KERNEL_GENERIC, "tiled": edge.KERNEL_TILED, "tiled2": edge.KERNEL_TILED2}[args.kernel])
     t0 = time.perf_counter()
     packed = edge.PackedBatch(local)
     pack_s = time.perf_counter() - t0
@@ -246,7 +246,7 @@ def main():
     barrier()
     sampler.stop_flag = True
     sampler.join(timeout=2)
-    kernel_used = {0: "none", 1: "generic", 2: "tiled"}[calc.last_kernel()]
+    kernel_used = {0: "none", 1: "generic", 2: "tiled", 3: "tiled2"}[calc.last_kernel()]
     lds_gbs, dmul_s = edge.measure_peaks(local_rank) if rank == 0 else (0.0, 0.0)
 
     # whole-job numbers: units of all ranks / max-over-ranks time

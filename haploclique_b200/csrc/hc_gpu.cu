@@ -458,6 +458,7 @@ __global__ void __launch_bounds__(256) score_band_kernel(DevParams P, const hc_r
 }
 
 #include "hc_tile.cuh"
+#include "hc_tile2.cuh"
 
 }  // namespace
 
@@ -489,6 +490,8 @@ struct hc_ctx {
     void* d_flush = nullptr; size_t flush_bytes = 0;
     // tiled band kernel (hc_tile.cuh)
     uint32_t* d_aux = nullptr; uint16_t* d_col2op = nullptr; uint32_t* d_tprog = nullptr;
+    // second-generation tiled kernel (hc_tile2.cuh): row / column operand formats and the 9-row split table
+    uint32_t* d_opsA = nullptr; uint16_t* d_opsF = nullptr; uint32_t* d_tab7 = nullptr;
     int4* d_items = nullptr; size_t items_cap = 0; int* d_item_counter = nullptr;
     hc_pair_result* d_detail = nullptr; size_t detail_cap = 0;
     int kernel_mode = HC_KERNEL_AUTO;
@@ -629,6 +632,45 @@ bool tile_eligible(const hc_ctx* c) {
     return tile_geometry(c).smem <= c->smem_optin;
 }
 
+// Second-generation tiled kernel: 9-row table (2304*K bytes split, 72*K*K bytes as doubles), 32-bit row records. The warp count shrinks
+// (24 -> 8) until the CTA fits; below 8 warps the first-generation kernel or the generic walker takes over.
+struct Tile2Geom { int maxw, abuf_bytes, nwarps; size_t smem; };
+
+// Table layout of the second-generation tiled kernel: split low/high words for K <= split_max_k() codes, doubles above.
+int split_max_k() {
+    static const int v = [] { const char* e = std::getenv("HC_T2_SPLIT_MAXK"); return e ? std::atoi(e) : tile2::kSplitMaxK; }();
+    return std::min(v, 32);
+}
+uint32_t tile2_row_bytes(int K) { return K <= split_max_k() ? 256u : 8u * (uint32_t)K; }
+uint32_t tile2_entry_bytes(int K) { return K <= split_max_k() ? 4u : 8u; }
+size_t tile2_table_words(int K) { return (size_t)tile2::kRows * K * tile2_row_bytes(K) / 4; }
+
+Tile2Geom tile2_geometry(const hc_ctx* c) {
+    Tile2Geom g;
+    g.maxw = (c->max_ops + 1) / 2 + 6;
+    g.abuf_bytes = ((c->max_ops * 4 + 15) & ~15) + 32;
+    g.nwarps = 0;
+    g.smem = 0;
+    for (int w = tile2::kMaxWarps; w >= 8; w -= 4) {
+        size_t o = 0;
+        o += ((size_t)tile2_table_words(c->K) * 4 + 15) & ~(size_t)15;
+        o += (size_t)tile::TP_COUNT * tile::TP_WORDS * 4;
+        o += 16 * 32 * 4;
+        o += (size_t)g.maxw * 128;
+        o += (size_t)w * 2 * (64 + g.abuf_bytes);
+        o += (size_t)w * 2 * 8;
+        o += 8 * 8;
+        o += 16;
+        if (o <= c->smem_optin) { g.nwarps = w; g.smem = o; break; }
+    }
+    return g;
+}
+
+bool tile2_eligible(const hc_ctx* c) {
+    if (c->d_simpson != nullptr || c->d_opsA == nullptr) return false;
+    return tile2_geometry(c).nwarps > 0;
+}
+
 // Work items of the tiled kernel for rows [row_begin,row_end).
 // Columns (the earlier reads j) are taken in windows of W consecutive reads; inside a window they are sorted by
 // (single/paired, last covered position) and cut into blocks of 32. For a later row read i the length of the
@@ -762,6 +804,7 @@ void hc_destroy(hc_ctx* c) {
     cudaFree(c->d_col0); cudaFree(c->d_word_off); cudaFree(c->d_adj); cudaFree(c->d_stats); cudaFree(c->d_amb);
     cudaFree(c->d_pi); cudaFree(c->d_pj); cudaFree(c->d_res); cudaFree(c->d_flush);
     cudaFree(c->d_aux); cudaFree(c->d_col2op); cudaFree(c->d_tprog); cudaFree(c->d_items); cudaFree(c->d_item_counter);
+    cudaFree(c->d_opsA); cudaFree(c->d_opsF); cudaFree(c->d_tab7);
     cudaFree(c->d_detail); cudaFree(c->d_colidx);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -808,7 +851,9 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     CU_TRY(c, cudaSetDevice(c->device));
     CU_TRY(c, cudaStreamSynchronize(c->stream));
     cudaFree(c->d_hdr); cudaFree(c->d_ops); cudaFree(c->d_table); cudaFree(c->d_ladder); cudaFree(c->d_aux); cudaFree(c->d_col2op);
+    cudaFree(c->d_opsA); cudaFree(c->d_opsF); cudaFree(c->d_tab7);
     c->d_hdr = nullptr; c->d_ops = nullptr; c->d_table = nullptr; c->d_ladder = nullptr; c->d_aux = nullptr; c->d_col2op = nullptr;
+    c->d_opsA = nullptr; c->d_opsF = nullptr; c->d_tab7 = nullptr;
     c->items_begin = c->items_end = -1;
     c->n_reads = p->n_reads;
     c->K = std::max(p->n_qual_codes, 1);
@@ -840,6 +885,36 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     CU_TRY(c, cudaMalloc((void**)&c->d_col2op, ((size_t)p->n_ops_total + 64) * sizeof(uint16_t)));
     if (p->n_reads > 0) {
         tile::build_aux_kernel<<<(2 * p->n_reads + 127) / 128, 128, 0, c->stream>>>(c->d_hdr, c->d_ops, p->n_reads, c->d_aux, c->d_col2op);
+        CU_TRY(c, cudaGetLastError());
+    }
+    // operand formats of the second-generation tiled kernel (hc_tile2.cuh): A-words, B-records, and the table as
+    // 9 rows per first quality (un x4, EQ, un x4), low words then high words. Skipped when the table alone
+    // would not fit a CTA's shared memory (the kernel is then not eligible).
+    std::vector<uint32_t> tab7;
+    if (tile2_table_words(K) * 4 + 65536 <= c->smem_optin && c->d_simpson == nullptr) {
+        tab7.assign(tile2_table_words(K), 0u);
+        const bool split = K <= split_max_k();
+        for (int a = 0; a < K; ++a)
+            for (int r = 0; r < tile2::kRows; ++r)
+                for (int b = 0; b < K; ++b) {
+                    const double v = tab[(r == 4 ? 0 : (size_t)K * K) + (size_t)a * K + b];
+                    uint64_t bits;
+                    std::memcpy(&bits, &v, 8);
+                    const size_t row = (size_t)a * tile2::kRows + r;
+                    if (split) {                       // 32 low words, then 32 high words
+                        tab7[row * 64 + b] = (uint32_t)bits;
+                        tab7[row * 64 + 32 + b] = (uint32_t)(bits >> 32);
+                    } else {                           // K doubles
+                        tab7[(row * K + b) * 2] = (uint32_t)bits;
+                        tab7[(row * K + b) * 2 + 1] = (uint32_t)(bits >> 32);
+                    }
+                }
+        const long long nrec = (long long)p->n_ops_total + 64;
+        CU_TRY(c, cudaMalloc((void**)&c->d_tab7, tab7.size() * sizeof(uint32_t)));
+        CU_TRY(c, cudaMemcpyAsync(c->d_tab7, tab7.data(), tab7.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+        CU_TRY(c, cudaMalloc((void**)&c->d_opsA, (size_t)nrec * sizeof(uint32_t)));
+        CU_TRY(c, cudaMalloc((void**)&c->d_opsF, (size_t)nrec * sizeof(uint16_t)));
+        tile2::build_formats_kernel<<<(unsigned)((nrec + 255) / 256), 256, 0, c->stream>>>(c->d_ops, nrec, tile2_row_bytes(K), tile2_entry_bytes(K), c->d_opsA, c->d_opsF);
         CU_TRY(c, cudaGetLastError());
     }
     c->cov_first.resize(p->n_reads);
@@ -883,14 +958,16 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
     const int nrows = row_end - row_begin;
     const long long total = c->lay_off[nrows];
     if ((adj || detail) && n_words < total) { c->err = "hc_score_band: output buffer smaller than hc_band_layout's n_words"; return HC_E_INVALID; }
-    const bool can_tile = tile_eligible(c);
-    if (c->kernel_mode == HC_KERNEL_TILED && !can_tile) {
+    const bool can_tile1 = tile_eligible(c), can_tile2 = tile2_eligible(c);
+    if ((c->kernel_mode == HC_KERNEL_TILED && !can_tile1) || (c->kernel_mode == HC_KERNEL_TILED2 && !can_tile2)) {
         c->err = "hc_score_band: the tiled kernel was requested but this batch / parameter set is not eligible "
-                 "(allele-frequency map set, or the column tile does not fit shared memory)";
+                 "(allele-frequency map set, or the tables and the column tile do not fit shared memory)";
         return HC_E_STATE;
     }
-    const bool use_tile = can_tile && c->kernel_mode != HC_KERNEL_GENERIC;
-    if (detail && !use_tile) { c->err = "hc_score_band_detail: only the tiled kernel writes per-slot detail; use hc_score_pairs"; return HC_E_STATE; }
+    const bool use_tile2 = can_tile2 && (c->kernel_mode == HC_KERNEL_AUTO || c->kernel_mode == HC_KERNEL_TILED2);
+    const bool use_tile1 = !use_tile2 && can_tile1 && c->kernel_mode != HC_KERNEL_GENERIC && c->kernel_mode != HC_KERNEL_TILED2;
+    const bool use_tile = use_tile1 || use_tile2;
+    if (detail && !use_tile) { c->err = "hc_score_band_detail: only the tiled kernels write per-slot detail; use hc_score_pairs"; return HC_E_STATE; }
     int rc;
     size_t cap2 = c->rows_cap;
     if ((rc = grow(c, c->d_col0, c->rows_cap, (size_t)nrows + 1)) != HC_OK) return rc;
@@ -909,9 +986,19 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
     c->last_kernel = 0;
     if (use_tile && total > 0) {
         const TileGeom g = tile_geometry(c);
-        CU_TRY(c, cudaFuncSetAttribute(tile::score_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
+        const Tile2Geom g2 = tile2_geometry(c);
+        const size_t smem_bytes = use_tile2 ? g2.smem : g.smem;
+        const int threads = use_tile2 ? g2.nwarps * 32 : tile::kThreads;
         int per_sm = 0;
-        CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile::score_tile_kernel, tile::kThreads, g.smem));
+        const bool split = c->K <= split_max_k();
+        if (use_tile2) {
+            auto kern = split ? tile2::score_tile2_kernel<true> : tile2::score_tile2_kernel<false>;
+            CU_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+            CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem_bytes));
+        } else {
+            CU_TRY(c, cudaFuncSetAttribute(tile::score_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+            CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile::score_tile_kernel, threads, smem_bytes));
+        }
         if (per_sm < 1) { c->err = "hc_score_band: tiled kernel does not fit on an SM"; return HC_E_CUDA; }
         const int n_ctas = c->sm_count * per_sm;
         build_items(c, row_begin, row_end, n_ctas);
@@ -924,21 +1011,25 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
         // words of rows whose band holds no scored column block stay zero
         CU_TRY(c, cudaMemsetAsync(c->d_adj, 0, (size_t)total * sizeof(uint32_t), c->stream));
         if (detail) CU_TRY(c, cudaMemsetAsync(c->d_detail, 0, (size_t)total * 32 * sizeof(hc_pair_result), c->stream));
-        tile::Args a{};
+        tile2::Args2 a{};
         a.P = dev_params(c);
+        a.opsA = c->d_opsA; a.opsF = c->d_opsF; a.tab7 = c->d_tab7; a.tab_words = (int)tile2_table_words(c->K);
+        a.row_bytes = tile2_row_bytes(c->K); a.entry_bytes = tile2_entry_bytes(c->K);
         a.hdr = c->d_hdr; a.ops = c->d_ops; a.aux = c->d_aux; a.col2op = c->d_col2op; a.prog = c->d_tprog;
         a.n_reads = c->n_reads; a.row_begin = row_begin; a.col0 = c->d_col0; a.word_off = c->d_word_off;
         a.colidx = c->d_colidx; a.items = c->d_items; a.n_items = (int)n_items; a.item_counter = c->d_item_counter;
         a.adj = c->d_adj; a.stats = c->d_stats; a.amb = amb ? c->d_amb : nullptr; a.amb_cap = amb ? amb_cap : 0;
         a.detail = detail ? c->d_detail : nullptr;
-        a.maxw = g.maxw; a.abuf_bytes = g.abuf_bytes;
+        a.maxw = use_tile2 ? g2.maxw : g.maxw; a.abuf_bytes = use_tile2 ? g2.abuf_bytes : g.abuf_bytes;
         CU_TRY(c, cudaEventRecord(c->ev0, c->stream));
         if (n_items > 0) {
             const int blocks = (int)std::min<size_t>(n_items, (size_t)n_ctas);
-            tile::score_tile_kernel<<<blocks, tile::kThreads, g.smem, c->stream>>>(a);
+            if (use_tile2 && split) tile2::score_tile2_kernel<true><<<blocks, threads, smem_bytes, c->stream>>>(a);
+            else if (use_tile2) tile2::score_tile2_kernel<false><<<blocks, threads, smem_bytes, c->stream>>>(a);
+            else tile::score_tile_kernel<<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
             CU_TRY(c, cudaGetLastError());
             launches = 1;
-            c->last_kernel = HC_KERNEL_TILED;
+            c->last_kernel = use_tile2 ? HC_KERNEL_TILED2 : HC_KERNEL_TILED;
         }
         CU_TRY(c, cudaEventRecord(c->ev1, c->stream));
     } else {
@@ -990,7 +1081,7 @@ int hc_score_band_detail(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32_t
 }
 
 int hc_set_kernel(hc_ctx* c, int32_t mode) {
-    if (!c || mode < HC_KERNEL_AUTO || mode > HC_KERNEL_TILED) return HC_E_INVALID;
+    if (!c || mode < HC_KERNEL_AUTO || mode > HC_KERNEL_TILED2) return HC_E_INVALID;
     c->kernel_mode = mode;
     return HC_OK;
 }

@@ -177,9 +177,11 @@ def quasispecies_sharded(n_frag: int, chunk: int = 50_000, start_window=None, se
     return ReadBatch.concat_sorted(parts)
 
 
-def zoo(n_reads: int, genome_len: int = 400, seed: int = 1, max_seg: int = 120, clique_frac: float = 0.3) -> ReadBatch:
+def zoo(n_reads: int, genome_len: int = 400, seed: int = 1, max_seg: int = 120, clique_frac: float = 0.3,
+        wide_qual=(2, 94)) -> ReadBatch:
     """Small adversarial batch for parity tests: single/paired mix, many start ties, leading/trailing S and
-    H clips, insertions and deletions anywhere inside, N bases, wide quality range, 'Clique' names."""
+    H clips, insertions and deletions anywhere inside, N bases, wide quality range (a fifth of the segments draw
+    Phred values from `wide_qual`, the rest from 20..41), 'Clique' names."""
     from .records import AlignmentRecord
     rng = np.random.default_rng(seed)
     recs = []
@@ -200,7 +202,7 @@ def zoo(n_reads: int, genome_len: int = 400, seed: int = 1, max_seg: int = 120, 
         cig = lead_op * lead + b"".join(mid) + trail_op * trail
         nq = sum(1 for ch in cig if ch in b"MIS")
         seq = _BASES[rng.choice(5, nq, p=[0.245, 0.245, 0.245, 0.245, 0.02])].tobytes()
-        qual = (rng.integers(2, 94, nq) + 33).astype(np.uint8).tobytes() if rng.random() < 0.2 else \
+        qual = (rng.integers(wide_qual[0], wide_qual[1], nq) + 33).astype(np.uint8).tobytes() if rng.random() < 0.2 else \
             (rng.integers(20, 42, nq) + 33).astype(np.uint8).tobytes()
         return start_ext + lead, start_ext + ncol - trail - 1, cig, seq, qual
 

@@ -140,12 +140,15 @@ def test_setOverlapCliques_changes_the_decision():
 
 
 # ---- the tiled band kernel (shared-memory column tiles, TMA-fed rows): every band slot against the oracle ----
-def _tiled_detail_vs_oracle(b, kw, label):
+TILED_KERNELS = [pytest.param(edge.KERNEL_TILED, id="tiled"), pytest.param(edge.KERNEL_TILED2, id="tiled2")]
+
+
+def _tiled_detail_vs_oracle(b, kw, label, kernel=edge.KERNEL_TILED):
     calc = edge.NewEdgeCalculator(**kw)
     calc.upload(b)
-    calc.set_kernel(edge.KERNEL_TILED)
+    calc.set_kernel(kernel)
     adj, pi, pj, det = calc.score_band_detail()
-    assert calc.last_kernel() == edge.KERNEL_TILED or b.n < 2
+    assert calc.last_kernel() == kernel or b.n < 2
     O = pyoracle.Oracle(b, **kw)
     orc = O.pairs(pi, pj)
     common.assert_pairs_equal(det, orc, label)
@@ -169,45 +172,62 @@ def _tiled_detail_vs_oracle(b, kw, label):
     return det, orc
 
 
+@pytest.mark.parametrize("kernel", TILED_KERNELS)
 @pytest.mark.parametrize("label", sorted(common.DATASETS))
-def test_tiled_kernel_matches_oracle_on_golden_sets(golden, label):
+def test_tiled_kernel_matches_oracle_on_golden_sets(golden, label, kernel):
     g = golden[label]
     b = common.load_batch(common.DATASETS[label])
     kw = common.calc_kwargs(g["params"], g["max_position"])
     calc = edge.NewEdgeCalculator(**kw)
     calc.upload(b)
-    adj = calc.score_band()
-    if calc.last_kernel() != edge.KERNEL_TILED:
-        pytest.skip("batch not eligible for the tiled kernel (longest read does not fit a shared-memory tile)")
-    _tiled_detail_vs_oracle(b, kw, label)
+    calc.set_kernel(kernel)
+    try:
+        adj = calc.score_band()
+    except edge.HcError:
+        pytest.skip("batch not eligible for this tiled kernel (tables + longest read do not fit a CTA's shared memory)")
+    assert calc.last_kernel() == kernel
+    _tiled_detail_vs_oracle(b, kw, label, kernel)
     assert adj.count() == g["edges"]
 
 
+def test_auto_prefers_the_second_generation_tiled_kernel():
+    b = synth.quasispecies(300, genome_len=1500, seed=2)
+    calc = edge.NewEdgeCalculator(noProb0=True, maxPosition=b.max_position())
+    calc.scoreBatch(b)
+    assert calc.last_kernel() == edge.KERNEL_TILED2
+
+
+@pytest.mark.parametrize("kernel", TILED_KERNELS)
 @pytest.mark.parametrize("seed", range(6))
-def test_tiled_kernel_zoo(seed):
-    b = synth.zoo(200, seed=100 + seed)
+def test_tiled_kernel_zoo(seed, kernel):
+    # 92 quality codes for the first tiled kernel; the second one takes 22 codes (split-word table) on even seeds
+    # and 44 codes (table of doubles) on odd seeds -- its 7-row table of 92 codes would not fit shared memory
+    wide = (2, 94) if kernel == edge.KERNEL_TILED else ((20, 42) if seed % 2 == 0 else (2, 46))
+    b = synth.zoo(200, seed=100 + seed, wide_qual=wide)
     kw = dict(noProb0=bool(seed % 2), edge_quasi_cutoff_single=0.8, edge_quasi_cutoff_mixed=0.85,
               edge_quasi_cutoff=0.9, overlap=0.3, overlap_single=0.2, maxPosition=b.max_position())
-    det, orc = _tiled_detail_vs_oracle(b, kw, "tiled-zoo%d" % seed)
+    det, orc = _tiled_detail_vs_oracle(b, kw, "tiled-zoo%d" % seed, kernel)
     assert set(np.unique(orc["layout"])) >= {100, 200, 300, 400}
 
 
-def test_tiled_kernel_quasispecies_with_indels_and_clips():
+@pytest.mark.parametrize("kernel", TILED_KERNELS)
+def test_tiled_kernel_quasispecies_with_indels_and_clips(kernel):
     b = synth.quasispecies(1500, genome_len=2500, seed=21, indel_err=3e-3, clip_frac=0.15)
     kw = dict(noProb0=True, maxPosition=b.max_position(), edge_quasi_cutoff_single=0.9)
-    det, orc = _tiled_detail_vs_oracle(b, kw, "tiled-quasi")
+    det, orc = _tiled_detail_vs_oracle(b, kw, "tiled-quasi", kernel)
     assert int(orc["edge"].sum()) > 1000 and int(orc["gap"].sum()) > 100
     kw["noProb0"] = False
-    _tiled_detail_vs_oracle(b, kw, "tiled-quasi-prob0")
+    _tiled_detail_vs_oracle(b, kw, "tiled-quasi-prob0", kernel)
 
 
-def test_tiled_kernel_row_windows_concatenate():
+@pytest.mark.parametrize("kernel", TILED_KERNELS)
+def test_tiled_kernel_row_windows_concatenate(kernel):
     # sharding by row windows (what N>1 ranks do): the windows' words are the full run's words
     b = synth.quasispecies(900, genome_len=2000, seed=5)
     kw = dict(noProb0=True, maxPosition=b.max_position())
     calc = edge.NewEdgeCalculator(**kw)
     calc.upload(b)
-    calc.set_kernel(edge.KERNEL_TILED)
+    calc.set_kernel(kernel)
     full = calc.score_band()
     parts = [calc.score_band(r0, r1) for r0, r1 in ((0, 301), (301, 650), (650, 900))]
     assert sum(p.count() for p in parts) == full.count()
