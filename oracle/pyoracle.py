@@ -35,10 +35,20 @@ RESULT_DTYPE = np.dtype([("status", np.int32), ("edge", np.int32), ("gap", np.in
                          ("score", np.float64)], align=True)
 
 
+class _QuasiParams(C.Structure):
+    _fields_ = [("cutoff_cliques", C.c_double), ("cutoff_mixed", C.c_double), ("cutoff_single", C.c_double),
+                ("overlap_cliques", C.c_double), ("overlap_single", C.c_double), ("frameshift_merge", C.c_int32),
+                ("simpson_len", C.c_int32), ("simpson", C.c_void_p)]
+
+
+QUASI_RESULT_DTYPE = np.dtype([("status", np.int32), ("edge", np.int32), ("n_single", np.int32), ("pad", np.int32),
+                               ("q", np.float64), ("cutoff", np.float64)], align=True)
+
+
 def build(force: bool = False) -> str:
     """Compiles the C restatement (gcc). Building the checker is not using it."""
-    src = os.path.join(_HERE, "edge_oracle.c")
-    if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("edge_oracle.c", "quasi_oracle.c", "orc_types.h")]
+    if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-s", "-C", _HERE, "oracle"])
     return _LIB
 
@@ -54,6 +64,7 @@ def lib():
         _lib.orc_edge_all.restype = C.c_int64
         assert _lib.orc_sizeof_read() == C.sizeof(_Read)
         assert _lib.orc_sizeof_result() == RESULT_DTYPE.itemsize
+        assert _lib.qorc_sizeof_result() == QUASI_RESULT_DTYPE.itemsize
     return _lib
 
 
@@ -123,6 +134,26 @@ class Oracle:
         e = np.zeros(npairs, np.uint8)
         edges = lib().orc_edge_all(self._reads, n, C.byref(self._par), None, e.ctypes.data_as(C.c_void_p))
         return int(edges), e
+
+
+class QuasiOracle(Oracle):
+    """QuasiOracle(batch, **QuasispeciesEdgeCalculator params): quasi_oracle.c, the restatement of the reference's older
+    scorer (QuasispeciesEdgeCalculator.cpp:55-426). Parameter names follow its constructor (QuasispeciesEdgeCalculator.h:57)."""
+
+    def __init__(self, batch, edge_quasi_cutoff=0.99, overlap=0.9, frameshift_merge=False, simpson_map=None,
+                 edge_quasi_cutoff_single=0.95, overlap_single=0.6, edge_quasi_cutoff_mixed=0.97, maxPosition=None):
+        super().__init__(batch, maxPosition=maxPosition, simpson_map=simpson_map)
+        self._qpar = _QuasiParams(edge_quasi_cutoff, edge_quasi_cutoff_mixed, edge_quasi_cutoff_single, overlap,
+                                  overlap_single, 1 if frameshift_merge else 0, self._simpson.shape[0],
+                                  self._simpson.ctypes.data)
+
+    def pairs(self, pi, pj) -> np.ndarray:
+        pi = np.ascontiguousarray(pi, np.int32)
+        pj = np.ascontiguousarray(pj, np.int32)
+        out = np.zeros(pi.shape[0], QUASI_RESULT_DTYPE)
+        lib().qorc_edge_pairs(self._reads, pi.ctypes.data_as(C.c_void_p), pj.ctypes.data_as(C.c_void_p),
+                              C.c_int64(pi.shape[0]), C.byref(self._qpar), out.ctypes.data_as(C.c_void_p))
+        return out
 
 
 def tri_pairs(n: int):

@@ -9,6 +9,18 @@
 // The reference CLI translation unit is included whole (the reference's own unit test does the
 // same: test/unit/unit1.cpp:11-12), which gives us readBamFile (src/haploclique.cpp:143) and
 // the CLI entry as HaploMain.
+// QuasispeciesEdgeCalculator::computeOverlap is private; the checker wants its value, not only the boolean. The class
+// body alone is read with `private` spelled `public` (its own includes come first, so nothing else is affected;
+// access specifiers do not change the layout of this class, which has a single access section of data members).
+#include <map>
+#include <set>
+#include <string>
+#include "AlignmentRecord.h"
+#include "EdgeCalculator.h"
+#define private public
+#include "QuasispeciesEdgeCalculator.h"
+#undef private
+
 #define main HaploMain
 #include "haploclique.cpp"
 #undef main
@@ -276,6 +288,30 @@ int hcref_pair_detail(void* p, int i, int j, int* gap, int* cc, int* tc, double*
     bool g = c->calc->checkGapsCigar(*c->recs[i], *c->recs[j], pm, p0, ccv, tcv);
     *gap = g; *cc = ccv; *tc = tcv; *probM = pm; *prob0 = p0;
     return 1;
+}
+
+// QuasispeciesEdgeCalculator (src/QuasispeciesEdgeCalculator.cpp): q = computeOverlap(records[pi], records[pj], cutoff)
+// with the cutoff edgeBetween picks from the two names (:59-66), and the boolean edgeBetween returns (:69).
+// simpson: the calculator's map<int,double> (its constructor copies it, :42).
+long hcref_quasi_pairs(void* p, const int* pi, const int* pj, long npairs, double cut_cliques, double ov_cliques,
+                       int frameshift, const int* simpson_pos, const double* simpson_val, int n_simpson, double cut_single,
+                       double ov_single, double cut_mixed, double* q_out, unsigned char* edge_out) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    std::map<int, double> simpson;
+    for (int i = 0; i < n_simpson; ++i) simpson[simpson_pos[i]] = simpson_val[i];
+    QuasispeciesEdgeCalculator calc(0.9, cut_cliques, ov_cliques, frameshift != 0, simpson, cut_single, ov_single, cut_mixed);
+    long edges = 0;
+    for (long k = 0; k < npairs; ++k) {
+        const AlignmentRecord& a = *c->recs[pi[k]];
+        const AlignmentRecord& b = *c->recs[pj[k]];
+        const bool ca = a.getName().find("Clique") != std::string::npos, cb = b.getName().find("Clique") != std::string::npos;
+        const double cutoff = (ca && cb) ? cut_cliques : ((ca || cb) ? cut_mixed : cut_single);
+        if (q_out) q_out[k] = calc.computeOverlap(a, b, cutoff);
+        const bool e = calc.edgeBetween(a, b);
+        if (edge_out) edge_out[k] = e;
+        edges += e;
+    }
+    return edges;
 }
 
 // All ordered pairs (i = later arrival, j < i), CLEVER's order (src/CLEVER.cpp:218-232).
