@@ -459,6 +459,7 @@ __global__ void __launch_bounds__(256) score_band_kernel(DevParams P, const hc_r
 
 #include "hc_tile.cuh"
 #include "hc_tile2.cuh"
+#include "hc_quasi.cuh"
 
 }  // namespace
 
@@ -490,7 +491,10 @@ struct hc_ctx {
     void* d_flush = nullptr; size_t flush_bytes = 0;
     // tiled band kernel (hc_tile.cuh)
     uint32_t* d_aux = nullptr; uint16_t* d_col2op = nullptr; uint32_t* d_tprog = nullptr;
-    // second-generation tiled kernel (hc_tile2.cuh): row / column operand formats and the 9-row split table
+    // QuasispeciesEdgeCalculator path (hc_quasi.cuh): host-tabulated log terms per (base1, base2, code1, code2), ln of the map
+    uint8_t qual_chars[128] = {0};
+    double* d_logsum = nullptr; double* d_simpson_ln = nullptr; hc_quasi_result* d_qres = nullptr; size_t qres_cap = 0;
+    // second-generation tiled kernel (hc_tile2.cuh): row / column operand formats and the 9-row table
     uint32_t* d_opsA = nullptr; uint16_t* d_opsF = nullptr; uint32_t* d_tab7 = nullptr;
     int4* d_items = nullptr; size_t items_cap = 0; int* d_item_counter = nullptr;
     hc_pair_result* d_detail = nullptr; size_t detail_cap = 0;
@@ -805,6 +809,7 @@ void hc_destroy(hc_ctx* c) {
     cudaFree(c->d_pi); cudaFree(c->d_pj); cudaFree(c->d_res); cudaFree(c->d_flush);
     cudaFree(c->d_aux); cudaFree(c->d_col2op); cudaFree(c->d_tprog); cudaFree(c->d_items); cudaFree(c->d_item_counter);
     cudaFree(c->d_opsA); cudaFree(c->d_opsF); cudaFree(c->d_tab7);
+    cudaFree(c->d_logsum); cudaFree(c->d_simpson_ln); cudaFree(c->d_qres);
     cudaFree(c->d_detail); cudaFree(c->d_colidx);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -851,7 +856,9 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     CU_TRY(c, cudaSetDevice(c->device));
     CU_TRY(c, cudaStreamSynchronize(c->stream));
     cudaFree(c->d_hdr); cudaFree(c->d_ops); cudaFree(c->d_table); cudaFree(c->d_ladder); cudaFree(c->d_aux); cudaFree(c->d_col2op);
-    cudaFree(c->d_opsA); cudaFree(c->d_opsF); cudaFree(c->d_tab7);
+    cudaFree(c->d_opsA); cudaFree(c->d_opsF); cudaFree(c->d_tab7); cudaFree(c->d_logsum);
+    c->d_logsum = nullptr;
+    std::memcpy(c->qual_chars, p->qual_chars, sizeof(c->qual_chars));
     c->d_hdr = nullptr; c->d_ops = nullptr; c->d_table = nullptr; c->d_ladder = nullptr; c->d_aux = nullptr; c->d_col2op = nullptr;
     c->d_opsA = nullptr; c->d_opsF = nullptr; c->d_tab7 = nullptr;
     c->items_begin = c->items_end = -1;
@@ -1078,6 +1085,122 @@ int hc_score_band_detail(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32_t
                          hc_band_stats* stats) {
     if (!detail) { if (c) c->err = "hc_score_band_detail: null detail buffer"; return HC_E_INVALID; }
     return score_band_impl(c, row_begin, row_end, adj, n_words, nullptr, 0, stats, detail);
+}
+
+// ---- QuasispeciesEdgeCalculator path (hc_quasi.cuh) ----------------------------------------------------
+static int quasi_prepare(hc_ctx* c, const hc_quasi_params* qp, quasi::QParams& P) {
+    if (!c->d_hdr) { c->err = "hc_quasi_*: no batch uploaded"; return HC_E_STATE; }
+    if (!(qp->edge_quasi_cutoff_cliques > 0 && qp->edge_quasi_cutoff_mixed > 0 && qp->edge_quasi_cutoff_single > 0)) {
+        c->err = "hc_quasi_*: cutoffs must be > 0";
+        return HC_E_INVALID;
+    }
+    CU_TRY(c, cudaSetDevice(c->device));
+    const int K = c->K;
+    if (!c->d_logsum) {
+        // log(sum) of src/QuasispeciesEdgeCalculator.cpp:307-324 for every (base1, base2, quality1, quality2), the
+        // reference's expression, summation order and libm
+        std::vector<double> qc(K), anti(K);
+        for (int a = 0; a < K; ++a) {
+            const char qual = (char)c->qual_chars[a];
+            qc[a] = 1 - std::pow(10, -(qual - 33) / 10.0);                 // ShortDnaSequence::qualityCorrect (:117-119)
+            anti[a] = (1.0 - qc[a]) / 3.0;
+        }
+        std::vector<double> tab((size_t)25 * K * K);
+        for (int b1 = 0; b1 < 5; ++b1)
+            for (int b2 = 0; b2 < 5; ++b2)
+                for (int a = 0; a < K; ++a)
+                    for (int b = 0; b < K; ++b) {
+                        double sum = 0.0;
+                        for (int x = 0; x < 4; ++x) sum += ((b1 == x ? qc[a] : anti[a]) * (b2 == x ? qc[b] : anti[b]));
+                        tab[(((size_t)b1 * 5 + b2) * K + a) * K + b] = std::log(sum);
+                    }
+        CU_TRY(c, cudaMalloc((void**)&c->d_logsum, tab.size() * sizeof(double)));
+        CU_TRY(c, cudaMemcpy(c->d_logsum, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice));
+    }
+    if (!c->simpson_host.empty() && !c->d_simpson_ln) {
+        std::vector<double> ln(c->simpson_host.size(), 0.0);
+        for (size_t k = 0; k < ln.size(); ++k) if (c->simpson_host[k] != 0.0) ln[k] = std::log(c->simpson_host[k]);
+        CU_TRY(c, cudaMalloc((void**)&c->d_simpson_ln, ln.size() * sizeof(double)));
+        CU_TRY(c, cudaMemcpy(c->d_simpson_ln, ln.data(), ln.size() * sizeof(double), cudaMemcpyHostToDevice));
+    }
+    P.cutoff[0] = qp->edge_quasi_cutoff_cliques; P.cutoff[1] = qp->edge_quasi_cutoff_mixed; P.cutoff[2] = qp->edge_quasi_cutoff_single;
+    P.min_overlap[0] = qp->min_overlap_cliques; P.min_overlap[1] = qp->min_overlap_single;
+    P.amb_tol = qp->ambiguity_rel_tol > 0 ? qp->ambiguity_rel_tol : 1e-12;
+    P.logsum = c->d_logsum;
+    P.simpson_ln = c->d_simpson_ln;
+    P.simpson_len = (int)c->simpson_host.size();
+    P.K = K;
+    P.frameshift = qp->frameshift_merge;
+    return HC_OK;
+}
+
+int hc_quasi_score_pairs(hc_ctx* c, const hc_quasi_params* qp, const int32_t* pi, const int32_t* pj, int64_t npairs,
+                         hc_quasi_result* out) {
+    if (!c || !qp || npairs < 0 || (npairs > 0 && (!pi || !pj || !out))) return HC_E_INVALID;
+    quasi::QParams P{};
+    int rc = quasi_prepare(c, qp, P);
+    if (rc != HC_OK) return rc;
+    if (npairs == 0) return HC_OK;
+    for (int64_t k = 0; k < npairs; ++k)
+        if (pi[k] < 0 || pi[k] >= c->n_reads || pj[k] < 0 || pj[k] >= c->n_reads) { c->err = "hc_quasi_score_pairs: read index out of range"; return HC_E_INVALID; }
+    size_t cap2 = c->pairs_cap;
+    if ((rc = grow(c, c->d_pi, c->pairs_cap, (size_t)npairs)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_pj, cap2, (size_t)npairs)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_qres, c->qres_cap, (size_t)npairs)) != HC_OK) return rc;
+    CU_TRY(c, cudaMemcpyAsync(c->d_pi, pi, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(c->d_pj, pj, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, c->stream));
+    const int blocks = (int)std::min<int64_t>((npairs + 127) / 128, (int64_t)c->sm_count * 16);
+    quasi::pairs_kernel<<<blocks, 128, 0, c->stream>>>(P, c->d_hdr, c->d_ops, c->d_pi, c->d_pj, npairs, c->d_qres);
+    CU_TRY(c, cudaGetLastError());
+    CU_TRY(c, cudaMemcpyAsync(out, c->d_qres, sizeof(hc_quasi_result) * npairs, cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    return HC_OK;
+}
+
+int hc_quasi_score_band(hc_ctx* c, const hc_quasi_params* qp, int32_t row_begin, int32_t row_end, uint32_t* adj, int64_t n_words,
+                        hc_band_stats* stats) {
+    if (!c || !qp) return HC_E_INVALID;
+    quasi::QParams P{};
+    int rc = quasi_prepare(c, qp, P);
+    if (rc != HC_OK) return rc;
+    if (row_begin < 0 || row_end < row_begin || row_end > c->n_reads) { c->err = "hc_quasi_score_band: bad row range"; return HC_E_INVALID; }
+    compute_layout(c, row_begin, row_end);
+    const int nrows = row_end - row_begin;
+    const long long total = c->lay_off[nrows];
+    if (adj && n_words < total) { c->err = "hc_quasi_score_band: output buffer smaller than hc_band_layout's n_words"; return HC_E_INVALID; }
+    size_t cap2 = c->rows_cap;
+    if ((rc = grow(c, c->d_col0, c->rows_cap, (size_t)nrows + 1)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_word_off, cap2, (size_t)nrows + 1)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_adj, c->adj_cap, (size_t)std::max<long long>(total, 1))) != HC_OK) return rc;
+    CU_TRY(c, cudaMemcpyAsync(c->d_col0, c->lay_col0.data(), sizeof(int32_t) * nrows, cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(c->d_word_off, c->lay_off.data(), sizeof(long long) * ((size_t)nrows + 1), cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemsetAsync(c->d_stats, 0, sizeof(BandStatsDev), c->stream));
+    CU_TRY(c, cudaEventRecord(c->ev0, c->stream));
+    int launches = 0;
+    if (total > 0) {
+        const long long want = (total + 3) / 4;
+        const int blocks = (int)std::min<long long>(want, (long long)c->sm_count * 16);
+        quasi::band_kernel<<<blocks, 128, 0, c->stream>>>(P, c->d_hdr, c->d_ops, row_begin, nrows, c->d_col0, c->d_word_off, total,
+                                                          c->d_adj, c->d_stats);
+        CU_TRY(c, cudaGetLastError());
+        launches = 1;
+    }
+    CU_TRY(c, cudaEventRecord(c->ev1, c->stream));
+    BandStatsDev hs{};
+    CU_TRY(c, cudaMemcpyAsync(&hs, c->d_stats, sizeof(hs), cudaMemcpyDeviceToHost, c->stream));
+    if (adj && total > 0) CU_TRY(c, cudaMemcpyAsync(adj, c->d_adj, (size_t)total * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        stats->pairs_total = (int64_t)hs.pairs_total; stats->pairs_scored = (int64_t)hs.pairs_scored;
+        stats->pairs_walked = (int64_t)hs.pairs_walked; stats->edges = (int64_t)hs.edges;
+        stats->undefined = (int64_t)hs.undefined; stats->ambiguous = (int64_t)hs.ambiguous;
+        float ms = 0.f;
+        CU_TRY(c, cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+        stats->kernel_ms = ms;
+        stats->launches = launches;
+    }
+    return HC_OK;
 }
 
 int hc_set_kernel(hc_ctx* c, int32_t mode) {

@@ -94,6 +94,8 @@ def load_library():
         L.hc_last_kernel.argtypes = [C.c_void_p]
         L.hc_measure_peaks.argtypes = [C.c_int32, C.c_void_p, C.c_void_p]
         L.hc_get_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.hc_quasi_score_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+        L.hc_quasi_score_band.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]
         assert C.sizeof(_BandStats) == 72 and HDR_DTYPE.itemsize == 64
         _lib = L
     return _lib
@@ -387,6 +389,69 @@ class NewEdgeCalculator(EdgeCalculator):
         un = np.zeros((127, 127), np.float64)
         self._check(self.L.hc_get_tables(self._ctx, _ptr(eq), _ptr(un)), "hc_get_tables")
         return eq, un
+
+
+class _QuasiParams(C.Structure):
+    _fields_ = [("edge_quasi_cutoff_cliques", C.c_double), ("edge_quasi_cutoff_mixed", C.c_double),
+                ("edge_quasi_cutoff_single", C.c_double), ("min_overlap_cliques", C.c_double),
+                ("min_overlap_single", C.c_double), ("frameshift_merge", C.c_int32), ("reserved", C.c_int32),
+                ("ambiguity_rel_tol", C.c_double)]
+
+
+QUASI_RESULT_DTYPE = np.dtype([("status", np.int32), ("edge", np.int32), ("n_single", np.int32), ("flags", np.int32),
+                               ("q", np.float64), ("cutoff", np.float64)], align=True)
+
+
+QUASI_AMBIGUOUS, QUASI_SUBNORMAL = 1, 2
+
+
+class QuasispeciesEdgeCalculator(NewEdgeCalculator):
+    """GPU-backed drop-in for the reference's older scorer QuasispeciesEdgeCalculator (constructor arguments in the
+    reference's order, src/QuasispeciesEdgeCalculator.h:57; ``maxPosition`` sizes the dense copy of simpson_map,
+    ``device`` as in NewEdgeCalculator). Same batch interface; scores with hc_quasi_score_band / hc_quasi_score_pairs."""
+
+    def __init__(self, Q: float = 0.9, edge_quasi_cutoff: float = 0.99, overlap: float = 0.9,
+                 frameshift_merge: bool = False, simpson_map: Optional[Dict[int, float]] = None,
+                 edge_quasi_cutoff_single: float = 0.95, overlap_single: float = 0.6,
+                 edge_quasi_cutoff_mixed: float = 0.97, maxPosition: int = 0, device: int = 0,
+                 ambiguity_rel_tol: float = 1e-12):
+        super().__init__(Q, edge_quasi_cutoff, overlap, frameshift_merge, simpson_map, edge_quasi_cutoff_single,
+                         overlap_single, edge_quasi_cutoff_mixed, maxPosition, False, device, ambiguity_rel_tol)
+        self._qpar = _QuasiParams(edge_quasi_cutoff, edge_quasi_cutoff_mixed, edge_quasi_cutoff_single, overlap,
+                                  overlap_single, int(bool(frameshift_merge)), 0, ambiguity_rel_tol)
+
+    def setOverlapCliques(self, d: float) -> None:
+        self._qpar.min_overlap_cliques = d
+        self._adj = None
+
+    def edgeBetween(self, ap1: AlignmentRecord, ap2: AlignmentRecord) -> bool:
+        if ap1.name == ap2.name:                               # src/QuasispeciesEdgeCalculator.cpp:56
+            return True
+        return super().edgeBetween(ap1, ap2)
+
+    def score_band(self, row_begin: int = 0, row_end: Optional[int] = None, out: Optional[np.ndarray] = None,
+                   amb_cap: int = 0, fetch: bool = True) -> Adjacency:
+        row_end = self._packed.n_reads if row_end is None else row_end
+        col0, off, nw = self.band_layout(row_begin, row_end)
+        if fetch and out is None:
+            out = np.zeros(max(nw, 1), np.uint32)
+        st = _BandStats()
+        self._check(self.L.hc_quasi_score_band(self._ctx, C.byref(self._qpar), row_begin, row_end,
+                                               _ptr(out) if fetch else None, nw, C.byref(st)), "hc_quasi_score_band")
+        stats = {k: getattr(st, k) for k, _ in _BandStats._fields_}
+        words = out[:nw] if fetch else np.zeros(0, np.uint32)
+        return Adjacency(row_begin, row_end, col0, off, words, stats, np.zeros(0, AMBIGUOUS_DTYPE))
+
+    def score_band_detail(self, row_begin: int = 0, row_end: Optional[int] = None):
+        raise HcError("QuasispeciesEdgeCalculator: per-slot detail comes from score_pairs")
+
+    def score_pairs(self, pi, pj) -> np.ndarray:
+        pi = np.ascontiguousarray(pi, np.int32)
+        pj = np.ascontiguousarray(pj, np.int32)
+        out = np.zeros(pi.shape[0], QUASI_RESULT_DTYPE)
+        self._check(self.L.hc_quasi_score_pairs(self._ctx, C.byref(self._qpar), _ptr(pi), _ptr(pj), pi.shape[0], _ptr(out)),
+                    "hc_quasi_score_pairs")
+        return out
 
 
 def pack_only(batch: ReadBatch) -> PackedBatch:

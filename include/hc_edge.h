@@ -201,6 +201,45 @@ int hc_last_kernel(const hc_ctx* ctx);
 /* Scores an explicit list of ordered pairs (ap1 = pi[k], ap2 = pj[k]), full detail per pair. */
 int hc_score_pairs(hc_ctx* ctx, const int32_t* pi, const int32_t* pj, int64_t npairs, hc_pair_result* out);
 
+/* ---- QuasispeciesEdgeCalculator (src/QuasispeciesEdgeCalculator.cpp), the reference's older scorer: same
+ * EdgeCalculator interface (src/EdgeCalculator.h:29), constructor src/QuasispeciesEdgeCalculator.h:57. It runs on
+ * the batch hc_upload made resident and uses the context's allele-frequency map (its SIMPSON_MAP; entries equal to
+ * 0.0 count as absent). q = computeOverlap(ap1, ap2, cutoff) (:72), edge = q >= cutoff (:69); the same-name
+ * shortcut (:56) does not apply inside one batch. The per-column log terms are tabulated on the host, so the
+ * running sum is bit-identical to the reference's; only the closing pow(exp(sum), 1/n) (:425) is device libm, and
+ * pairs with |q - cutoff| <= ambiguity_rel_tol * |cutoff| are flagged. status = HC_ST_UNDEFINED where the reference
+ * would not terminate (:258-267, :347-381) or would index out of range. */
+typedef struct {
+    double edge_quasi_cutoff_cliques, edge_quasi_cutoff_mixed, edge_quasi_cutoff_single;   /* :36-38 */
+    double min_overlap_cliques, min_overlap_single;                                         /* :39-40 */
+    int32_t frameshift_merge;                                                               /* :41 */
+    int32_t reserved;
+    double ambiguity_rel_tol;           /* 0 -> 1e-12 */
+} hc_quasi_params;
+
+typedef struct {
+    int32_t status;                     /* HC_ST_WALKED or HC_ST_UNDEFINED */
+    int32_t edge;
+    int32_t n_single;                   /* singleOverlap calls computeOverlap made: 0 (rejected by the overlap gates), 1, 2 */
+    int32_t flags;                      /* HC_QUASI_* */
+    double q;                           /* computeOverlap's value */
+    double cutoff;                      /* the cutoff edgeBetween picked (:59-66) */
+} hc_quasi_result;
+
+#define HC_QUASI_AMBIGUOUS 1             /* |q - cutoff| within ambiguity_rel_tol */
+#define HC_QUASI_SUBNORMAL 2             /* a singleOverlap's log sum is below log(DBL_MIN): exp(sum) (:425) is subnormal or 0,
+                                            q = pow(exp(sum), 1/n) has lost its precision in the reference itself (its exp
+                                            result has few or no significant bits left); q < 0.06 there for n <= 250 */
+
+/* Explicit list of ordered pairs (ap1 = pi[k], ap2 = pj[k]). */
+int hc_quasi_score_pairs(hc_ctx* ctx, const hc_quasi_params* params, const int32_t* pi, const int32_t* pj,
+                         int64_t npairs, hc_quasi_result* out);
+
+/* Banded adjacency of rows [row_begin,row_end) in hc_band_layout's layout. Pairs outside the band have disjoint
+ * covered intervals, for which computeOverlap returns 0: no edge as long as the cutoffs are > 0 (required here). */
+int hc_quasi_score_band(hc_ctx* ctx, const hc_quasi_params* params, int32_t row_begin, int32_t row_end, uint32_t* adj,
+                        int64_t n_words, hc_band_stats* stats);
+
 /* Replaces the scalar scoring parameters (cutoffs, min overlaps, no_prob0, tolerance) of a live context;
  * the allele-frequency map and the device stay as given to hc_create. Mirrors
  * EdgeCalculator::setOverlapCliques (src/EdgeCalculator.h:35). */

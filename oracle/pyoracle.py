@@ -41,7 +41,7 @@ class _QuasiParams(C.Structure):
                 ("simpson_len", C.c_int32), ("simpson", C.c_void_p)]
 
 
-QUASI_RESULT_DTYPE = np.dtype([("status", np.int32), ("edge", np.int32), ("n_single", np.int32), ("pad", np.int32),
+QUASI_RESULT_DTYPE = np.dtype([("status", np.int32), ("edge", np.int32), ("n_single", np.int32), ("subnormal", np.int32),
                                ("q", np.float64), ("cutoff", np.float64)], align=True)
 
 

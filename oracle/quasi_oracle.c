@@ -32,7 +32,7 @@ typedef struct {
     int32_t status;          /* 0 = defined, 3 = the reference would hang or read out of bounds */
     int32_t edge;            /* q >= cutoff (:69) */
     int32_t n_single;        /* how many singleOverlap calls computeOverlap made (0, 1 or 2) */
-    int32_t pad;
+    int32_t subnormal;       /* some singleOverlap had exp(sum) below DBL_MIN: q has lost its precision (:425) */
     double q;                /* computeOverlap's return value */
     double cutoff;
 } qorc_result;
@@ -74,7 +74,7 @@ static void add_simpson(const qorc_params* P, int pos, double* acc) {
 /* singleOverlap (:181-426). A/B: the chosen segments ("strains") of ap1/ap2. *undef is set where the reference would
  * not terminate or would index out of range. */
 static double single_overlap(const orc_seg* A, const orc_seg* B, const qorc_params* P, double MIN_OVERLAP, double cutoff,
-                             int* undef) {
+                             int* undef, int* subnormal) {
     const orc_seg *S1 = A, *S2 = B;
     if (S2->start < S1->start) { const orc_seg* t = S1; S1 = S2; S2 = t; }                 /* :215-220 */
     const int s1 = S1->start, e1 = S1->end, s2 = S2->start, e2 = S2->end;
@@ -163,11 +163,13 @@ static double single_overlap(const orc_seg* A, const orc_seg* B, const qorc_para
         }
     }
     if (perfect) return 1;
+    if (overlap_probability < -708.3964185322641) *subnormal = 1;                           /* log(DBL_MIN) */
     return pow(exp(overlap_probability), 1.0 / total_size);                                 /* :425 */
 }
 
 /* computeOverlap (:72-131) */
-static double compute_overlap(const orc_read* a, const orc_read* b, const qorc_params* P, double cutoff, int* undef, int* ncalls) {
+static double compute_overlap(const orc_read* a, const orc_read* b, const qorc_params* P, double cutoff, int* undef, int* ncalls,
+                              int* subnormal) {
     const double MIN_OVERLAP = (a->is_clique && b->is_clique) ? P->overlap_cliques : P->overlap_single;   /* :74-79 */
     const orc_seg *a1 = &a->s[0], *a2 = &a->s[1], *b1 = &b->s[0], *b2 = &b->s[1];
 #define MINI(x, y) ((x) < (y) ? (x) : (y))
@@ -178,7 +180,7 @@ static double compute_overlap(const orc_read* a, const orc_read* b, const qorc_p
         if (MIN_OVERLAP <= 1) overlap_size1 /= (float)read_size1;
         if (overlap_size1 < MIN_OVERLAP) return 0;
         *ncalls = 1;
-        return single_overlap(a1, b1, P, MIN_OVERLAP, cutoff, undef);
+        return single_overlap(a1, b1, P, MIN_OVERLAP, cutoff, undef, subnormal);
     } else if (a->single_end || b->single_end) {                                            /* :87-117 */
         const orc_seg *x1, *y1, *x2, *y2;          /* the two singleOverlap calls: (x1,y1) and (x2,y2) */
         int read_size1, read_size2;
@@ -200,8 +202,8 @@ static double compute_overlap(const orc_read* a, const orc_read* b, const qorc_p
         if ((overlap_size1 >= MIN_OVERLAP && overlap_size2 >= MIN_OVERLAP) ||
             (overlap_size1 + overlap_size2 >= MIN_OVERLAP && overlap_size1 > 0 && overlap_size2 > 0)) {
             *ncalls = 2;
-            const double p = single_overlap(x1, y1, P, MIN_OVERLAP, cutoff, undef);
-            const double q = single_overlap(x2, y2, P, MIN_OVERLAP, cutoff, undef);
+            const double p = single_overlap(x1, y1, P, MIN_OVERLAP, cutoff, undef, subnormal);
+            const double q = single_overlap(x2, y2, P, MIN_OVERLAP, cutoff, undef, subnormal);
             return p * q;
         }
         return 0;
@@ -215,8 +217,8 @@ static double compute_overlap(const orc_read* a, const orc_read* b, const qorc_p
         if (MIN_OVERLAP <= 1) overlap_size2 /= (float)read_size2;
         if (overlap_size2 < MIN_OVERLAP) return 0;
         *ncalls = 2;
-        const double p = single_overlap(a1, b1, P, MIN_OVERLAP, cutoff, undef);
-        const double q = single_overlap(a2, b2, P, MIN_OVERLAP, cutoff, undef);
+        const double p = single_overlap(a1, b1, P, MIN_OVERLAP, cutoff, undef, subnormal);
+        const double q = single_overlap(a2, b2, P, MIN_OVERLAP, cutoff, undef, subnormal);
         return p * q;
     }
 #undef MINI
@@ -228,14 +230,15 @@ void qorc_edge(const orc_read* a, const orc_read* b, const qorc_params* P, qorc_
     if (a->is_clique && b->is_clique) cutoff = P->cutoff_cliques;
     else if (a->is_clique || b->is_clique) cutoff = P->cutoff_mixed;
     else cutoff = P->cutoff_single;
-    int undef = 0, ncalls = 0;
-    const double q = compute_overlap(a, b, P, cutoff, &undef, &ncalls);
+    int undef = 0, ncalls = 0, subnormal = 0;
+    const double q = compute_overlap(a, b, P, cutoff, &undef, &ncalls, &subnormal);
     memset(out, 0, sizeof *out);
     out->status = undef ? 3 : 0;
     out->q = undef ? 0.0 : q;
     out->cutoff = cutoff;
     out->edge = !undef && q >= cutoff;
     out->n_single = ncalls;
+    out->subnormal = !undef && subnormal;
 }
 
 void qorc_edge_pairs(const orc_read* reads, const int32_t* pi, const int32_t* pj, int64_t npairs, const qorc_params* P,

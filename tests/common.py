@@ -73,3 +73,24 @@ def assert_pairs_equal(dev, orc, label=""):
     unflagged = differ & (dev["ambiguous"] == 0)
     assert not unflagged.any(), label + ": edge differs on unflagged pairs %s" % np.nonzero(unflagged)[0][:5]
     return int(differ.sum())
+
+
+# ---- QuasispeciesEdgeCalculator ------------------------------------------------------
+def quasi_pair_sample(n: int, near: int = 40, far: int = 20000, seed: int = 7):
+    """A fixed list of ordered pairs (i > j): every pair at most `near` arrivals apart plus `far` random ones."""
+    i, j = tri_pairs(n)
+    k = np.flatnonzero(i - j <= near)
+    rng = np.random.default_rng(seed)
+    if i.size > far:
+        k = np.unique(np.concatenate([k, rng.choice(i.size, far, replace=False)]))
+    else:
+        k = np.arange(i.size)
+    return i[k], j[k]
+
+
+def quasi_kwargs(params: dict, max_position: int) -> dict:
+    kw = dict(params)
+    if kw.get("simpson_map") == "every7th":
+        kw["simpson_map"] = {p: 0.05 + 0.9 * ((p * 37) % 101) / 101.0 for p in range(1, max_position + 1, 7)}
+    kw["maxPosition"] = max_position
+    return kw

@@ -1,0 +1,76 @@
+"""B200: the CUDA QuasispeciesEdgeCalculator path (hc_quasi_score_pairs / hc_quasi_score_band through the C ABI)
+against oracle/quasi_oracle.c. The running log sum is bit-identical (host-tabulated terms); the closing
+pow(exp(sum), 1/n) is device libm: q within 1e-12 relative, decision identical unless the device flags the pair."""
+import numpy as np
+import pytest
+
+from haploclique_b200 import edge, synth
+from oracle import pyoracle
+from tests import common
+from tests.golden.make_quasi_golden import FIXTURES, PARAM_SETS
+
+pytestmark = pytest.mark.gpu
+REL_TOL = 1e-12
+
+
+def _compare(dev, orc, label):
+    assert (dev["status"] == np.where(orc["status"] == 3, 3, 2)).all(), label + ": status"
+    ok = orc["status"] != 3
+    assert (dev["n_single"][ok] == orc["n_single"][ok]).all(), label + ": singleOverlap call count"
+    assert (dev["cutoff"][ok] == orc["cutoff"][ok]).all()
+    # exp(sum) subnormal: the reference's own q has lost its precision there (both sides flag the same pairs, from the
+    # bit-identical log sum); q is compared on the others, the decision on all
+    sub = orc["subnormal"][ok] != 0
+    assert (((dev["flags"][ok] & edge.QUASI_SUBNORMAL) != 0) == sub).all(), label + ": subnormal flag"
+    dq, oq = dev["q"][ok][~sub], orc["q"][ok][~sub]
+    assert ((dq == 0) == (oq == 0)).all(), label + ": q == 0 pattern"
+    rel = np.abs(dq - oq) / np.maximum(np.abs(oq), 1e-300)
+    assert float(rel[oq != 0].max(initial=0.0)) <= REL_TOL, label + ": q differs by %g" % rel[oq != 0].max()
+    differ = (dev["edge"][ok] != orc["edge"][ok])
+    assert not (differ & ((dev["flags"][ok] & edge.QUASI_AMBIGUOUS) == 0)).any(), label + ": decision differs on unflagged pairs"
+    return int(differ.sum())
+
+
+@pytest.mark.parametrize("fixture", FIXTURES)
+@pytest.mark.parametrize("pset", sorted(PARAM_SETS))
+def test_quasi_pairs_match_oracle(fixture, pset):
+    b = common.load_batch(fixture)
+    kw = common.quasi_kwargs(PARAM_SETS[pset], b.max_position())
+    pi, pj = common.quasi_pair_sample(b.n)
+    calc = edge.QuasispeciesEdgeCalculator(**kw)
+    calc.upload(b)
+    dev = calc.score_pairs(pi, pj)
+    orc = pyoracle.QuasiOracle(b, **kw).pairs(pi, pj)
+    _compare(dev, orc, "%s/%s" % (fixture, pset))
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_quasi_zoo_and_band(seed):
+    b = synth.zoo(160, seed=40 + seed)
+    kw = dict(overlap_single=0.1, overlap=0.1, edge_quasi_cutoff_single=0.5, edge_quasi_cutoff_mixed=0.5, edge_quasi_cutoff=0.5,
+              frameshift_merge=bool(seed % 2), maxPosition=b.max_position())
+    calc = edge.QuasispeciesEdgeCalculator(**kw)
+    adj = calc.scoreBatch(b)
+    pi, pj = common.tri_pairs(b.n)
+    orc = pyoracle.QuasiOracle(b, **kw).pairs(pi, pj)
+    dev = calc.score_pairs(pi, pj)
+    flips = _compare(dev, orc, "quasi-zoo%d" % seed)
+    # the banded adjacency says the same as the pair list, and nothing outside the band is an edge
+    ai, aj = adj.edges()
+    if flips == 0:
+        e = (orc["edge"] == 1) & (orc["status"] != 3)
+        assert adj.count() == int(e.sum())
+        assert (ai == pi[e]).all() and (aj == pj[e]).all()
+    assert adj.stats["launches"] == 1 and adj.stats["pairs_total"] >= adj.count()
+
+
+def test_quasi_reference_interface():
+    b = synth.quasispecies(300, genome_len=1500, seed=9)
+    calc = edge.QuasispeciesEdgeCalculator(overlap_single=0.3, edge_quasi_cutoff_single=0.8, maxPosition=b.max_position())
+    adj = calc.scoreBatch(b)
+    orc = pyoracle.QuasiOracle(b, overlap_single=0.3, edge_quasi_cutoff_single=0.8)
+    pi, pj = common.tri_pairs(b.n)
+    o = orc.pairs(pi, pj)
+    assert adj.count() == int(o["edge"].sum()) > 0
+    with pytest.raises(edge.HcError):
+        edge.QuasispeciesEdgeCalculator(edge_quasi_cutoff_single=0.0).scoreBatch(b)     # cutoffs must be > 0
