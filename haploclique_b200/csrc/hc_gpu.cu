@@ -18,6 +18,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "hc_internal.h"
@@ -496,6 +497,10 @@ struct hc_ctx {
     double* d_logsum = nullptr; double* d_simpson_ln = nullptr; hc_quasi_result* d_qres = nullptr; size_t qres_cap = 0;
     // second-generation tiled kernel (hc_tile2.cuh): row / column operand formats and the 9-row table
     uint32_t* d_opsA = nullptr; uint16_t* d_opsF = nullptr; uint32_t* d_tab7 = nullptr;
+    bool have_formats = false;
+    // capacities (elements) of the per-batch device buffers: they only grow, so a steady stream of hc_upload calls does
+    // no cudaMalloc / cudaFree (both synchronise the device and would serialise the copies with the host-side layout work)
+    size_t cap_hdr = 0, cap_ops = 0, cap_table = 0, cap_ladder = 0, cap_aux = 0, cap_col2op = 0, cap_opsA = 0, cap_opsF = 0, cap_tab7 = 0;
     int4* d_items = nullptr; size_t items_cap = 0; int* d_item_counter = nullptr;
     hc_pair_result* d_detail = nullptr; size_t detail_cap = 0;
     int kernel_mode = HC_KERNEL_AUTO;
@@ -550,21 +555,35 @@ DevParams dev_params(const hc_ctx* c) {
     return P;
 }
 
+// f(begin, end) over [0, n) on up to 8 host threads (the per-upload layout work: binary searches and window sorts)
+template <class F>
+void parallel_ranges(int n, int min_per_thread, F f) {
+    int T = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 8u);
+    T = std::max(1, std::min(T, n / std::max(1, min_per_thread)));
+    if (T <= 1) { f(0, n); return; }
+    std::vector<std::thread> pool;
+    for (int t = 1; t < T; ++t) pool.emplace_back([=, &f] { f((int)((long long)n * t / T), (int)((long long)n * (t + 1) / T)); });
+    f(0, (int)((long long)n / T));
+    for (auto& th : pool) th.join();
+}
+
 int compute_layout(hc_ctx* c, int row_begin, int row_end) {
     if (c->lay_begin == row_begin && c->lay_end == row_end) return HC_OK;
     const int nrows = row_end - row_begin;
     c->lay_col0.assign(nrows, 0);
     c->lay_off.assign((size_t)nrows + 1, 0);
+    parallel_ranges(nrows, 4096, [&](int k0, int k1) {
+        for (int k = k0; k < k1; ++k) {
+            const int i = row_begin + k;
+            // first j whose running maximum of cov_last reaches cov_first[i]; everything before it is disjoint
+            const auto it = std::lower_bound(c->cov_last_pmax.begin(), c->cov_last_pmax.begin() + i, c->cov_first[i]);
+            c->lay_col0[k] = (int)(it - c->cov_last_pmax.begin()) & ~31;
+        }
+    });
     long long acc = 0;
     for (int k = 0; k < nrows; ++k) {
-        const int i = row_begin + k;
-        // first j whose running maximum of cov_last reaches cov_first[i]; everything before it is disjoint
-        const auto it = std::lower_bound(c->cov_last_pmax.begin(), c->cov_last_pmax.begin() + i, c->cov_first[i]);
-        int lo = (int)(it - c->cov_last_pmax.begin());
-        lo &= ~31;
-        c->lay_col0[k] = lo;
         c->lay_off[k] = acc;
-        acc += (i - lo + 31) / 32;
+        acc += (row_begin + k - c->lay_col0[k] + 31) / 32;
     }
     c->lay_off[nrows] = acc;
     c->lay_begin = row_begin;
@@ -671,7 +690,7 @@ Tile2Geom tile2_geometry(const hc_ctx* c) {
 }
 
 bool tile2_eligible(const hc_ctx* c) {
-    if (c->d_simpson != nullptr || c->d_opsA == nullptr) return false;
+    if (c->d_simpson != nullptr || !c->have_formats) return false;
     return tile2_geometry(c).nwarps > 0;
 }
 
@@ -694,29 +713,38 @@ void build_items(hc_ctx* c, int row_begin, int row_end, int n_ctas) {
         const int jhi = row_end - 1;                                   // columns [jlo, jhi)
         int W = (int)(band / nrows / 16);
         W = std::max(32, std::min(1024, (W + 16) / 32 * 32));
-        std::vector<int32_t> order;
         struct Blk { int first_j; int maxend; };
-        std::vector<Blk> blks;
-        for (int w0 = jlo; w0 < jhi; w0 += W) {
-            const int w1 = std::min(w0 + W, jhi);
-            order.resize(w1 - w0);
-            for (int j = w0; j < w1; ++j) order[j - w0] = j;
-            std::sort(order.begin(), order.end(), [&](int x, int y) {
-                const int tx = c->is_single[x] ? 0 : 1, ty = c->is_single[y] ? 0 : 1;
-                if (tx != ty) return tx < ty;
-                if (c->cov_last[x] != c->cov_last[y]) return c->cov_last[x] < c->cov_last[y];
-                return x < y;
-            });
-            for (size_t p = 0; p < order.size(); p += 32) {
-                Blk b{INT32_MAX, INT32_MIN};
-                for (size_t q = p; q < p + 32; ++q) {
-                    const int j = q < order.size() ? order[q] : -1;
-                    c->colidx.push_back(j);
-                    if (j >= 0) { b.first_j = std::min(b.first_j, j); b.maxend = std::max(b.maxend, c->cov_last[j]); }
-                }
-                blks.push_back(b);
-            }
+        // windows are independent: block / colidx positions follow from the window sizes, so threads write in place
+        const int nwin = jhi > jlo ? (jhi - jlo + W - 1) / W : 0;
+        std::vector<size_t> blk0((size_t)nwin + 1, 0);
+        for (int w = 0; w < nwin; ++w) {
+            const int w0 = jlo + w * W, w1 = std::min(w0 + W, jhi);
+            blk0[w + 1] = blk0[w] + (size_t)(w1 - w0 + 31) / 32;
         }
+        std::vector<Blk> blks(blk0[nwin]);
+        c->colidx.assign(blk0[nwin] * 32, -1);
+        parallel_ranges(nwin, 16, [&](int wa, int wb) {
+            std::vector<uint64_t> order;             // key = single/paired, last covered position, read index
+            for (int w = wa; w < wb; ++w) {
+                const int w0 = jlo + w * W, w1 = std::min(w0 + W, jhi);
+                order.resize(w1 - w0);
+                for (int j = w0; j < w1; ++j)
+                    order[j - w0] = ((uint64_t)(c->is_single[j] ? 0 : 1) << 63) |
+                                    ((uint64_t)(uint32_t)(c->cov_last[j] + (1 << 30)) << 32) | (uint32_t)j;
+                std::sort(order.begin(), order.end());
+                for (size_t p = 0; p < order.size(); p += 32) {
+                    Blk b{INT32_MAX, INT32_MIN};
+                    const size_t bi = blk0[w] + p / 32;
+                    for (size_t q = p; q < p + 32 && q < order.size(); ++q) {
+                        const int j = (int)(uint32_t)order[q];
+                        c->colidx[bi * 32 + (q - p)] = j;
+                        b.first_j = std::min(b.first_j, j);
+                        b.maxend = std::max(b.maxend, c->cov_last[j]);
+                    }
+                    blks[bi] = b;
+                }
+            }
+        });
         // rows that can reach a block: i > first_j and cov_first[i] <= maxend; cov_first_smin is the suffix minimum of
         // cov_first (monotone), so the admissible rows are a prefix
         std::vector<int> first(blks.size()), last(blks.size());
@@ -855,20 +883,18 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     if (!c || !p) return HC_E_INVALID;
     CU_TRY(c, cudaSetDevice(c->device));
     CU_TRY(c, cudaStreamSynchronize(c->stream));
-    cudaFree(c->d_hdr); cudaFree(c->d_ops); cudaFree(c->d_table); cudaFree(c->d_ladder); cudaFree(c->d_aux); cudaFree(c->d_col2op);
-    cudaFree(c->d_opsA); cudaFree(c->d_opsF); cudaFree(c->d_tab7); cudaFree(c->d_logsum);
-    c->d_logsum = nullptr;
+    if (c->d_logsum) { cudaFree(c->d_logsum); c->d_logsum = nullptr; }     // depends on the quality codes of the batch
     std::memcpy(c->qual_chars, p->qual_chars, sizeof(c->qual_chars));
-    c->d_hdr = nullptr; c->d_ops = nullptr; c->d_table = nullptr; c->d_ladder = nullptr; c->d_aux = nullptr; c->d_col2op = nullptr;
-    c->d_opsA = nullptr; c->d_opsF = nullptr; c->d_tab7 = nullptr;
+    c->have_formats = false;
+    int rc;
     c->items_begin = c->items_end = -1;
     c->n_reads = p->n_reads;
     c->K = std::max(p->n_qual_codes, 1);
     c->max_ops = p->max_ops_per_read;
     c->lay_begin = c->lay_end = -1;
     const size_t nh = std::max(p->n_reads, 1);
-    CU_TRY(c, cudaMalloc((void**)&c->d_hdr, nh * sizeof(hc_read_hdr)));
-    CU_TRY(c, cudaMalloc((void**)&c->d_ops, ((size_t)p->n_ops_total + 64) * sizeof(uint16_t)));
+    if ((rc = grow(c, c->d_hdr, c->cap_hdr, nh)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_ops, c->cap_ops, (size_t)p->n_ops_total + 64)) != HC_OK) return rc;
     CU_TRY(c, cudaMemcpyAsync(c->d_hdr, p->hdr, (size_t)p->n_reads * sizeof(hc_read_hdr), cudaMemcpyHostToDevice, c->stream));
     CU_TRY(c, cudaMemcpyAsync(c->d_ops, p->ops, ((size_t)p->n_ops_total + 64) * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
     // probability tables re-indexed by quality code: [equal | unequal][code1][code2]
@@ -880,16 +906,16 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
             tab[(size_t)a * K + b] = c->eq[qa * 127 + qb];
             tab[(size_t)K * K + (size_t)a * K + b] = c->uneq[qa * 127 + qb];
         }
-    CU_TRY(c, cudaMalloc((void**)&c->d_table, tab.size() * sizeof(double)));
+    if ((rc = grow(c, c->d_table, c->cap_table, tab.size())) != HC_OK) return rc;
     CU_TRY(c, cudaMemcpyAsync(c->d_table, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     std::vector<double> ladder;
     c->ladder_len = 2 * c->max_ops + 2;
     hc::build_prob0_ladder(ladder, c->ladder_len - 1);
-    CU_TRY(c, cudaMalloc((void**)&c->d_ladder, ladder.size() * sizeof(double)));
+    if ((rc = grow(c, c->d_ladder, c->cap_ladder, ladder.size())) != HC_OK) return rc;
     CU_TRY(c, cudaMemcpyAsync(c->d_ladder, ladder.data(), ladder.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     // prefix counts of the segments that are not "clips, plain M, clips" (the tiled kernel's O(1) tails)
-    CU_TRY(c, cudaMalloc((void**)&c->d_aux, ((size_t)p->n_ops_total + 2 * (size_t)p->n_reads + 64) * sizeof(uint32_t)));
-    CU_TRY(c, cudaMalloc((void**)&c->d_col2op, ((size_t)p->n_ops_total + 64) * sizeof(uint16_t)));
+    if ((rc = grow(c, c->d_aux, c->cap_aux, (size_t)p->n_ops_total + 2 * (size_t)p->n_reads + 64)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_col2op, c->cap_col2op, (size_t)p->n_ops_total + 64)) != HC_OK) return rc;
     if (p->n_reads > 0) {
         tile::build_aux_kernel<<<(2 * p->n_reads + 127) / 128, 128, 0, c->stream>>>(c->d_hdr, c->d_ops, p->n_reads, c->d_aux, c->d_col2op);
         CU_TRY(c, cudaGetLastError());
@@ -917,10 +943,11 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
                     }
                 }
         const long long nrec = (long long)p->n_ops_total + 64;
-        CU_TRY(c, cudaMalloc((void**)&c->d_tab7, tab7.size() * sizeof(uint32_t)));
+        if ((rc = grow(c, c->d_tab7, c->cap_tab7, tab7.size())) != HC_OK) return rc;
         CU_TRY(c, cudaMemcpyAsync(c->d_tab7, tab7.data(), tab7.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
-        CU_TRY(c, cudaMalloc((void**)&c->d_opsA, (size_t)nrec * sizeof(uint32_t)));
-        CU_TRY(c, cudaMalloc((void**)&c->d_opsF, (size_t)nrec * sizeof(uint16_t)));
+        if ((rc = grow(c, c->d_opsA, c->cap_opsA, (size_t)nrec)) != HC_OK) return rc;
+        if ((rc = grow(c, c->d_opsF, c->cap_opsF, (size_t)nrec)) != HC_OK) return rc;
+        c->have_formats = true;
         tile2::build_formats_kernel<<<(unsigned)((nrec + 255) / 256), 256, 0, c->stream>>>(c->d_ops, nrec, tile2_row_bytes(K), tile2_entry_bytes(K), c->d_opsA, c->d_opsF);
         CU_TRY(c, cudaGetLastError());
     }
@@ -939,6 +966,12 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     }
     int smin = INT32_MAX;
     for (int r = p->n_reads - 1; r >= 0; --r) { smin = std::min(smin, c->cov_first[r]); c->cov_first_smin[r] = smin; }
+    // the band layout and the tiled kernels' work items of the whole batch depend on the headers only: computed here, on
+    // the host, while the copies and the device-side builds above are in flight (hc_score_band(0, n) finds them cached)
+    if (p->n_reads > 1 && (tile_eligible(c) || tile2_eligible(c))) {
+        compute_layout(c, 0, p->n_reads);
+        build_items(c, 0, p->n_reads, c->sm_count);
+    }
     CU_TRY(c, cudaStreamSynchronize(c->stream));
     return HC_OK;
 }
