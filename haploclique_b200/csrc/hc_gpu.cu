@@ -694,6 +694,12 @@ bool tile2_eligible(const hc_ctx* c) {
     return tile2_geometry(c).nwarps > 0;
 }
 
+// Column windows are (mean band width) / item_window_div() reads wide (HC_ITEM_WINDOW_DIV overrides, for experiments)
+int item_window_div() {
+    static const int v = [] { const char* e = std::getenv("HC_ITEM_WINDOW_DIV"); return e ? std::max(1, std::atoi(e)) : 16; }();
+    return v;
+}
+
 // Work items of the tiled kernel for rows [row_begin,row_end).
 // Columns (the earlier reads j) are taken in windows of W consecutive reads; inside a window they are sorted by
 // (single/paired, last covered position) and cut into blocks of 32. For a later row read i the length of the
@@ -711,8 +717,8 @@ void build_items(hc_ctx* c, int row_begin, int row_end, int n_ctas) {
         long long band = 0;
         for (int k = 0; k < nrows; ++k) { jlo = std::min(jlo, c->lay_col0[k]); band += (row_begin + k) - c->lay_col0[k]; }
         const int jhi = row_end - 1;                                   // columns [jlo, jhi)
-        int W = (int)(band / nrows / 16);
-        W = std::max(32, std::min(1024, (W + 16) / 32 * 32));
+        int W = (int)(band / nrows / item_window_div());
+        W = std::max(32, std::min(4096, (W + 16) / 32 * 32));
         struct Blk { int first_j; int maxend; };
         // windows are independent: block / colidx positions follow from the window sizes, so threads write in place
         const int nwin = jhi > jlo ? (jhi - jlo + W - 1) / W : 0;
@@ -819,7 +825,7 @@ int hc_create(const hc_params* params, hc_ctx** out) {
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
     if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
-    if ((e = cudaMalloc((void**)&c->d_stats, sizeof(BandStatsDev))) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = cudaMalloc((void**)&c->d_stats, 2 * sizeof(BandStatsDev))) != cudaSuccess) return fail("cudaMalloc", e);
     if (!c->simpson_host.empty()) {
         const size_t bytes = c->simpson_host.size() * sizeof(double);
         if ((e = cudaMalloc((void**)&c->d_simpson, bytes)) != cudaSuccess) return fail("cudaMalloc", e);
@@ -1021,7 +1027,7 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
     }
     CU_TRY(c, cudaMemcpyAsync(c->d_col0, c->lay_col0.data(), sizeof(int32_t) * nrows, cudaMemcpyHostToDevice, c->stream));
     CU_TRY(c, cudaMemcpyAsync(c->d_word_off, c->lay_off.data(), sizeof(long long) * ((size_t)nrows + 1), cudaMemcpyHostToDevice, c->stream));
-    CU_TRY(c, cudaMemsetAsync(c->d_stats, 0, sizeof(BandStatsDev), c->stream));
+    CU_TRY(c, cudaMemsetAsync(c->d_stats, 0, 2 * sizeof(BandStatsDev), c->stream));    // [1]: HC_T2_PROFILE counters
     int launches = 0;
     c->last_kernel = 0;
     if (use_tile && total > 0) {
@@ -1089,6 +1095,15 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
     }
     BandStatsDev hs{};
     CU_TRY(c, cudaMemcpyAsync(&hs, c->d_stats, sizeof(hs), cudaMemcpyDeviceToHost, c->stream));
+#ifdef HC_T2_PROFILE
+    {
+        BandStatsDev pr{};
+        CU_TRY(c, cudaMemcpy(&pr, c->d_stats + 1, sizeof(pr), cudaMemcpyDeviceToHost));
+        std::fprintf(stderr, "[HC_T2_PROFILE] 8-column iterations: first pass %llu (%.2f lanes), later passes %llu (%.2f lanes)\n",
+                     pr.pairs_total, pr.pairs_total ? (double)pr.pairs_scored / pr.pairs_total : 0.0, pr.pairs_walked,
+                     pr.pairs_walked ? (double)pr.edges / pr.pairs_walked : 0.0);
+    }
+#endif
     if (adj && total > 0) CU_TRY(c, cudaMemcpyAsync(adj, c->d_adj, (size_t)total * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
     if (detail && total > 0) CU_TRY(c, cudaMemcpyAsync(detail, c->d_detail, (size_t)total * 32 * sizeof(hc_pair_result), cudaMemcpyDeviceToHost, c->stream));
     CU_TRY(c, cudaStreamSynchronize(c->stream));

@@ -103,7 +103,13 @@ __device__ __forceinline__ void overlap2(const Args2& a, const int* hA, const in
         T2_MUL(__dp2a_lo((BW), 0x00000001u, (AW0)));                                       \
         T2_MUL(__dp2a_hi((BW), 0x01000000u, (AW1)));                                       \
     } while (0)
+#ifdef HC_T2_PROFILE
+    int pass__ = 0;
+#endif
     for (;;) {
+#ifdef HC_T2_PROFILE
+        pass__++;
+#endif
         if (more && !qx) {
             const int run = min(min(hi - ref + 1, nA - ca), nB - cb);
             if (run >= 1) {
@@ -127,6 +133,15 @@ __device__ __forceinline__ void overlap2(const Args2& a, const int* hA, const in
                     asm volatile("" : "+r"(shb));
                     uint32_t b0 = pb[0];
                     while (done + 8 <= run) {
+#ifdef HC_T2_PROFILE
+                        {   // [0] iterations, [1] active lanes, [2]/[3] the same for second and later passes of the slot
+                            const unsigned am = __activemask();
+                            if ((int)(threadIdx.x & 31) == __ffs(am) - 1) {
+                                atomicAdd(&a.stats[1].pairs_total + (pass__ > 1 ? 2 : 0), 1ull);
+                                atomicAdd(&a.stats[1].pairs_total + (pass__ > 1 ? 3 : 1), (unsigned long long)__popc(am));
+                            }
+                        }
+#endif
                         const uint4 A0 = pa[0], A1 = pa[1];
                         const uint32_t b1 = pb[32], b2 = pb[64], b3 = pb[96], b4 = pb[128];
                         const uint32_t B01 = __funnelshift_r(b0, b1, shb), B23 = __funnelshift_r(b1, b2, shb);

@@ -235,3 +235,40 @@ def test_tiled_kernel_row_windows_concatenate(kernel):
     pi_ = np.concatenate([p.edges()[0] for p in parts])
     pj_ = np.concatenate([p.edges()[1] for p in parts])
     assert (fi == pi_).all() and (fj == pj_).all()
+
+
+def test_full_size_C2_three_kernels_agree():
+    """BASELINE configs[1] at full size (100k fragments, 4.7e8 scored pairs): the oracle cannot walk that many pairs in
+    test time, so the check is a size-independent property -- the three band kernels (generic one-lane-per-pair walker,
+    first- and second-generation tiled kernels; the walker shares no walking code with the tiled ones) produce the same
+    adjacency words and the same column totals, row windows concatenate to the full run, and a sample of 200k band
+    pairs matches the oracle bit for bit."""
+    import bench
+    b = synth.quasispecies(100_000, **{k: v for k, v in synth.CONFIGS["C2"].items() if k != "n_frag"})
+    kw = dict(bench.PARAMS, maxPosition=b.max_position() + 2000)
+    calc = edge.NewEdgeCalculator(**kw)
+    calc.upload(b)
+    res = {}
+    for name, mode in (("tiled2", edge.KERNEL_TILED2), ("tiled", edge.KERNEL_TILED), ("generic", edge.KERNEL_GENERIC)):
+        calc.set_kernel(mode)
+        res[name] = calc.score_band(amb_cap=0)
+        assert calc.last_kernel() == mode
+    ref = res["generic"]
+    for name in ("tiled2", "tiled"):
+        assert (res[name].words == ref.words).all(), name
+        for k in ("pairs_scored", "pairs_walked", "edges", "sum_cc", "sum_tc", "undefined"):
+            assert res[name].stats[k] == ref.stats[k], (name, k)
+    assert ref.stats["pairs_scored"] > 4e8 and ref.stats["edges"] > 1e7 and ref.stats["undefined"] == 0
+    # row windows (what N>1 ranks score) concatenate to the full run
+    calc.set_kernel(edge.KERNEL_TILED2)
+    cuts = [0, 20_000, 50_001, 77_777, b.n]
+    parts = [calc.score_band(r0, r1, amb_cap=0) for r0, r1 in zip(cuts[:-1], cuts[1:])]
+    assert (np.concatenate([p.words for p in parts]) == ref.words).all()
+    # a sample of band pairs against the oracle, every field
+    rng = np.random.default_rng(5)
+    i = rng.integers(5000, b.n, 200_000).astype(np.int32)
+    j = (i - rng.integers(1, 4000, i.size)).astype(np.int32)
+    dev = calc.score_pairs(i, j)
+    orc = pyoracle.Oracle(b, **kw).pairs(i, j)
+    common.assert_pairs_equal(dev, orc, "C2-sample")
+    assert (np.array([ref.edge(int(a), int(c)) for a, c in zip(i[:5000], j[:5000])]) == (orc["edge"][:5000] == 1)).all()
