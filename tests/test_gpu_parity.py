@@ -272,3 +272,29 @@ def test_full_size_C2_three_kernels_agree():
     orc = pyoracle.Oracle(b, **kw).pairs(i, j)
     common.assert_pairs_equal(dev, orc, "C2-sample")
     assert (np.array([ref.edge(int(a), int(c)) for a, c in zip(i[:5000], j[:5000])]) == (orc["edge"][:5000] == 1)).all()
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_long_super_read_like_batch(seed):
+    """BASELINE configs[4] shape: a few dozen records of 1-9.7 kb, most named Clique_* (cutoffs 0.99 / 0.97, min overlap
+    0.9), long sequential products down to the underflow zone. Too long for a shared-memory tile: AUTO takes the generic
+    walker for them; every pair against the oracle, every field."""
+    b = synth.quasispecies(70, genome_len=9719, read_len=3200, frag_mean=5200.0, frag_sd=1800.0, frag_min=900, frag_max=9719,
+                           indel_err=2e-4, clip_frac=0.05, seed=900 + seed)
+    rng = np.random.default_rng(seed)
+    b.is_clique[:] = (rng.random(b.n) < 0.7).astype(b.is_clique.dtype)
+    for no_prob0 in (True, False):
+        kw = dict(noProb0=no_prob0, maxPosition=b.max_position(), overlap=0.5, overlap_single=0.3,
+                  edge_quasi_cutoff=0.97, edge_quasi_cutoff_mixed=0.95, edge_quasi_cutoff_single=0.9)
+        calc = edge.NewEdgeCalculator(**kw)
+        adj = calc.scoreBatch(b)
+        pi, pj = common.tri_pairs(b.n)
+        dev = calc.score_pairs(pi, pj)
+        O = pyoracle.Oracle(b, **kw)
+        orc = O.pairs(pi, pj)
+        flips = common.assert_pairs_equal(dev, orc, "long-reads")
+        assert int(orc["cc"].max()) > 3000
+        if flips == 0:
+            e = orc["edge"] == 1
+            ai, aj = adj.edges()
+            assert adj.count() == int(e.sum()) and (ai == pi[e]).all() and (aj == pj[e]).all()
