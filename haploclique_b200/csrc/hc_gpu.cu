@@ -555,17 +555,7 @@ DevParams dev_params(const hc_ctx* c) {
     return P;
 }
 
-// f(begin, end) over [0, n) on up to 8 host threads (the per-upload layout work: binary searches and window sorts)
-template <class F>
-void parallel_ranges(int n, int min_per_thread, F f) {
-    int T = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 8u);
-    T = std::max(1, std::min(T, n / std::max(1, min_per_thread)));
-    if (T <= 1) { f(0, n); return; }
-    std::vector<std::thread> pool;
-    for (int t = 1; t < T; ++t) pool.emplace_back([=, &f] { f((int)((long long)n * t / T), (int)((long long)n * (t + 1) / T)); });
-    f(0, (int)((long long)n / T));
-    for (auto& th : pool) th.join();
-}
+using hc::parallel_ranges;
 
 int compute_layout(hc_ctx* c, int row_begin, int row_end) {
     if (c->lay_begin == row_begin && c->lay_end == row_end) return HC_OK;
@@ -664,7 +654,11 @@ int split_max_k() {
     static const int v = [] { const char* e = std::getenv("HC_T2_SPLIT_MAXK"); return e ? std::atoi(e) : tile2::kSplitMaxK; }();
     return std::min(v, 32);
 }
-uint32_t tile2_row_bytes(int K) { return K <= split_max_k() ? 256u : 8u * (uint32_t)K; }
+int row_pad() {      // extra doubles per table row (HC_T2_ROWPAD, experiments on the bank mapping of neighbouring rows)
+    static const int v = [] { const char* e = std::getenv("HC_T2_ROWPAD"); return e ? std::max(0, std::atoi(e)) : 0; }();
+    return v;
+}
+uint32_t tile2_row_bytes(int K) { return K <= split_max_k() ? 256u : 8u * (uint32_t)(K + row_pad()); }
 uint32_t tile2_entry_bytes(int K) { return K <= split_max_k() ? 4u : 8u; }
 size_t tile2_table_words(int K) { return (size_t)tile2::kRows * K * tile2_row_bytes(K) / 4; }
 
@@ -944,8 +938,9 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
                         tab7[row * 64 + b] = (uint32_t)bits;
                         tab7[row * 64 + 32 + b] = (uint32_t)(bits >> 32);
                     } else {                           // K doubles
-                        tab7[(row * K + b) * 2] = (uint32_t)bits;
-                        tab7[(row * K + b) * 2 + 1] = (uint32_t)(bits >> 32);
+                        const size_t Kp = tile2_row_bytes(K) / 8;
+                        tab7[(row * Kp + b) * 2] = (uint32_t)bits;
+                        tab7[(row * Kp + b) * 2 + 1] = (uint32_t)(bits >> 32);
                     }
                 }
         const long long nrec = (long long)p->n_ops_total + 64;

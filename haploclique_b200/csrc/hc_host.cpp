@@ -127,25 +127,37 @@ int hc_pack(const hc_reads* rd, hc_packed** out) {
     std::memset(p, 0, sizeof(*p));
     p->owner = own;
 
-    // pass 1: which quality chars occur -> dense codes; total op count
-    // Every read's op stream starts on a 16-byte boundary (8 records) so that one TMA bulk copy moves it
-    bool seen[256] = {false};
-    int64_t total_ops = 0;
+    // pass 1: which quality chars occur -> dense codes; where each read's op stream starts.
+    // Every read's op stream starts on a 16-byte boundary (8 records) so that one TMA bulk copy moves it.
+    // Both passes run on up to 8 host threads (reads are independent once the start offsets are known).
+    std::vector<int64_t> start(static_cast<size_t>(n) + 1, 0);
     for (int r = 0; r < n; ++r) {
-        const int nseg = rd->single_end[r] ? 1 : 2;
-        for (int s = 0; s < nseg; ++s) {
+        int64_t ops = 0;
+        for (int s = 0; s < (rd->single_end[r] ? 1 : 2); ++s) {
             const int k = 2 * r + s;
-            const uint8_t* q = rd->qual + rd->seq_off[k];
-            for (int t = 0; t < rd->seq_len[k]; ++t) seen[q[t]] = true;
             if (rd->cig_len[k] < 0 || rd->cig_len[k] > 65534) {
                 hc::set_global_error("hc_pack: a segment's unrolled CIGAR is longer than 65534 ops");
                 hc_packed_free(p);
                 return HC_E_INVALID;
             }
-            total_ops += rd->cig_len[k];
+            ops += rd->cig_len[k];
         }
-        total_ops = (total_ops + 7) & ~int64_t(7);
+        start[r + 1] = (start[r] + ops + 7) & ~int64_t(7);
     }
+    const int64_t total_ops = start[n];
+    std::mutex mu;
+    bool seen[256] = {false};
+    hc::parallel_ranges(n, 2048, [&](int r0, int r1) {
+        bool mine[256] = {false};
+        for (int r = r0; r < r1; ++r)
+            for (int s = 0; s < (rd->single_end[r] ? 1 : 2); ++s) {
+                const int k = 2 * r + s;
+                const uint8_t* q = rd->qual + rd->seq_off[k];
+                for (int t = 0; t < rd->seq_len[k]; ++t) mine[q[t]] = true;
+            }
+        std::lock_guard<std::mutex> lk(mu);
+        for (int c = 0; c < 256; ++c) seen[c] |= mine[c];
+    });
     int code_of[256];
     int K = 0;
     for (int c = 0; c < 256; ++c) {
@@ -172,66 +184,74 @@ int hc_pack(const hc_reads* rd, hc_packed** out) {
     }
     hc_read_hdr* hdr_out = static_cast<hc_read_hdr*>(own->hdr.p);
     uint16_t* ops_out = static_cast<uint16_t*>(own->ops.p);
-    std::memset(ops_out, 0, sizeof(uint16_t) * (static_cast<size_t>(total_ops) + 64));
+    std::memset(ops_out + total_ops, 0, sizeof(uint16_t) * 64);
 
     // pass 2: headers and op records
-    int64_t w = 0;
     int max_ops = 0;
-    for (int r = 0; r < n; ++r) {
-        hc_read_hdr& h = hdr_out[r];
-        std::memset(&h, 0, sizeof(h));
-        const bool single = rd->single_end[r] != 0;
-        h.ncov_flags = (static_cast<uint32_t>(rd->ncov[r]) & 0x3fffffffu) | (single ? HC_FLAG_SINGLE_END : 0u) |
-                       (rd->is_clique[r] ? HC_FLAG_IS_CLIQUE : 0u);
-        h.cov_first = rd->cov_first[r];
-        h.cov_last = rd->cov_last[r];
-        int read_ops = 0;
-        for (int s = 0; s < (single ? 1 : 2); ++s) {
-            const int k = 2 * r + s;
-            const uint8_t* cg = rd->cig + rd->cig_off[k];
-            const uint8_t* sq = rd->seq + rd->seq_off[k];
-            const uint8_t* ql = rd->qual + rd->seq_off[k];
-            const int nc = rd->cig_len[k], nq = rd->seq_len[k];
-            int lead = 0, trail = 0;
-            while (lead < nc && (cg[lead] == 'S' || cg[lead] == 'H')) ++lead;
-            while (trail < nc && (cg[nc - 1 - trail] == 'S' || cg[nc - 1 - trail] == 'H')) ++trail;
-            h.raw[2 * s] = rd->seg_start[k];
-            h.raw[2 * s + 1] = rd->seg_end[k];
-            h.ext[2 * s] = rd->seg_start[k] - lead;
-            h.ext[2 * s + 1] = rd->seg_end[k] + trail;
-            h.ops_off[s] = static_cast<uint32_t>(w);
-            h.n_ops[s] = nc;
-            int qi = 0;
-            bool ins = false, plain = true;      // plain: only M between the leading and the trailing clip run
-            for (int t = 0; t < nc; ++t) {
-                const int op = op_code(cg[t]);
-                if (op < 0) {
-                    hc::set_global_error(std::string("hc_pack: CIGAR op '") + static_cast<char>(cg[t]) +
-                                         "' is outside MIDSH (the reference's walk does not define it)");
-                    hc_packed_free(p);
-                    return HC_E_INVALID;
-                }
-                uint16_t rec = static_cast<uint16_t>(op << HC_OP_SHIFT);
-                if (op == HC_OP_M || op == HC_OP_I || op == HC_OP_S) {
-                    if (qi >= nq) {
-                        hc::set_global_error("hc_pack: CIGAR consumes more query bases than the read has");
-                        hc_packed_free(p);
-                        return HC_E_INVALID;
+    std::string error;
+    hc::parallel_ranges(n, 2048, [&](int r0, int r1) {
+        int my_max = 0;
+        std::string my_error;
+        for (int r = r0; r < r1 && my_error.empty(); ++r) {
+            int64_t w = start[r];
+            hc_read_hdr& h = hdr_out[r];
+            std::memset(&h, 0, sizeof(h));
+            const bool single = rd->single_end[r] != 0;
+            h.ncov_flags = (static_cast<uint32_t>(rd->ncov[r]) & 0x3fffffffu) | (single ? HC_FLAG_SINGLE_END : 0u) |
+                           (rd->is_clique[r] ? HC_FLAG_IS_CLIQUE : 0u);
+            h.cov_first = rd->cov_first[r];
+            h.cov_last = rd->cov_last[r];
+            int read_ops = 0;
+            for (int s = 0; s < (single ? 1 : 2) && my_error.empty(); ++s) {
+                const int k = 2 * r + s;
+                const uint8_t* cg = rd->cig + rd->cig_off[k];
+                const uint8_t* sq = rd->seq + rd->seq_off[k];
+                const uint8_t* ql = rd->qual + rd->seq_off[k];
+                const int nc = rd->cig_len[k], nq = rd->seq_len[k];
+                int lead = 0, trail = 0;
+                while (lead < nc && (cg[lead] == 'S' || cg[lead] == 'H')) ++lead;
+                while (trail < nc && (cg[nc - 1 - trail] == 'S' || cg[nc - 1 - trail] == 'H')) ++trail;
+                h.raw[2 * s] = rd->seg_start[k];
+                h.raw[2 * s + 1] = rd->seg_end[k];
+                h.ext[2 * s] = rd->seg_start[k] - lead;
+                h.ext[2 * s + 1] = rd->seg_end[k] + trail;
+                h.ops_off[s] = static_cast<uint32_t>(w);
+                h.n_ops[s] = nc;
+                int qi = 0;
+                bool ins = false, plain = true;      // plain: only M between the leading and the trailing clip run
+                for (int t = 0; t < nc; ++t) {
+                    const int op = op_code(cg[t]);
+                    if (op < 0) {
+                        my_error = std::string("hc_pack: CIGAR op '") + static_cast<char>(cg[t]) +
+                                   "' is outside MIDSH (the reference's walk does not define it)";
+                        break;
                     }
-                    rec |= static_cast<uint16_t>(base_code(sq[qi]) << HC_BASE_SHIFT) | static_cast<uint16_t>(code_of[ql[qi]] << HC_QUAL_SHIFT);
-                    ++qi;
+                    uint16_t rec = static_cast<uint16_t>(op << HC_OP_SHIFT);
+                    if (op == HC_OP_M || op == HC_OP_I || op == HC_OP_S) {
+                        if (qi >= nq) { my_error = "hc_pack: CIGAR consumes more query bases than the read has"; break; }
+                        rec |= static_cast<uint16_t>(base_code(sq[qi]) << HC_BASE_SHIFT) | static_cast<uint16_t>(code_of[ql[qi]] << HC_QUAL_SHIFT);
+                        ++qi;
+                    }
+                    ins |= (op == HC_OP_I);
+                    if (t >= lead && t < nc - trail && op != HC_OP_M) plain = false;
+                    ops_out[static_cast<size_t>(w++)] = rec;
                 }
-                ins |= (op == HC_OP_I);
-                if (t >= lead && t < nc - trail && op != HC_OP_M) plain = false;
-                ops_out[static_cast<size_t>(w++)] = rec;
+                if (lead + trail > nc) plain = false;             // a segment made of clips only
+                h.seg_flags[s] = static_cast<uint16_t>((ins ? HC_SEG_HAS_INS : 0) | (plain ? 0 : HC_SEG_NOT_PLAIN));
+                read_ops += nc;
             }
-            if (lead + trail > nc) plain = false;             // a segment made of clips only
-            h.seg_flags[s] = static_cast<uint16_t>((ins ? HC_SEG_HAS_INS : 0) | (plain ? 0 : HC_SEG_NOT_PLAIN));
-            read_ops += nc;
+            if (single) h.ops_off[1] = static_cast<uint32_t>(w);
+            while (w < start[r + 1]) ops_out[static_cast<size_t>(w++)] = 0;      // the alignment padding behind the read
+            if (read_ops > my_max) my_max = read_ops;
         }
-        if (single) h.ops_off[1] = static_cast<uint32_t>(w);
-        w = (w + 7) & ~int64_t(7);
-        if (read_ops > max_ops) max_ops = read_ops;
+        std::lock_guard<std::mutex> lk(mu);
+        if (my_max > max_ops) max_ops = my_max;
+        if (!my_error.empty() && error.empty()) error = my_error;
+    });
+    if (!error.empty()) {
+        hc::set_global_error(error);
+        hc_packed_free(p);
+        return HC_E_INVALID;
     }
     p->n_reads = n;
     p->n_qual_codes = K;

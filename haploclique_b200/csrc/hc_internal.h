@@ -1,6 +1,8 @@
 // Library-private declarations shared by the host packer (hc_host.cpp) and the CUDA side (hc_gpu.cu).
 #pragma once
+#include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/hc_edge.h"
@@ -29,6 +31,18 @@ struct HostBuf {
     void release();
     ~HostBuf() { release(); }
 };
+
+// f(begin, end) over [0, n) on up to 8 host threads (per-batch host work: packing, band layout, work items).
+template <class F>
+void parallel_ranges(int n, int min_per_thread, F f) {
+    int T = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 8u);
+    T = std::max(1, std::min(T, n / std::max(1, min_per_thread)));
+    if (T <= 1) { f(0, n); return; }
+    std::vector<std::thread> pool;
+    for (int t = 1; t < T; ++t) pool.emplace_back([=, &f] { f((int)((long long)n * t / T), (int)((long long)n * (t + 1) / T)); });
+    f(0, (int)((long long)n / T));
+    for (auto& th : pool) th.join();
+}
 
 struct PackedOwner {
     HostBuf hdr, ops;
