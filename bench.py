@@ -43,6 +43,7 @@ UNIT = "pairs/s"
 PARAMS = dict(edge_quasi_cutoff=0.99, overlap=0.9, edge_quasi_cutoff_single=0.95, overlap_single=0.6,
               edge_quasi_cutoff_mixed=0.97, noProb0=True)   # defaults + --no_prob0 (edges must exist)
 HALO = 1000                                                 # >= longest fragment span (800) + clips
+MAX_WORDS = 1 << 29                                         # adjacency words per row window (2 GiB)
 
 
 def workload_name(args, world):
@@ -202,9 +203,26 @@ def main():
     packed = edge.PackedBatch(local)
     pack_s = time.perf_counter() - t0
     calc.upload(packed)
-    _, _, nw = calc.band_layout(row_begin, row_end)
-    pinned = edge.PinnedBuffer(max(nw, 1), np.uint32)
+    # the adjacency band is produced in row windows of at most MAX_WORDS 32-bit words (one window for C2/C3; the dense
+    # amplicon C4 at full size has 1.6e10 words): each window is scored and, in the e2e leg, copied to the same pinned buffer
+    _, off, nw = calc.band_layout(row_begin, row_end)
+    cuts = [row_begin]
+    while cuts[-1] < row_end:
+        k0 = cuts[-1] - row_begin
+        k1 = int(np.searchsorted(off, off[k0] + MAX_WORDS, side="right")) - 1
+        cuts.append(row_begin + max(k1, k0 + 1))
+    cuts[-1] = min(cuts[-1], row_end)
+    windows = list(zip(cuts[:-1], cuts[1:]))
+    win_words = max(int(off[b - row_begin] - off[a - row_begin]) for a, b in windows) if windows else 1
+    pinned = edge.PinnedBuffer(max(win_words, 1), np.uint32)
     L, ctx = calc.L, calc._ctx
+
+    def score_windows(**kw):
+        tot = None
+        for a, b in windows:
+            st = calc.score_band(a, b, **kw).stats
+            tot = dict(st) if tot is None else {k: tot[k] + st[k] for k in st}
+        return tot
 
     def barrier():
         torch.cuda.synchronize()
@@ -213,15 +231,15 @@ def main():
 
     def step_resident():
         L.hc_l2_flush(ctx)
-        return calc.score_band(row_begin, row_end, fetch=False, amb_cap=0).stats
+        return score_windows(fetch=False, amb_cap=0)
 
     def step_e2e():
         L.hc_l2_flush(ctx)
         torch.cuda.synchronize()
         t = time.perf_counter()
         calc.upload(packed)
-        adj = calc.score_band(row_begin, row_end, out=pinned.array, amb_cap=1024)
-        return time.perf_counter() - t, adj
+        st = score_windows(out=pinned.array, amb_cap=1024)
+        return time.perf_counter() - t, st
 
     warm = max(args.warmup, 3)
     for _ in range(warm):
@@ -284,7 +302,7 @@ def main():
             "warmup": warm, "ms_per_step": ms_kernel, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_text(wname, cfg), "params": "defaults + no_prob0", "kernel": kernel_used,
-                       "l2": "flushed between steps (256 MiB memset)",
+                       "l2": "flushed between steps (256 MiB memset)", "row_windows": len(windows),
                        "sharding": ("%d genome-position windows + %d-column left halo, no collective" % (world, HALO)) if world > 1 else "single GPU"},
             "pairs": {"scored": scored, "examined": total, "walked": walked, "edges": edges, "sum_cc": sum_cc, "sum_tc": sum_tc,
                       "rows": rows, "ambiguous_within_1e-12": amb, "undefined": undef},
