@@ -926,6 +926,18 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     std::vector<uint32_t> tab7;
     if (tile2_table_words(K) * 4 + 65536 <= c->smem_optin && c->d_simpson == nullptr) {
         tab7.assign(tile2_table_words(K), 0u);
+        // order of the quality codes inside a table row (HC_T2_PERM, experiments on bank conflicts): 0 identity,
+        // 1 even codes first, 2 reversed, 3 stride 5
+        tile2::ColumnOrder ord{};
+        {
+            static const int mode = [] { const char* e = std::getenv("HC_T2_PERM"); return e ? std::atoi(e) : 0; }();
+            std::vector<int> seq(K);
+            for (int q = 0; q < K; ++q) seq[q] = q;
+            if (mode == 1) { int w = 0; for (int q = 0; q < K; q += 2) seq[w++] = q; for (int q = 1; q < K; q += 2) seq[w++] = q; }
+            else if (mode == 2) std::reverse(seq.begin(), seq.end());
+            else if (mode == 3) { std::vector<int> t; for (int s0 = 0; s0 < 5; ++s0) for (int q = s0; q < K; q += 5) t.push_back(q); seq = t; }
+            for (int pos = 0; pos < K; ++pos) ord.slot[seq[pos]] = (uint8_t)pos;
+        }
         const bool split = K <= split_max_k();
         for (int a = 0; a < K; ++a)
             for (int r = 0; r < tile2::kRows; ++r)
@@ -935,12 +947,12 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
                     std::memcpy(&bits, &v, 8);
                     const size_t row = (size_t)a * tile2::kRows + r;
                     if (split) {                       // 32 low words, then 32 high words
-                        tab7[row * 64 + b] = (uint32_t)bits;
-                        tab7[row * 64 + 32 + b] = (uint32_t)(bits >> 32);
+                        tab7[row * 64 + ord.slot[b]] = (uint32_t)bits;
+                        tab7[row * 64 + 32 + ord.slot[b]] = (uint32_t)(bits >> 32);
                     } else {                           // K doubles
                         const size_t Kp = tile2_row_bytes(K) / 8;
-                        tab7[(row * Kp + b) * 2] = (uint32_t)bits;
-                        tab7[(row * Kp + b) * 2 + 1] = (uint32_t)(bits >> 32);
+                        tab7[(row * Kp + ord.slot[b]) * 2] = (uint32_t)bits;
+                        tab7[(row * Kp + ord.slot[b]) * 2 + 1] = (uint32_t)(bits >> 32);
                     }
                 }
         const long long nrec = (long long)p->n_ops_total + 64;
@@ -949,7 +961,7 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
         if ((rc = grow(c, c->d_opsA, c->cap_opsA, (size_t)nrec)) != HC_OK) return rc;
         if ((rc = grow(c, c->d_opsF, c->cap_opsF, (size_t)nrec)) != HC_OK) return rc;
         c->have_formats = true;
-        tile2::build_formats_kernel<<<(unsigned)((nrec + 255) / 256), 256, 0, c->stream>>>(c->d_ops, nrec, tile2_row_bytes(K), tile2_entry_bytes(K), c->d_opsA, c->d_opsF);
+        tile2::build_formats_kernel<<<(unsigned)((nrec + 255) / 256), 256, 0, c->stream>>>(c->d_ops, nrec, tile2_row_bytes(K), tile2_entry_bytes(K), ord, c->d_opsA, c->d_opsF);
         CU_TRY(c, cudaGetLastError());
     }
     c->cov_first.resize(p->n_reads);

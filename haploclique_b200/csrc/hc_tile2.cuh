@@ -44,7 +44,9 @@ struct Args2 : tile::Args {
 constexpr int kRows = 9;
 
 // ---- row / column formats, built on the device once per upload ---------------------------------------
-__global__ void build_formats_kernel(const uint16_t* __restrict__ ops, long long n, uint32_t ROW, uint32_t ESZ,
+struct ColumnOrder { uint8_t slot[128]; };   // position of quality code q inside a table row (a permutation of 0..K-1)
+
+__global__ void build_formats_kernel(const uint16_t* __restrict__ ops, long long n, uint32_t ROW, uint32_t ESZ, ColumnOrder ord,
                                      uint32_t* __restrict__ opsA, uint16_t* __restrict__ opsF) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
@@ -52,7 +54,7 @@ __global__ void build_formats_kernel(const uint16_t* __restrict__ ops, long long
     const uint32_t base = HC_REC_BASE(r), op = HC_REC_OP(r), q = HC_REC_QUAL(r);
     const bool esc = op != HC_OP_M || base > 4u;
     opsA[t] = esc ? A_ESC : ROW * (q * 9u + 4u - base);
-    opsF[t] = (uint16_t)(esc ? B_ESC : ROW * base + ESZ * q);
+    opsF[t] = (uint16_t)(esc ? B_ESC : ROW * base + ESZ * ord.slot[q]);
 }
 
 // The lock-step loop of one slot (see tile::overlap for the contract; same results, different operand format).
