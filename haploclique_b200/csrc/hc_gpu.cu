@@ -684,7 +684,7 @@ Tile2Geom tile2_geometry(const hc_ctx* c) {
 }
 
 bool tile2_eligible(const hc_ctx* c) {
-    if (c->d_simpson != nullptr || !c->have_formats) return false;
+    if (!c->have_formats) return false;        // an allele-frequency map is fine here: the MAP variant walks the tails
     return tile2_geometry(c).nwarps > 0;
 }
 
@@ -924,7 +924,7 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     // 9 rows per first quality (un x4, EQ, un x4), low words then high words. Skipped when the table alone
     // would not fit a CTA's shared memory (the kernel is then not eligible).
     std::vector<uint32_t> tab7;
-    if (tile2_table_words(K) * 4 + 65536 <= c->smem_optin && c->d_simpson == nullptr) {
+    if (tile2_table_words(K) * 4 + 65536 <= c->smem_optin) {
         tab7.assign(tile2_table_words(K), 0u);
         // order of the quality codes inside a table row (HC_T2_PERM, experiments on bank conflicts): 0 identity,
         // 1 even codes first, 2 reversed, 3 stride 5
@@ -1045,7 +1045,9 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
         int per_sm = 0;
         const bool split = c->K <= split_max_k();
         if (use_tile2) {
-            auto kern = split ? tile2::score_tile2_kernel<true> : tile2::score_tile2_kernel<false>;
+            const bool map = c->d_simpson != nullptr;
+            auto kern = split ? (map ? tile2::score_tile2_kernel<true, true> : tile2::score_tile2_kernel<true, false>)
+                              : (map ? tile2::score_tile2_kernel<false, true> : tile2::score_tile2_kernel<false, false>);
             CU_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
             CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem_bytes));
         } else {
@@ -1077,8 +1079,11 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
         CU_TRY(c, cudaEventRecord(c->ev0, c->stream));
         if (n_items > 0) {
             const int blocks = (int)std::min<size_t>(n_items, (size_t)n_ctas);
-            if (use_tile2 && split) tile2::score_tile2_kernel<true><<<blocks, threads, smem_bytes, c->stream>>>(a);
-            else if (use_tile2) tile2::score_tile2_kernel<false><<<blocks, threads, smem_bytes, c->stream>>>(a);
+            const bool map = c->d_simpson != nullptr;
+            if (use_tile2 && split && map) tile2::score_tile2_kernel<true, true><<<blocks, threads, smem_bytes, c->stream>>>(a);
+            else if (use_tile2 && split) tile2::score_tile2_kernel<true, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
+            else if (use_tile2 && map) tile2::score_tile2_kernel<false, true><<<blocks, threads, smem_bytes, c->stream>>>(a);
+            else if (use_tile2) tile2::score_tile2_kernel<false, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
             else tile::score_tile_kernel<<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
             CU_TRY(c, cudaGetLastError());
             launches = 1;

@@ -145,13 +145,15 @@ __device__ __forceinline__ void tail(const Args& a, const int* hA, const int* hB
 }
 
 // One of the cheap (non-loop) micro-ops. `shape` carries checkGapsSingle's case between SPRE/SOVL/SPOST.
-__device__ __forceinline__ void cheap(const Args& a, const int* hA, const int* hB, int rA, int rB, uint32_t m, Lane& L, int& shape) {
+// TF: how a run of noOverlapCheckgap steps is evaluated -- tf(side, seg, exclusive limit, L).
+template <class TF>
+__device__ __forceinline__ void cheap_with(const int* hA, const int* hB, uint32_t m, Lane& L, int& shape, TF& tf) {
     const uint32_t op = m & 15u;
     if (op == M_NOP || L.gap || L.undef) return;
     const int x = (m >> 4) & 1, y = (m >> 5) & 1, ia = (m >> 6) & 15, ib = (m >> 10) & 15;
     switch (op) {
         case M_START: L.ref = bound(hA, hB, ia); break;
-        case M_TLT: tail(a, hA, hB, rA, rB, x, y, bound(hA, hB, ia), L); break;
+        case M_TLT: tf(x, y, bound(hA, hB, ia), L); break;
         case M_SEAT: {
             const int* h = x ? hB : hA;
             const int st = x ? 32 : 1;
@@ -162,7 +164,7 @@ __device__ __forceinline__ void cheap(const Args& a, const int* hA, const int* h
             int which = -1;
             if (L.ref - 1 == bound(hA, hB, ia)) which = ib;
             else if (L.ref - 1 == bound(hA, hB, ib)) which = ia;
-            if (which >= 0) tail(a, hA, hB, rA, rB, (which >> 2) & 1, (which >> 1) & 1, bound(hA, hB, which) + 1, L);
+            if (which >= 0) tf((which >> 2) & 1, (which >> 1) & 1, bound(hA, hB, which) + 1, L);
             break;
         }
         case M_SPRE: {                               // checkGapsSingle (:269-395): shape, fresh cursors, leading tail
@@ -173,17 +175,26 @@ __device__ __forceinline__ void cheap(const Args& a, const int* hA, const int* h
             else shape = 3;
             set_cur(L, 0, x, 0);
             set_cur(L, 1, y, 0);
-            if (shape < 2) { L.ref = xs1; tail(a, hA, hB, rA, rB, 0, x, xs2, L); }
-            else { L.ref = xs2; tail(a, hA, hB, rA, rB, 1, y, xs1, L); }
+            if (shape < 2) { L.ref = xs1; tf(0, x, xs2, L); }
+            else { L.ref = xs2; tf(1, y, xs1, L); }
             break;
         }
         case M_SPOST: {
-            if (shape == 0 || shape == 2) tail(a, hA, hB, rA, rB, 1, y, hB[(5 + 2 * y) * 32] + 1, L);
-            else tail(a, hA, hB, rA, rB, 0, x, hA[5 + 2 * x] + 1, L);
+            if (shape == 0 || shape == 2) tf(1, y, hB[(5 + 2 * y) * 32] + 1, L);
+            else tf(0, x, hA[5 + 2 * x] + 1, L);
             break;
         }
         default: break;
     }
+}
+
+struct TailO1 {            // the O(1) evaluation from prefix counts (no allele-frequency map)
+    const Args& a; const int* hA; const int* hB; int rA, rB;
+    __device__ __forceinline__ void operator()(int side, int seg, int limit, Lane& L) const { tail(a, hA, hB, rA, rB, side, seg, limit, L); }
+};
+__device__ __forceinline__ void cheap(const Args& a, const int* hA, const int* hB, int rA, int rB, uint32_t m, Lane& L, int& shape) {
+    TailO1 tf{a, hA, hB, rA, rB};
+    cheap_with(hA, hB, m, L, shape, tf);
 }
 
 __device__ __forceinline__ bool consumes_q(uint32_t op) { return op == HC_OP_M || op == HC_OP_I || op == HC_OP_S; }

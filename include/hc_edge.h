@@ -187,13 +187,14 @@ int hc_score_band(hc_ctx* ctx, int32_t row_begin, int32_t row_end, uint32_t* adj
 int hc_score_band_detail(hc_ctx* ctx, int32_t row_begin, int32_t row_end, uint32_t* adj, hc_pair_result* detail,
                          int64_t n_words, hc_band_stats* stats);
 
-/* Which band kernel hc_score_band uses. AUTO: a tiled kernel (shared-memory column tiles, TMA-fed rows) when
- * the batch is eligible -- no allele-frequency map, and the tables plus the longest read fit a CTA's shared
- * memory -- else the generic one-lane-per-pair walker. Of the two tiled kernels AUTO prefers TILED2 (operands
- * stored as table-address addends, 9-row table: 72*K*K bytes (or 2304*K with the split-word layout, K <= 32) for K quality codes) and falls back to TILED
- * (16-bit op records, 16*K*K bytes of tables) when K is too large for it. GENERIC / TILED / TILED2 force one;
- * a forced tiled kernel fails with HC_E_STATE when not eligible. All three produce identical results.
- * hc_last_kernel: the kernel the last hc_score_band call launched (0 = none). */
+/* Which band kernel hc_score_band uses. AUTO: a tiled kernel (shared-memory column tiles, TMA-fed rows) when the batch
+ * is eligible -- the tables plus the longest read fit a CTA's shared memory -- else the generic one-lane-per-pair
+ * walker. Of the two tiled kernels AUTO prefers TILED2 (operands stored as table-address addends; 9-row table of
+ * 72*K*K bytes for K quality codes; walks the tail columns when the context has an allele-frequency map) and falls
+ * back to TILED (16-bit op records, 16*K*K bytes of tables; contexts without allele-frequency map only) when K is
+ * too large for TILED2. GENERIC / TILED / TILED2 force one; a forced tiled kernel fails with HC_E_STATE when not
+ * eligible. All three produce identical results. hc_last_kernel: the kernel the last hc_score_band call launched
+ * (0 = none). */
 enum { HC_KERNEL_AUTO = 0, HC_KERNEL_GENERIC = 1, HC_KERNEL_TILED = 2, HC_KERNEL_TILED2 = 3 };
 int hc_set_kernel(hc_ctx* ctx, int32_t mode);
 int hc_last_kernel(const hc_ctx* ctx);
