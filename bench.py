@@ -4,6 +4,9 @@
 Workloads (synthetic, seeded; `config.workload` names the one used):
   C2  HIV-1 9.7 kb, 5 haplotypes, 100k 2x250 fragments                      -- N=1 (BASELINE configs[1])
   C3  the same mix at 1M fragments, sharded by genome-position windows      -- N>1 (BASELINE configs[2])
+  C4  1.5 kb amplicon, 1M fragments = 2M 2x150 reads, dense tiles           -- --workload C4 (BASELINE configs[3])
+  C5  a super-read round: 4000 records of 0.5-9.7 kb, 70 % merged cliques, 76 quality codes -- --workload C5
+      (BASELINE configs[4]; N>1: every rank holds the set and scores an equal-area block of rows)
 A step = one pass of the hot path over the whole read set: every ordered pair (later read i, earlier read j) inside
 the sorted-start band is decided exactly as NewEdgeCalculator::edgeBetween would and the banded adjacency bitset is
 produced. "Scored" pairs = pairs that pass the reference's first reject (covered intervals intersect,
@@ -53,6 +56,15 @@ def workload_name(args, world):
 def make_workload(name, n_frag, rank=0, world=1):
     """Returns (local batch, first local row this rank owns, config dict). world == 1: the whole read set."""
     from haploclique_b200 import synth
+    if name == "C5":
+        kw = dict(synth.C5)
+        n = n_frag or kw["n_frag"]
+        b = synth.super_reads(n, **{k: v for k, v in kw.items() if k != "n_frag"})
+        # every read overlaps most others: no position windows; rank r scores rows [cut_r, cut_r+1) of equal pair area
+        cuts = [int(round(b.n * np.sqrt(r / world))) for r in range(world + 1)]
+        if world > 1:
+            b = b.permute(np.arange(0, cuts[rank + 1]))
+        return b, cuts[rank], dict(kw, n_frag=n)
     kw = dict(synth.CONFIGS[name])
     if n_frag:
         kw["n_frag"] = n_frag
@@ -137,6 +149,9 @@ def run_cpu(batch, steps, warmup, threads, max_position):
 
 
 def workload_text(name, cfg):
+    if name == "C5":
+        return "C5: synthetic super-read round, %d records of %d-%d columns (70 %% Clique_*, posterior qualities up to char 126), genome %d, seed 20261104" % (
+            cfg["n_frag"], cfg["frag_min"], cfg["frag_max"], cfg["genome_len"])
     return "%s: synthetic HIV-1 quasispecies, 5 haplotypes, %d fragments 2x%d bp, genome %d, seed 20261104" % (
         name, cfg["n_frag"], cfg["read_len"], cfg["genome_len"])
 
@@ -147,9 +162,9 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="auto", choices=["auto", "C2", "C3", "C4"])
+    ap.add_argument("--workload", default="auto", choices=["auto", "C2", "C3", "C4", "C5"])
     ap.add_argument("--n-frag", type=int, default=0, help="override the fragment count (debugging only)")
-    ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "tiled", "tiled2"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "tiled", "tiled2", "streamed"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -162,12 +177,13 @@ def main():
         if rank != 0:
             return 0
         from haploclique_b200 import synth
-        cfg = dict(synth.CONFIGS[wname])
+        cfg = dict(synth.C5 if wname == "C5" else synth.CONFIGS[wname])
         if args.n_frag:
             cfg["n_frag"] = args.n_frag
         # the CPU arm scores a bounded sample; a 100k-fragment draw of the same mix has the same local read density
         n_draw = min(cfg["n_frag"], 100_000)
-        batch = synth.quasispecies(n_draw, **{k: v for k, v in cfg.items() if k != "n_frag"})
+        gen = synth.super_reads if wname == "C5" else synth.quasispecies
+        batch = gen(n_draw, **{k: v for k, v in cfg.items() if k != "n_frag"})
         value, ms, kind, threads, desc = run_cpu(batch, max(args.steps, 1), min(args.warmup, 1), cores, batch.max_position())
         if n_draw != cfg["n_frag"]:
             desc += "; drawn at %d fragments: pairs/s of the CPU scorer does not depend on the set size" % n_draw
@@ -198,7 +214,8 @@ def main():
     max_position = cfg["genome_len"] + 2 * HALO
 
     calc = edge.NewEdgeCalculator(maxPosition=max_position, device=local_rank, **PARAMS)
-    calc.set_kernel({"auto": edge.KERNEL_AUTO, "generic": edge.KERNEL_GENERIC, "tiled": edge.KERNEL_TILED, "tiled2": edge.KERNEL_TILED2}[args.kernel])
+    calc.set_kernel({"auto": edge.KERNEL_AUTO, "generic": edge.KERNEL_GENERIC, "tiled": edge.KERNEL_TILED, "tiled2": edge.KERNEL_TILED2,
+                     "streamed": edge.KERNEL_STREAMED}[args.kernel])
     t0 = time.perf_counter()
     packed = edge.PackedBatch(local)
     pack_s = time.perf_counter() - t0
@@ -264,7 +281,7 @@ def main():
     barrier()
     sampler.stop_flag = True
     sampler.join(timeout=2)
-    kernel_used = {0: "none", 1: "generic", 2: "tiled", 3: "tiled2"}[calc.last_kernel()]
+    kernel_used = {0: "none", 1: "generic", 2: "tiled", 3: "tiled2", 4: "streamed"}[calc.last_kernel()]
     lds_gbs, dmul_s = edge.measure_peaks(local_rank) if rank == 0 else (0.0, 0.0)
 
     # whole-job numbers: units of all ranks / max-over-ranks time
@@ -303,7 +320,8 @@ def main():
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_text(wname, cfg), "params": "defaults + no_prob0", "kernel": kernel_used,
                        "l2": "flushed between steps (256 MiB memset)", "row_windows": len(windows),
-                       "sharding": ("%d genome-position windows + %d-column left halo, no collective" % (world, HALO)) if world > 1 else "single GPU"},
+                       "sharding": "single GPU" if world == 1 else ("%d equal-area row blocks of the replicated set, no collective" % world) if wname == "C5"
+                                   else ("%d genome-position windows + %d-column left halo, no collective" % (world, HALO))},
             "pairs": {"scored": scored, "examined": total, "walked": walked, "edges": edges, "sum_cc": sum_cc, "sum_tc": sum_tc,
                       "rows": rows, "ambiguous_within_1e-12": amb, "undefined": undef},
             "column_steps_per_s": (sum_cc + sum_tc) / secs,

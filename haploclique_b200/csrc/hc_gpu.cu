@@ -645,6 +645,29 @@ bool tile_eligible(const hc_ctx* c) {
     return tile_geometry(c).smem <= c->smem_optin;
 }
 
+// Streamed variant of the first-generation kernel: only the two probability tables, the programs and the headers live in
+// shared memory (16*K*K + ~7 KB: any K up to 118), the op streams are read in place. Takes the batches neither tiled kernel
+// can hold: super-read rounds (reads of several thousand columns, quality alphabets of 60-94 codes).
+TileGeom stream_geometry(const hc_ctx* c) {
+    TileGeom g;
+    g.maxw = 0;
+    g.abuf_bytes = 0;
+    size_t o = 0;
+    o += ((size_t)2 * c->K * c->K * 8 + 15) & ~(size_t)15;
+    o += (size_t)tile::TP_COUNT * tile::TP_WORDS * 4;
+    o += 16 * 32 * 4;
+    o += (size_t)tile::kWarps * 2 * 64;
+    o += tile::kWarps * 2 * 8;
+    o += 8 * 8;
+    o += 16;
+    g.smem = o;
+    return g;
+}
+bool stream_eligible(const hc_ctx* c) {
+    if (c->d_simpson != nullptr) return false;
+    return c->max_ops < 65536 && stream_geometry(c).smem <= c->smem_optin;
+}
+
 // Second-generation tiled kernel: 9-row table (2304*K bytes split, 72*K*K bytes as doubles), 32-bit row records. The warp count shrinks
 // (24 -> 8) until the CTA fits; below 8 warps the first-generation kernel or the generic walker takes over.
 struct Tile2Geom { int maxw, abuf_bytes, nwarps; size_t smem; };
@@ -981,7 +1004,7 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     for (int r = p->n_reads - 1; r >= 0; --r) { smin = std::min(smin, c->cov_first[r]); c->cov_first_smin[r] = smin; }
     // the band layout and the tiled kernels' work items of the whole batch depend on the headers only: computed here, on
     // the host, while the copies and the device-side builds above are in flight (hc_score_band(0, n) finds them cached)
-    if (p->n_reads > 1 && (tile_eligible(c) || tile2_eligible(c))) {
+    if (p->n_reads > 1 && (tile_eligible(c) || tile2_eligible(c) || stream_eligible(c))) {
         compute_layout(c, 0, p->n_reads);
         build_items(c, 0, p->n_reads, c->sm_count);
     }
@@ -1011,15 +1034,17 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
     const int nrows = row_end - row_begin;
     const long long total = c->lay_off[nrows];
     if ((adj || detail) && n_words < total) { c->err = "hc_score_band: output buffer smaller than hc_band_layout's n_words"; return HC_E_INVALID; }
-    const bool can_tile1 = tile_eligible(c), can_tile2 = tile2_eligible(c);
-    if ((c->kernel_mode == HC_KERNEL_TILED && !can_tile1) || (c->kernel_mode == HC_KERNEL_TILED2 && !can_tile2)) {
+    const bool can_tile1 = tile_eligible(c), can_tile2 = tile2_eligible(c), can_stream = stream_eligible(c);
+    if ((c->kernel_mode == HC_KERNEL_TILED && !can_tile1) || (c->kernel_mode == HC_KERNEL_TILED2 && !can_tile2) ||
+        (c->kernel_mode == HC_KERNEL_STREAMED && !can_stream)) {
         c->err = "hc_score_band: the tiled kernel was requested but this batch / parameter set is not eligible "
                  "(allele-frequency map set, or the tables and the column tile do not fit shared memory)";
         return HC_E_STATE;
     }
     const bool use_tile2 = can_tile2 && (c->kernel_mode == HC_KERNEL_AUTO || c->kernel_mode == HC_KERNEL_TILED2);
-    const bool use_tile1 = !use_tile2 && can_tile1 && c->kernel_mode != HC_KERNEL_GENERIC && c->kernel_mode != HC_KERNEL_TILED2;
-    const bool use_tile = use_tile1 || use_tile2;
+    const bool use_tile1 = !use_tile2 && can_tile1 && (c->kernel_mode == HC_KERNEL_AUTO || c->kernel_mode == HC_KERNEL_TILED);
+    const bool use_stream = !use_tile2 && !use_tile1 && can_stream && (c->kernel_mode == HC_KERNEL_AUTO || c->kernel_mode == HC_KERNEL_STREAMED);
+    const bool use_tile = use_tile1 || use_tile2 || use_stream;
     if (detail && !use_tile) { c->err = "hc_score_band_detail: only the tiled kernels write per-slot detail; use hc_score_pairs"; return HC_E_STATE; }
     int rc;
     size_t cap2 = c->rows_cap;
@@ -1038,7 +1063,7 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
     int launches = 0;
     c->last_kernel = 0;
     if (use_tile && total > 0) {
-        const TileGeom g = tile_geometry(c);
+        const TileGeom g = use_stream ? stream_geometry(c) : tile_geometry(c);
         const Tile2Geom g2 = tile2_geometry(c);
         const size_t smem_bytes = use_tile2 ? g2.smem : g.smem;
         const int threads = use_tile2 ? g2.nwarps * 32 : tile::kThreads;
@@ -1051,8 +1076,9 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
             CU_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
             CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem_bytes));
         } else {
-            CU_TRY(c, cudaFuncSetAttribute(tile::score_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-            CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile::score_tile_kernel, threads, smem_bytes));
+            auto kern = use_stream ? tile::score_tile_kernel<true> : tile::score_tile_kernel<false>;
+            CU_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+            CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem_bytes));
         }
         if (per_sm < 1) { c->err = "hc_score_band: tiled kernel does not fit on an SM"; return HC_E_CUDA; }
         const int n_ctas = c->sm_count * per_sm;
@@ -1084,10 +1110,11 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
             else if (use_tile2 && split) tile2::score_tile2_kernel<true, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
             else if (use_tile2 && map) tile2::score_tile2_kernel<false, true><<<blocks, threads, smem_bytes, c->stream>>>(a);
             else if (use_tile2) tile2::score_tile2_kernel<false, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
-            else tile::score_tile_kernel<<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
+            else if (use_stream) tile::score_tile_kernel<true><<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
+            else tile::score_tile_kernel<false><<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
             CU_TRY(c, cudaGetLastError());
             launches = 1;
-            c->last_kernel = use_tile2 ? HC_KERNEL_TILED2 : HC_KERNEL_TILED;
+            c->last_kernel = use_tile2 ? HC_KERNEL_TILED2 : (use_stream ? HC_KERNEL_STREAMED : HC_KERNEL_TILED);
         }
         CU_TRY(c, cudaEventRecord(c->ev1, c->stream));
     } else {
@@ -1264,7 +1291,7 @@ int hc_quasi_score_band(hc_ctx* c, const hc_quasi_params* qp, int32_t row_begin,
 }
 
 int hc_set_kernel(hc_ctx* c, int32_t mode) {
-    if (!c || mode < HC_KERNEL_AUTO || mode > HC_KERNEL_TILED2) return HC_E_INVALID;
+    if (!c || mode < HC_KERNEL_AUTO || mode > HC_KERNEL_STREAMED) return HC_E_INVALID;
     c->kernel_mode = mode;
     return HC_OK;
 }

@@ -199,11 +199,19 @@ __device__ __forceinline__ void cheap(const Args& a, const int* hA, const int* h
 
 __device__ __forceinline__ bool consumes_q(uint32_t op) { return op == HC_OP_M || op == HC_OP_I || op == HC_OP_S; }
 
+// Operand loads of the lock-step loop. G = false: the staged copies in shared memory (row buffer, transposed column
+// tile: word w of the lane's read at opsB[w*32]). G = true ("streamed" kernel, reads too long or quality alphabets too
+// wide for a tile): both op streams are read in place from global memory (L1/L2), word w at opsB[w].
+template <bool G> __device__ __forceinline__ uint32_t ldw(const uint32_t* p) { return G ? __ldg(p) : *p; }
+template <bool G> __device__ __forceinline__ uint32_t ldh(const uint16_t* p) { return G ? (uint32_t)__ldg(p) : (uint32_t)*p; }
+
 // The lock-step loop of one slot, all 32 lanes together (lanes without an overlap phase in this slot idle).
+template <bool G>
 __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int* hB, const uint16_t* opsA, const uint32_t* opsB,
                                         const unsigned char* Tb, uint32_t m, Lane& L, int shape) {
     const uint32_t op = m & 15u;
     bool more = (op == M_OVL || op == M_OVL2 || op == M_OVLQX || op == M_SOVL) && !L.gap && !L.undef;
+    constexpr int BS = G ? 1 : 32;                  // stride of the lane's words in opsB
     const int sa = (m >> 4) & 1, sb = (m >> 5) & 1;
     const bool qx = op == M_OVLQX;
     int hi = 0;
@@ -218,7 +226,7 @@ __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int*
     const int aoff = sa ? hA[10] : 0, boff = sb ? hB[10 * 32] : 0;
     int ca = get_cur(L, 0, sa), cb = get_cur(L, 1, sb);
     int cq = 0;
-    if (more && qx) { while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
+    if (more && qx) { while (cq < nA && !consumes_q(HC_REC_OP(ldh<G>(opsA + aoff + cq)))) cq++; }
     const uint32_t K8 = (uint32_t)a.P.K * 8u;
     const uint32_t teq = smem_u32(Tb), tun = teq + (uint32_t)a.P.KK * 8u;   // shared-space addresses of the two tables
     const uint32_t* opsA32 = reinterpret_cast<const uint32_t*>(opsA);
@@ -245,19 +253,19 @@ __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int*
             if (run >= 1) {
                 const int ia = aoff + ca, ib = boff + cb;
                 const uint32_t* pa = opsA32 + (ia >> 1);
-                const uint32_t* pb = opsB + (ib >> 1) * 32;
+                const uint32_t* pb = opsB + (ib >> 1) * BS;
                 int sha = (ia & 1) * 16, shb = (ib & 1) * 16;
                 asm volatile("" : "+r"(sha), "+r"(shb));          // keep the two shift amounts in registers
-                uint32_t a0 = pa[0], a1 = pa[1], a2 = pa[2];
-                uint32_t b0 = pb[0], b1 = pb[32], b2 = pb[64];
+                uint32_t a0 = ldw<G>(pa), a1 = ldw<G>(pa + 1), a2 = ldw<G>(pa + 2);
+                uint32_t b0 = ldw<G>(pb), b1 = ldw<G>(pb + BS), b2 = ldw<G>(pb + 2 * BS);
                 int done = 0;
                 while (done + 4 <= run) {
                     const uint32_t A01 = __funnelshift_r(a0, a1, sha), A23 = __funnelshift_r(a1, a2, sha);
                     const uint32_t B01 = __funnelshift_r(b0, b1, shb), B23 = __funnelshift_r(b1, b2, shb);
                     if ((A01 | B01 | A23 | B23) & 0x00380038u) break;
-                    pa += 2; pb += 64;
+                    pa += 2; pb += 2 * BS;
                     a0 = a2; b0 = b2;
-                    a1 = pa[1]; a2 = pa[2]; b1 = pb[32]; b2 = pb[64];
+                    a1 = ldw<G>(pa + 1); a2 = ldw<G>(pa + 2); b1 = ldw<G>(pb + BS); b2 = ldw<G>(pb + 2 * BS);
                     TILE_MUL2(A01, B01);
                     TILE_MUL2(A23, B23);
                     done += 4;
@@ -280,8 +288,8 @@ __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int*
         while (more) {
             if (ref > hi) { more = false; break; }
             if (ca >= nA || cb >= nB) { L.undef = true; more = false; break; }
-            const uint32_t ra = opsA[aoff + ca];
-            const uint32_t wb = opsB[((boff + cb) >> 1) * 32];
+            const uint32_t ra = ldh<G>(opsA + aoff + ca);
+            const uint32_t wb = ldw<G>(opsB + ((boff + cb) >> 1) * BS);
             const uint32_t rb = ((boff + cb) & 1) ? (wb >> 16) : (wb & 0xffffu);
             const int oa = (int)HC_REC_OP(ra), ob = (int)HC_REC_OP(rb);
             const int act = (oa | ob) == 0 ? ACT_SCORE : op_action(oa, ob);
@@ -289,19 +297,19 @@ __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int*
                 uint32_t sq = ra;
                 if (qx) {
                     if (cq >= nA) { L.undef = true; more = false; break; }
-                    sq = opsA[aoff + cq];
+                    sq = ldh<G>(opsA + aoff + cq);
                 }
                 TILE_MUL(HC_REC_QUAL(sq), HC_REC_QUAL(rb), HC_REC_BASE(sq ^ rb) != 0u);
                 cc++;
                 if (oa == HC_OP_M) ref++;
                 ca++; cb++;
-                if (qx) { cq++; while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
+                if (qx) { cq++; while (cq < nA && !consumes_q(HC_REC_OP(ldh<G>(opsA + aoff + cq)))) cq++; }
             } else if (act == ACT_SKIP) {
                 ref++; ca++; cb++;
-                if (qx && consumes_q(oa)) { cq++; while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
+                if (qx && consumes_q(oa)) { cq++; while (cq < nA && !consumes_q(HC_REC_OP(ldh<G>(opsA + aoff + cq)))) cq++; }
             } else if (act == ACT_ADV_A) {
                 ca++;
-                if (qx) { cq++; while (cq < nA && !consumes_q(HC_REC_OP((uint32_t)opsA[aoff + cq]))) cq++; }
+                if (qx) { cq++; while (cq < nA && !consumes_q(HC_REC_OP(ldh<G>(opsA + aoff + cq)))) cq++; }
             } else if (act == ACT_ADV_B) {
                 cb++;
             } else {
@@ -309,8 +317,8 @@ __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int*
             }
             // hand back to the fast loop as soon as the next column is M against M again
             if (!qx && ref <= hi && ca < nA && cb < nB) {
-                const uint32_t na = opsA[aoff + ca];
-                const uint32_t nw = opsB[((boff + cb) >> 1) * 32];
+                const uint32_t na = ldh<G>(opsA + aoff + ca);
+                const uint32_t nw = ldw<G>(opsB + ((boff + cb) >> 1) * BS);
                 const uint32_t nb = ((boff + cb) & 1) ? (nw >> 16) : (nw & 0xffffu);
                 if (((na | nb) & 0x38u) == 0u) break;
             }
@@ -370,6 +378,9 @@ __device__ __forceinline__ bool tile_layout_reject(const int* hA, const int* hB,
     return Ae2 < Bs1 || (Ae1 < Bs1 && Be1 < As2) || Be1 < As1;
 }
 
+// G = true: the streamed variant -- no column tile and no row op buffers (a.maxw = 0, a.abuf_bytes = 0); the lock-step loop
+// reads both op streams in place. Everything else (work items, headers, programs, tails, decision) is the same code.
+template <bool G>
 __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel(const Args a) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -401,7 +412,6 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
     uint32_t parity = 0;       // bit k = phase parity of this warp's barrier k
     const unsigned char* Tb = reinterpret_cast<const unsigned char*>(Tsm);
     const int* hB = hBsm + lane;
-    const uint32_t* opsB = tileB + lane;
 
     auto load_info = [&](int row, int r1) {
         RowInfo ri;
@@ -415,7 +425,7 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
         return ri;
     };
     auto issue = [&](int k, int row, const RowInfo& ri) {       // lane 0 only
-        const uint32_t ob = ((uint32_t)ri.n_ops * 2u + 15u) & ~15u;
+        const uint32_t ob = G ? 0u : (((uint32_t)ri.n_ops * 2u + 15u) & ~15u);
         uint64_t* bar = &bars[warp * 2 + k];
         fence_proxy_async();
         mbar_expect_tx(bar, 64u + ob);
@@ -435,7 +445,10 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
         // ---- stage the 32 column reads: headers transposed, op streams interleaved word-wise
         static_assert(kWarps >= 16, "one thread per (header field, lane)");
         if (warp < 16) hBsm[warp * 32 + lane] = jmine >= 0 ? __ldg(reinterpret_cast<const int*>(a.hdr + jmine) + warp) : 0;
-        {
+        const uint32_t* opsB = tileB + lane;
+        if (G) {
+            if (jmine >= 0) opsB = reinterpret_cast<const uint32_t*>(a.ops + (unsigned)__ldg(reinterpret_cast<const int*>(a.hdr + jmine) + 8));
+        } else {
             const int l = lane;
             const int j = jmine;
             if (j >= 0) {
@@ -469,7 +482,7 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
             mbar_wait(&bars[warp * 2 + kb], (parity >> kb) & 1u);
             parity ^= 1u << kb;
             const int* hA = reinterpret_cast<const int*>(mybuf0 + kb * bufstride);
-            const uint16_t* opsA = reinterpret_cast<const uint16_t*>(mybuf0 + kb * bufstride + 64);
+            const uint16_t* opsA = G ? a.ops + infA.ops_off : reinterpret_cast<const uint16_t*>(mybuf0 + kb * bufstride + 64);
             const int i = rowA;
             const int j = jmine;
             const bool active = j >= 0 && j < i;
@@ -492,7 +505,7 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
                     const bool mine = pid == TP_SINGLE00;
                     if (mine) cheap(a, hA, hB, i, j, TILE_MOP(M_SPRE, 0, 0, 0, 0), L, shape);
                     __syncwarp();
-                    overlap(a, hA, hB, opsA, opsB, Tb, mine ? TILE_MOP(M_SOVL, 0, 0, 0, 0) : 0u, L, shape);
+                    overlap<G>(a, hA, hB, opsA, opsB, Tb, mine ? TILE_MOP(M_SOVL, 0, 0, 0, 0) : 0u, L, shape);
                     if (mine) cheap(a, hA, hB, i, j, TILE_MOP(M_SPOST, 0, 0, 0, 0), L, shape);
                 } else {
                     const uint32_t* pg = progsm + pid * TP_WORDS;
@@ -503,7 +516,7 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
                         cheap(a, hA, hB, i, j, pg[s * 4 + 2], L, shape);
                         __syncwarp();
                         const uint32_t mo = pg[s * 4 + 3];
-                        if (__any_sync(FULL, (mo & 15u) != M_NOP)) overlap(a, hA, hB, opsA, opsB, Tb, mo, L, shape);
+                        if (__any_sync(FULL, (mo & 15u) != M_NOP)) overlap<G>(a, hA, hB, opsA, opsB, Tb, mo, L, shape);
                     }
                     cheap(a, hA, hB, i, j, pg[SLOT_FINAL], L, shape);
                 }

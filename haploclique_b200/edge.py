@@ -19,7 +19,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libhcgpu.so")
 
 HC_OK = 0
-KERNEL_AUTO, KERNEL_GENERIC, KERNEL_TILED, KERNEL_TILED2 = 0, 1, 2, 3
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_TILED, KERNEL_TILED2, KERNEL_STREAMED = 0, 1, 2, 3, 4
 ST_REJECT_COV, ST_REJECT_LAYOUT, ST_WALKED, ST_UNDEFINED = 0, 1, 2, 3
 
 
@@ -343,7 +343,7 @@ class NewEdgeCalculator(EdgeCalculator):
         return Adjacency(row_begin, row_end, col0, off, words, stats, amb[:min(int(st.ambiguous), amb_cap)].copy())
 
     def set_kernel(self, mode: int) -> None:
-        """KERNEL_AUTO / KERNEL_GENERIC / KERNEL_TILED / KERNEL_TILED2 (include/hc_edge.h: hc_set_kernel)."""
+        """KERNEL_AUTO / KERNEL_GENERIC / KERNEL_TILED / KERNEL_TILED2 / KERNEL_STREAMED (include/hc_edge.h: hc_set_kernel)."""
         self._check(self.L.hc_set_kernel(self._ctx, mode), "hc_set_kernel")
 
     def last_kernel(self) -> int:

@@ -20,6 +20,8 @@ CONFIGS = {
     "C3": dict(n_frag=1_000_000, genome_len=9719, read_len=250, frag_mean=450.0, frag_sd=60.0, frag_min=260, frag_max=800),
     "C4": dict(n_frag=1_000_000, genome_len=1500, read_len=150, frag_mean=320.0, frag_sd=40.0, frag_min=160, frag_max=600),
 }
+# BASELINE configs[4]: a super-read round (kwargs of super_reads())
+C5 = dict(n_frag=4000, genome_len=9719, read_len=3500, frag_mean=3000.0, frag_sd=2500.0, frag_min=500, frag_max=9719)
 
 
 def quasispecies(n_frag: int, genome_len: int = 9719, read_len: int = 250, frag_mean: float = 450.0,
@@ -175,6 +177,29 @@ def quasispecies_sharded(n_frag: int, chunk: int = 50_000, start_window=None, se
         left -= n
         k += 1
     return ReadBatch.concat_sorted(parts)
+
+
+def super_reads(n_frag: int = 4000, clique_frac: float = 0.7, seed: int = 20261104, **kw) -> ReadBatch:
+    """A batch shaped like a later iteration's input (BASELINE configs[4]): a few thousand records of 0.5-9.7 kb, most of
+    them merged cliques (name Clique_*: cutoffs 0.99 / 0.97 and min overlap 0.9 apply, NewEdgeCalculator.cpp:1111-1125),
+    the rest left-over reads. Columns of a super-read carry posterior qualities raised by every agreeing member
+    (computeEntry, AlignmentRecord.cpp:169-184: up to char 126), so the quality alphabet is 60-90 codes wide instead of
+    the ~25 of raw reads -- which is what decides the kernel (tables of 16*K*K bytes, reads of thousands of columns)."""
+    args = dict(C5)
+    args.update(kw)
+    args.pop("n_frag", None)
+    b = quasispecies(n_frag, indel_err=2e-4, clip_frac=0.02, seed=seed, **args)
+    rng = np.random.default_rng(seed + 7)
+    b.is_clique[:] = (rng.random(b.n) < clique_frac).astype(b.is_clique.dtype)
+    depth = np.where(b.is_clique != 0, rng.integers(5, 56, b.n), 0)           # quality raised by the clique's depth
+    seg_len = np.asarray(b.seq_len, np.int64)
+    seg_boost = np.repeat(depth, 2)
+    idx = np.repeat(np.asarray(b.seq_off, np.int64) - (np.cumsum(seg_len) - seg_len), seg_len) + np.arange(int(seg_len.sum()))
+    boost = np.repeat(seg_boost, seg_len)
+    q = b.qual.astype(np.int64)
+    q[idx] = np.minimum(q[idx] + np.where(boost > 0, boost + rng.integers(-4, 5, boost.size), 0), 126)
+    b.qual = q.astype(np.uint8)
+    return b
 
 
 def zoo(n_reads: int, genome_len: int = 400, seed: int = 1, max_seg: int = 120, clique_frac: float = 0.3,

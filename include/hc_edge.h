@@ -192,10 +192,13 @@ int hc_score_band_detail(hc_ctx* ctx, int32_t row_begin, int32_t row_end, uint32
  * walker. Of the two tiled kernels AUTO prefers TILED2 (operands stored as table-address addends; 9-row table of
  * 72*K*K bytes for K quality codes; walks the tail columns when the context has an allele-frequency map) and falls
  * back to TILED (16-bit op records, 16*K*K bytes of tables; contexts without allele-frequency map only) when K is
- * too large for TILED2. GENERIC / TILED / TILED2 force one; a forced tiled kernel fails with HC_E_STATE when not
- * eligible. All three produce identical results. hc_last_kernel: the kernel the last hc_score_band call launched
+ * too large for TILED2. When the reads are too long or K too large for either tile (super-read rounds: reads of
+ * thousands of columns, 60-94 quality codes) AUTO takes STREAMED: the same work decomposition and lock-step loop as
+ * TILED with both op streams read in place from global memory (shared memory: 16*K*K bytes of tables only; no
+ * allele-frequency map). GENERIC / TILED / TILED2 / STREAMED force one; a forced kernel fails with HC_E_STATE when
+ * not eligible. All four produce identical results. hc_last_kernel: the kernel the last hc_score_band call launched
  * (0 = none). */
-enum { HC_KERNEL_AUTO = 0, HC_KERNEL_GENERIC = 1, HC_KERNEL_TILED = 2, HC_KERNEL_TILED2 = 3 };
+enum { HC_KERNEL_AUTO = 0, HC_KERNEL_GENERIC = 1, HC_KERNEL_TILED = 2, HC_KERNEL_TILED2 = 3, HC_KERNEL_STREAMED = 4 };
 int hc_set_kernel(hc_ctx* ctx, int32_t mode);
 int hc_last_kernel(const hc_ctx* ctx);
 

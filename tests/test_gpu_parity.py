@@ -140,7 +140,8 @@ def test_setOverlapCliques_changes_the_decision():
 
 
 # ---- the tiled band kernel (shared-memory column tiles, TMA-fed rows): every band slot against the oracle ----
-TILED_KERNELS = [pytest.param(edge.KERNEL_TILED, id="tiled"), pytest.param(edge.KERNEL_TILED2, id="tiled2")]
+TILED_KERNELS = [pytest.param(edge.KERNEL_TILED, id="tiled"), pytest.param(edge.KERNEL_TILED2, id="tiled2"),
+                 pytest.param(edge.KERNEL_STREAMED, id="streamed")]
 
 
 def _tiled_detail_vs_oracle(b, kw, label, kernel=edge.KERNEL_TILED):
@@ -202,7 +203,7 @@ def test_auto_prefers_the_second_generation_tiled_kernel():
 def test_tiled_kernel_zoo(seed, kernel):
     # 92 quality codes for the first tiled kernel; the second one takes 22 codes (split-word table) on even seeds
     # and 44 codes (table of doubles) on odd seeds -- its 7-row table of 92 codes would not fit shared memory
-    wide = (2, 94) if kernel == edge.KERNEL_TILED else ((20, 42) if seed % 2 == 0 else (2, 46))
+    wide = (2, 94) if kernel != edge.KERNEL_TILED2 else ((20, 42) if seed % 2 == 0 else (2, 46))
     b = synth.zoo(200, seed=100 + seed, wide_qual=wide)
     kw = dict(noProb0=bool(seed % 2), edge_quasi_cutoff_single=0.8, edge_quasi_cutoff_mixed=0.85,
               edge_quasi_cutoff=0.9, overlap=0.3, overlap_single=0.2, maxPosition=b.max_position())
@@ -277,8 +278,8 @@ def test_full_size_C2_three_kernels_agree():
 @pytest.mark.parametrize("seed", [1, 2])
 def test_long_super_read_like_batch(seed):
     """BASELINE configs[4] shape: a few dozen records of 1-9.7 kb, most named Clique_* (cutoffs 0.99 / 0.97, min overlap
-    0.9), long sequential products down to the underflow zone. Too long for a shared-memory tile: AUTO takes the generic
-    walker for them; every pair against the oracle, every field."""
+    0.9), long sequential products down to the underflow zone. Too long for a shared-memory tile: AUTO takes the streamed
+    kernel for them; every pair against the oracle, every field, from the pair-list kernel and from the band kernel."""
     b = synth.quasispecies(70, genome_len=9719, read_len=3200, frag_mean=5200.0, frag_sd=1800.0, frag_min=900, frag_max=9719,
                            indel_err=2e-4, clip_frac=0.05, seed=900 + seed)
     rng = np.random.default_rng(seed)
@@ -288,6 +289,8 @@ def test_long_super_read_like_batch(seed):
                   edge_quasi_cutoff=0.97, edge_quasi_cutoff_mixed=0.95, edge_quasi_cutoff_single=0.9)
         calc = edge.NewEdgeCalculator(**kw)
         adj = calc.scoreBatch(b)
+        assert calc.last_kernel() == edge.KERNEL_STREAMED
+        _tiled_detail_vs_oracle(b, kw, "long-reads-band", edge.KERNEL_STREAMED)
         pi, pj = common.tri_pairs(b.n)
         dev = calc.score_pairs(pi, pj)
         O = pyoracle.Oracle(b, **kw)
@@ -298,6 +301,29 @@ def test_long_super_read_like_batch(seed):
             e = orc["edge"] == 1
             ai, aj = adj.edges()
             assert adj.count() == int(e.sum()) and (ai == pi[e]).all() and (aj == pj[e]).all()
+
+
+@pytest.mark.parametrize("noprob0", [False, True])
+def test_super_read_round_C5_shape(noprob0):
+    """bench.py's C5 generator at 160 records (reads of 0.5-9.7 kb, 70 % Clique_*, ~75 quality codes): the tables of the
+    second-generation kernel (72*K*K bytes) and the column tile of the first do not fit shared memory, AUTO streams the op
+    records from global memory instead; every band slot against the oracle, and the same words from the generic walker."""
+    b = synth.super_reads(160, seed=4242)
+    assert len(np.unique(b.qual)) > 60 and int(b.cig_len.reshape(-1, 2).sum(1).max()) > 6000
+    kw = dict(noProb0=noprob0, maxPosition=b.max_position() + 10)
+    calc = edge.NewEdgeCalculator(**kw)
+    calc.scoreBatch(b)
+    assert calc.last_kernel() == edge.KERNEL_STREAMED
+    for mode in (edge.KERNEL_TILED, edge.KERNEL_TILED2):
+        calc.set_kernel(mode)
+        with pytest.raises(edge.HcError):
+            calc.score_band()
+    det, orc = _tiled_detail_vs_oracle(b, kw, "C5-shape", edge.KERNEL_STREAMED)
+    assert int(orc["cc"].max()) > 5000 and int((orc["status"] == 2).sum()) > 5000
+    # looser parameters so that edges exist between the haplotypes' reads
+    kw2 = dict(kw, edge_quasi_cutoff=0.9, edge_quasi_cutoff_mixed=0.9, edge_quasi_cutoff_single=0.85, overlap=0.5, overlap_single=0.3)
+    det, orc = _tiled_detail_vs_oracle(b, kw2, "C5-shape-loose", edge.KERNEL_STREAMED)
+    assert int(orc["edge"].sum()) > (50 if noprob0 else 0)      # with prob0 the tail penalty leaves a handful
 
 
 @pytest.mark.parametrize("noprob0", [False, True])
