@@ -495,6 +495,7 @@ struct hc_ctx {
     // QuasispeciesEdgeCalculator path (hc_quasi.cuh): host-tabulated log terms per (base1, base2, code1, code2), ln of the map
     uint8_t qual_chars[128] = {0};
     double* d_logsum = nullptr; double* d_simpson_ln = nullptr; hc_quasi_result* d_qres = nullptr; size_t qres_cap = 0;
+    int4* d_qseg = nullptr; size_t qseg_cap = 0; bool have_qseg = false;
     // second-generation tiled kernel (hc_tile2.cuh): row / column operand formats and the 9-row table
     uint32_t* d_opsA = nullptr; uint16_t* d_opsF = nullptr; uint32_t* d_tab7 = nullptr;
     bool have_formats = false;
@@ -860,7 +861,7 @@ void hc_destroy(hc_ctx* c) {
     cudaFree(c->d_pi); cudaFree(c->d_pj); cudaFree(c->d_res); cudaFree(c->d_flush);
     cudaFree(c->d_aux); cudaFree(c->d_col2op); cudaFree(c->d_tprog); cudaFree(c->d_items); cudaFree(c->d_item_counter);
     cudaFree(c->d_opsA); cudaFree(c->d_opsF); cudaFree(c->d_tab7);
-    cudaFree(c->d_logsum); cudaFree(c->d_simpson_ln); cudaFree(c->d_qres);
+    cudaFree(c->d_logsum); cudaFree(c->d_simpson_ln); cudaFree(c->d_qres); cudaFree(c->d_qseg);
     cudaFree(c->d_detail); cudaFree(c->d_colidx);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -907,6 +908,7 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     CU_TRY(c, cudaSetDevice(c->device));
     CU_TRY(c, cudaStreamSynchronize(c->stream));
     if (c->d_logsum) { cudaFree(c->d_logsum); c->d_logsum = nullptr; }     // depends on the quality codes of the batch
+    c->have_qseg = false;
     std::memcpy(c->qual_chars, p->qual_chars, sizeof(c->qual_chars));
     c->have_formats = false;
     int rc;
@@ -1210,6 +1212,15 @@ static int quasi_prepare(hc_ctx* c, const hc_quasi_params* qp, quasi::QParams& P
         CU_TRY(c, cudaMalloc((void**)&c->d_simpson_ln, ln.size() * sizeof(double)));
         CU_TRY(c, cudaMemcpy(c->d_simpson_ln, ln.data(), ln.size() * sizeof(double), cudaMemcpyHostToDevice));
     }
+    const bool no_fast = std::getenv("HC_QUASI_NO_FAST") != nullptr;             // tests: force the general walk
+    if (!c->have_qseg && !no_fast) {
+        int rc;
+        if ((rc = grow(c, c->d_qseg, c->qseg_cap, (size_t)2 * c->n_reads)) != HC_OK) return rc;
+        quasi::build_qseg_kernel<<<(2 * c->n_reads + 127) / 128, 128, 0, c->stream>>>(c->d_hdr, c->d_ops, c->n_reads, c->d_qseg);
+        CU_TRY(c, cudaGetLastError());
+        c->have_qseg = true;
+    }
+    P.qseg = no_fast ? nullptr : c->d_qseg;
     P.cutoff[0] = qp->edge_quasi_cutoff_cliques; P.cutoff[1] = qp->edge_quasi_cutoff_mixed; P.cutoff[2] = qp->edge_quasi_cutoff_single;
     P.min_overlap[0] = qp->min_overlap_cliques; P.min_overlap[1] = qp->min_overlap_single;
     P.amb_tol = qp->ambiguity_rel_tol > 0 ? qp->ambiguity_rel_tol : 1e-12;

@@ -26,9 +26,27 @@ struct QParams {
     int simpson_len;
     int K;
     int frameshift;
+    const int4* qseg;          // per segment (2*read + s): {consuming ops, last consuming op, first non-clip op, first S at or after it}
 };
 
-struct SegV { const uint16_t* ops; int n, start, end; };
+struct SegV { const uint16_t* ops; int n, start, end; int4 q; };
+
+// Per-segment facts the fast walk needs instead of scanning the op stream per pair (built once per upload).
+__global__ void build_qseg_kernel(const hc_read_hdr* __restrict__ hdr, const uint16_t* __restrict__ ops, int n_reads, int4* __restrict__ qseg) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= 2 * n_reads) return;
+    const hc_read_hdr& h = hdr[t >> 1];
+    const int s = t & 1, n = h.n_ops[s];
+    const uint16_t* o = ops + h.ops_off[s];
+    int nq = 0, lastc = -1, first = n, mid_s = n;
+    for (int c = 0; c < n; ++c) {
+        const int op = (int)HC_REC_OP((uint32_t)o[c]);
+        if (op == HC_OP_M || op == HC_OP_I || op == HC_OP_S) { nq++; lastc = c; }
+        if (first == n && op != HC_OP_S && op != HC_OP_H) first = c;
+        if (first != n && mid_s == n && op == HC_OP_S) mid_s = c;
+    }
+    qseg[t] = make_int4(nq, lastc, first, mid_s);
+}
 
 __device__ __forceinline__ int opc(const SegV& s, int c) { return (int)HC_REC_OP((uint32_t)__ldg(s.ops + c)); }
 __device__ __forceinline__ bool consuming(int op) { return op == HC_OP_M || op == HC_OP_I || op == HC_OP_S; }
@@ -67,9 +85,106 @@ __device__ __forceinline__ void add_simpson(const QParams& P, int pos, double& a
     if (P.simpson_ln != nullptr && pos >= 0 && pos < P.simpson_len) acc = __dadd_rn(acc, __ldg(P.simpson_ln + pos));
 }
 
-// singleOverlap (:181-426). `undef`: the reference would spin forever or index out of range here.
+// singleOverlap (:181-426) without the per-pair scans of the general restatement below. The reference's sequence
+// cursors (j_seq, j_seq2) are functions of its CIGAR cursors as long as every op a cursor passes advances both or
+// neither in step with "consumes a base": true for the clip loop (:258-267), for M/I/D in the prefix loop (:268-295)
+// and for every branch of the main loop (:307-381) -- not in exact-match mode (:298-306 advances all four cursors
+// on any op) and not when the prefix loop runs over an S op (:268-295 passes it without touching j_seq). Under that
+// invariant sequence[j_seq] is the record at the CIGAR cursor whenever that op is M or I, and "j_seq < size" is
+// "a consuming op exists at or after the CIGAR cursor". Returns false (nothing decided) when the invariant cannot be
+// guaranteed; the caller then runs the general walk. Same additions in the same order: bit-identical sums.
+__device__ __forceinline__ bool single_overlap_fast(const SegV& A, const SegV& B, const QParams& P, double MIN_OVERLAP, double cutoff,
+                                                    bool& undef, bool& subnormal, double& result) {
+    if (cutoff == 1.0 || P.qseg == nullptr) return false;
+    const bool swap = B.start < A.start;
+    const SegV& S1 = swap ? B : A;
+    const SegV& S2 = swap ? A : B;
+    const int s1 = S1.start, e1 = S1.end, s2 = S2.start, e2 = S2.end;
+    const int n1 = S1.n, n2 = S2.n;
+    int offset1 = 0, offset2 = 0, overlap = 0;
+    compute_offsets(s1, s2, e1, e2, offset1, offset2, overlap);
+    result = 0.0;
+    if ((double)overlap < MIN_OVERLAP) return true;
+    if (offset1 < 0 || offset2 < 0 || offset1 >= S1.q.x || offset2 >= S2.q.x) return true;
+    const int last1 = S1.q.y, last2 = S2.q.y;
+    int jc1 = 0, jc2 = 0, j = 0, j2 = 0;
+    for (;;) {
+        if (!(jc1 < n1 && jc2 < n2)) { undef = true; return true; }
+        const int c1 = opc(S1, jc1), c2 = opc(S2, jc2);
+        if (c1 != HC_OP_S && c2 != HC_OP_S && c1 != HC_OP_H && c2 != HC_OP_H) break;
+        if (c1 == HC_OP_S) jc1++;
+        if (c2 == HC_OP_S) jc2++;
+        if (jc1 >= n1 || jc2 >= n2) { undef = true; return true; }
+        if (opc(S1, jc1) == HC_OP_H) jc1++;
+        if (opc(S2, jc2) == HC_OP_H) jc2++;
+    }
+    if (jc1 < S1.q.z || min(jc1 + offset1, n1) > S1.q.w) { undef = false; return false; }     // the prefix would pass an S
+    double acc = 0.0, total_size = 0.0;
+    const bool smap = P.simpson_ln != nullptr;
+    if (!smap) jc1 += offset1;
+    else {
+        for (int k = 0; k != offset1; ++k) {
+            if (jc1 < n1 && opc(S1, jc1) == HC_OP_M) { add_simpson(P, s1 + j, acc); j++; }
+            jc1++;
+        }
+    }
+    while (jc1 < n1 && jc2 < n2 && jc1 <= last1 && jc2 <= last2) {
+        const uint32_t r1 = __ldg(S1.ops + jc1), r2 = __ldg(S2.ops + jc2);
+        const int c1 = (int)HC_REC_OP(r1), c2 = (int)HC_REC_OP(r2);
+        if (c1 == HC_OP_S || c2 == HC_OP_S) break;
+        if (c1 == c2 && (c1 == HC_OP_M || c1 == HC_OP_I)) {
+            const size_t idx = (((size_t)HC_REC_BASE(r1) * 5 + HC_REC_BASE(r2)) * P.K + HC_REC_QUAL(r1)) * P.K + HC_REC_QUAL(r2);
+            acc = __dadd_rn(acc, __ldg(P.logsum + idx));
+            total_size += 1.0;
+            jc1++; jc2++;
+            if (smap && jc1 < n1 && opc(S1, jc1) == HC_OP_M) { j++; j2++; }
+        } else if (c1 == c2 && c1 == HC_OP_D) {
+            jc1++; jc2++;
+        } else if (P.frameshift) {
+            if (c2 == HC_OP_M) {
+                if (c1 == HC_OP_D) { jc1++; jc2++; j2++; }
+                else if (c1 == HC_OP_I) { jc1++; }
+                else { undef = true; return true; }
+            } else if (c1 == HC_OP_M) {
+                if (c2 == HC_OP_D) { jc2++; jc1++; j++; }
+                else if (c2 == HC_OP_I) { jc2++; }
+                else { undef = true; return true; }
+            } else {
+                return true;
+            }
+        } else {
+            return true;
+        }
+    }
+    if (smap) {
+        if (jc1 < n1 && opc(S1, jc1) != HC_OP_S) {
+            while (jc1 < n1) {
+                const int c = opc(S1, jc1);
+                if (c == HC_OP_S) break;
+                if (c == HC_OP_M) { add_simpson(P, s1 + j, acc); j++; }
+                jc1++;
+            }
+        } else if (jc2 < n2 && opc(S2, jc2) != HC_OP_S) {
+            while (jc2 < n2) {
+                const int c = opc(S2, jc2);
+                if (c == HC_OP_S) break;
+                if (c == HC_OP_M) { add_simpson(P, s2 + j2, acc); j2++; }
+                jc2++;
+            }
+        }
+    }
+    if (acc < -708.3964185322641) subnormal = true;
+    result = pow(exp(acc), __ddiv_rn(1.0, total_size));
+    return true;
+}
+
+// singleOverlap (:181-426), the general restatement. `undef`: the reference would spin forever or index out of range here.
 __device__ double single_overlap(const SegV& A, const SegV& B, const QParams& P, double MIN_OVERLAP, double cutoff, bool& undef,
                                  bool& subnormal) {
+    {
+        double r = 0.0;
+        if (single_overlap_fast(A, B, P, MIN_OVERLAP, cutoff, undef, subnormal, r)) return r;
+    }
     const bool swap = B.start < A.start;                                                    // :215-220
     const SegV& S1 = swap ? B : A;
     const SegV& S2 = swap ? A : B;
@@ -173,6 +288,7 @@ __device__ __forceinline__ SegV seg_view(const hc_read_hdr& h, const uint16_t* o
     v.n = h.n_ops[s];
     v.start = h.raw[2 * s];
     v.end = h.raw[2 * s + 1];
+    v.q = make_int4(0, 0, 0, 0);
     return v;
 }
 
@@ -185,7 +301,11 @@ __device__ void score_pair(const QParams& P, const hc_read_hdr* __restrict__ hdr
     const bool se1 = ha.ncov_flags & HC_FLAG_SINGLE_END, se2 = hb.ncov_flags & HC_FLAG_SINGLE_END;
     const double cutoff = P.cutoff[(cl1 && cl2) ? 0 : ((cl1 || cl2) ? 1 : 2)];
     const double MIN_OVERLAP = P.min_overlap[(cl1 && cl2) ? 0 : 1];
-    const SegV a1 = seg_view(ha, ops, 0), a2 = seg_view(ha, ops, 1), b1 = seg_view(hb, ops, 0), b2 = seg_view(hb, ops, 1);
+    SegV a1 = seg_view(ha, ops, 0), a2 = seg_view(ha, ops, 1), b1 = seg_view(hb, ops, 0), b2 = seg_view(hb, ops, 1);
+    if (P.qseg != nullptr) {
+        a1.q = __ldg(P.qseg + 2 * i); a2.q = __ldg(P.qseg + 2 * i + 1);
+        b1.q = __ldg(P.qseg + 2 * j); b2.q = __ldg(P.qseg + 2 * j + 1);
+    }
     bool undef = false, subnormal = false;
     int ncalls = 0;
     double q = 0.0;

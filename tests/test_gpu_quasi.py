@@ -13,6 +13,17 @@ pytestmark = pytest.mark.gpu
 REL_TOL = 1e-12
 
 
+@pytest.fixture(params=["fast", "general"], autouse=True)
+def walk(request, monkeypatch):
+    """Both device walks: the fast one (sequence cursors derived from the CIGAR cursors, per-segment facts precomputed)
+    and the general restatement it falls back to (HC_QUASI_NO_FAST forces it for every pair)."""
+    if request.param == "general":
+        monkeypatch.setenv("HC_QUASI_NO_FAST", "1")
+    else:
+        monkeypatch.delenv("HC_QUASI_NO_FAST", raising=False)
+    return request.param
+
+
 def _compare(dev, orc, label):
     assert (dev["status"] == np.where(orc["status"] == 3, 3, 2)).all(), label + ": status"
     ok = orc["status"] != 3
@@ -62,6 +73,30 @@ def test_quasi_zoo_and_band(seed):
         assert adj.count() == int(e.sum())
         assert (ai == pi[e]).all() and (aj == pj[e]).all()
     assert adj.stats["launches"] == 1 and adj.stats["pairs_total"] >= adj.count()
+
+
+@pytest.mark.parametrize("frameshift", [False, True])
+def test_quasi_super_read_round(frameshift):
+    """BASELINE configs[4] names this scorer for the super-read rounds: bench.py's C5 generator at 140 records (reads of
+    0.5-9.7 kb, ~75 quality codes, indels and clips), every ordered pair against the oracle, with and without an
+    allele-frequency map."""
+    b = synth.super_reads(140, seed=777)
+    rng = np.random.default_rng(12)
+    simpson = {int(p): float(rng.uniform(0.3, 1.0)) for p in rng.choice(np.arange(1, 9700), 4000, replace=False)}
+    pi, pj = common.tri_pairs(b.n)
+    for sm in (None, simpson):
+        kw = dict(overlap_single=0.3, overlap=0.5, edge_quasi_cutoff_single=0.8, edge_quasi_cutoff_mixed=0.85, edge_quasi_cutoff=0.9,
+                  frameshift_merge=frameshift, simpson_map=sm, maxPosition=max(b.max_position(), 9700) + 10)
+        calc = edge.QuasispeciesEdgeCalculator(**kw)
+        adj = calc.scoreBatch(b)
+        dev = calc.score_pairs(pi, pj)
+        orc = pyoracle.QuasiOracle(b, **kw).pairs(pi, pj)
+        flips = _compare(dev, orc, "quasi-C5")
+        assert int((orc["n_single"] > 0).sum()) > 1000 and int(((orc["q"] > 0) & (orc["status"] != 3)).sum()) > 200
+        if flips == 0:
+            e = (orc["edge"] == 1) & (orc["status"] != 3)
+            ai, aj = adj.edges()
+            assert adj.count() == int(e.sum()) and (ai == pi[e]).all() and (aj == pj[e]).all()
 
 
 def test_quasi_reference_interface():
