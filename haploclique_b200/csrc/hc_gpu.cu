@@ -640,9 +640,8 @@ TileGeom tile_geometry(const hc_ctx* c) {
     return g;
 }
 
-// The tiled kernel needs: no allele-frequency map (prob0 comes from the ladder), and a column tile that fits.
+// The tiled kernel needs a column tile that fits (with an allele-frequency map its MAP variant walks the tails).
 bool tile_eligible(const hc_ctx* c) {
-    if (c->d_simpson != nullptr) return false;
     return tile_geometry(c).smem <= c->smem_optin;
 }
 
@@ -665,7 +664,6 @@ TileGeom stream_geometry(const hc_ctx* c) {
     return g;
 }
 bool stream_eligible(const hc_ctx* c) {
-    if (c->d_simpson != nullptr) return false;
     return c->max_ops < 65536 && stream_geometry(c).smem <= c->smem_optin;
 }
 
@@ -1040,7 +1038,7 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
     if ((c->kernel_mode == HC_KERNEL_TILED && !can_tile1) || (c->kernel_mode == HC_KERNEL_TILED2 && !can_tile2) ||
         (c->kernel_mode == HC_KERNEL_STREAMED && !can_stream)) {
         c->err = "hc_score_band: the tiled kernel was requested but this batch / parameter set is not eligible "
-                 "(allele-frequency map set, or the tables and the column tile do not fit shared memory)";
+                 "(the tables and the column tile do not fit shared memory)";
         return HC_E_STATE;
     }
     const bool use_tile2 = can_tile2 && (c->kernel_mode == HC_KERNEL_AUTO || c->kernel_mode == HC_KERNEL_TILED2);
@@ -1078,7 +1076,9 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
             CU_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
             CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem_bytes));
         } else {
-            auto kern = use_stream ? tile::score_tile_kernel<true> : tile::score_tile_kernel<false>;
+            const bool map = c->d_simpson != nullptr;
+            auto kern = use_stream ? (map ? tile::score_tile_kernel<true, true> : tile::score_tile_kernel<true, false>)
+                                   : (map ? tile::score_tile_kernel<false, true> : tile::score_tile_kernel<false, false>);
             CU_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
             CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem_bytes));
         }
@@ -1112,8 +1112,10 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
             else if (use_tile2 && split) tile2::score_tile2_kernel<true, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
             else if (use_tile2 && map) tile2::score_tile2_kernel<false, true><<<blocks, threads, smem_bytes, c->stream>>>(a);
             else if (use_tile2) tile2::score_tile2_kernel<false, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
-            else if (use_stream) tile::score_tile_kernel<true><<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
-            else tile::score_tile_kernel<false><<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
+            else if (use_stream && map) tile::score_tile_kernel<true, true><<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
+            else if (use_stream) tile::score_tile_kernel<true, false><<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
+            else if (map) tile::score_tile_kernel<false, true><<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
+            else tile::score_tile_kernel<false, false><<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
             CU_TRY(c, cudaGetLastError());
             launches = 1;
             c->last_kernel = use_tile2 ? HC_KERNEL_TILED2 : (use_stream ? HC_KERNEL_STREAMED : HC_KERNEL_TILED);

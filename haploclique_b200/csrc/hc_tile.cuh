@@ -197,6 +197,46 @@ __device__ __forceinline__ void cheap(const Args& a, const int* hA, const int* h
     cheap_with(hA, hB, m, L, shape, tf);
 }
 
+// A run of noOverlapCheckgap steps (:234-267) when an allele-frequency map is set: prob0 is a running sum in column
+// order (computeProb0, :133-143), so every tail column is visited (the O(1) evaluation of hc_tile.cuh needs the ladder).
+// Segments that are "clips, plain M, clips" need no record reads; the others read the raw records from global memory.
+struct TailWalk {
+    const Args& a; const int* hA; const int* hB; const uint16_t* rawA; const uint16_t* rawB; double* prob0;
+    __device__ __forceinline__ void operator()(int side, int seg, int limit, Lane& L) const {
+        if (limit - L.ref <= 0) return;
+        const int* h = side ? hB : hA;
+        const int st = side ? 32 : 1;
+        const int n = h[(10 + seg) * st];
+        int c = get_cur(L, side, seg);
+        const unsigned fl = ((unsigned)h[15 * st] >> (16 * seg)) & 0xffffu;
+        const int lead = h[(2 * seg) * st] - h[(4 + 2 * seg) * st];
+        const int trail = h[(5 + 2 * seg) * st] - h[(1 + 2 * seg) * st];
+        const uint16_t* raw = (side ? rawB : rawA) + (seg ? h[10 * st] : 0);
+        int ref = L.ref, tc = L.tc;
+        double p0 = *prob0;
+        while (ref < limit) {
+            if (c >= n) { L.undef = true; break; }
+            int op;
+            if (fl == 0) op = (c >= lead && c < n - trail) ? (int)HC_OP_M : (int)HC_OP_S;
+            else op = (int)HC_REC_OP((uint32_t)__ldg(raw + c));
+            if (op == HC_OP_M || op == HC_OP_I) {
+                tc++;
+                double d = 0.0;
+                if (ref < 0 || ref >= a.P.simpson_len) {
+                    if (!a.P.no_prob0) { L.undef = true; break; }       // the reference reads SIMPSON_MAP out of bounds here
+                } else {
+                    d = __ldg(a.P.simpson + ref);
+                }
+                p0 = __dadd_rn(p0, d != 0.0 ? d : a.P.log10_quarter);
+            }
+            if (op != HC_OP_I) ref++;
+            c++;
+        }
+        L.ref = ref; L.tc = tc; *prob0 = p0;
+        set_cur(L, side, seg, c);
+    }
+};
+
 __device__ __forceinline__ bool consumes_q(uint32_t op) { return op == HC_OP_M || op == HC_OP_I || op == HC_OP_S; }
 
 // Operand loads of the lock-step loop. G = false: the staged copies in shared memory (row buffer, transposed column
@@ -380,7 +420,8 @@ __device__ __forceinline__ bool tile_layout_reject(const int* hA, const int* hB,
 
 // G = true: the streamed variant -- no column tile and no row op buffers (a.maxw = 0, a.abuf_bytes = 0); the lock-step loop
 // reads both op streams in place. Everything else (work items, headers, programs, tails, decision) is the same code.
-template <bool G>
+// MAP = true: an allele-frequency map is set, the tails are walked (TailWalk) instead of evaluated in O(1).
+template <bool G, bool MAP>
 __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel(const Args a) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -446,8 +487,9 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
         static_assert(kWarps >= 16, "one thread per (header field, lane)");
         if (warp < 16) hBsm[warp * 32 + lane] = jmine >= 0 ? __ldg(reinterpret_cast<const int*>(a.hdr + jmine) + warp) : 0;
         const uint32_t* opsB = tileB + lane;
+        const uint16_t* rawB = a.ops + (jmine >= 0 ? (unsigned)__ldg(reinterpret_cast<const int*>(a.hdr + jmine) + 8) : 0u);
         if (G) {
-            if (jmine >= 0) opsB = reinterpret_cast<const uint32_t*>(a.ops + (unsigned)__ldg(reinterpret_cast<const int*>(a.hdr + jmine) + 8));
+            opsB = reinterpret_cast<const uint32_t*>(rawB);
         } else {
             const int l = lane;
             const int j = jmine;
@@ -500,6 +542,13 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
                 Lane L;
                 L.ref = 0; L.cc = 0; L.tc = 0; L.probM = 1.0; L.curs = 0ull; L.gap = false; L.undef = false;
                 int shape = 0;
+                double prob0_run = 0.0;                             // MAP: the running sum of the tail columns
+                TailWalk tail_walk{a, hA, hB, a.ops + infA.ops_off, rawB, &prob0_run};
+                TailO1 tail_o1{a, hA, hB, i, j};
+                auto cheap = [&](const Args&, const int*, const int*, int, int, uint32_t mo_, Lane& L_, int& shape_) {
+                    if (MAP) cheap_with(hA, hB, mo_, L_, shape_, tail_walk);
+                    else cheap_with(hA, hB, mo_, L_, shape_, tail_o1);
+                };
                 if (__all_sync(FULL, pid == TP_SINGLE00 || pid == TP_NOP)) {
                     // the common case, checkGapsSingle on segments 1/1 for every lane: straight-line code
                     const bool mine = pid == TP_SINGLE00;
@@ -526,7 +575,8 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
                 bool edge = false, ambiguous = false;
                 if (status == HC_ST_WALKED) {
                     if (!L.undef) {
-                        if (L.tc >= a.P.ladder_len) L.undef = true;
+                        if (MAP) prob0 = prob0_run;
+                        else if (L.tc >= a.P.ladder_len) L.undef = true;
                         else prob0 = __ldg(a.P.ladder + L.tc);
                     }
                     if (L.undef) status = HC_ST_UNDEFINED;

@@ -221,46 +221,6 @@ __device__ __forceinline__ void overlap2(const Args2& a, const int* hA, const in
     if (op == M_OVL || op == M_OVL2 || op == M_OVLQX || op == M_SOVL) { set_cur(L, 0, sa, ca); set_cur(L, 1, sb, cb); }
 }
 
-// A run of noOverlapCheckgap steps (:234-267) when an allele-frequency map is set: prob0 is a running sum in column
-// order (computeProb0, :133-143), so every tail column is visited (the O(1) evaluation of hc_tile.cuh needs the ladder).
-// Segments that are "clips, plain M, clips" need no record reads; the others read the raw records from global memory.
-struct TailWalk {
-    const Args2& a; const int* hA; const int* hB; const uint16_t* rawA; const uint16_t* rawB; double* prob0;
-    __device__ __forceinline__ void operator()(int side, int seg, int limit, Lane& L) const {
-        if (limit - L.ref <= 0) return;
-        const int* h = side ? hB : hA;
-        const int st = side ? 32 : 1;
-        const int n = h[(10 + seg) * st];
-        int c = get_cur(L, side, seg);
-        const unsigned fl = ((unsigned)h[15 * st] >> (16 * seg)) & 0xffffu;
-        const int lead = h[(2 * seg) * st] - h[(4 + 2 * seg) * st];
-        const int trail = h[(5 + 2 * seg) * st] - h[(1 + 2 * seg) * st];
-        const uint16_t* raw = (side ? rawB : rawA) + (seg ? h[10 * st] : 0);
-        int ref = L.ref, tc = L.tc;
-        double p0 = *prob0;
-        while (ref < limit) {
-            if (c >= n) { L.undef = true; break; }
-            int op;
-            if (fl == 0) op = (c >= lead && c < n - trail) ? (int)HC_OP_M : (int)HC_OP_S;
-            else op = (int)HC_REC_OP((uint32_t)__ldg(raw + c));
-            if (op == HC_OP_M || op == HC_OP_I) {
-                tc++;
-                double d = 0.0;
-                if (ref < 0 || ref >= a.P.simpson_len) {
-                    if (!a.P.no_prob0) { L.undef = true; break; }       // the reference reads SIMPSON_MAP out of bounds here
-                } else {
-                    d = __ldg(a.P.simpson + ref);
-                }
-                p0 = __dadd_rn(p0, d != 0.0 ? d : a.P.log10_quarter);
-            }
-            if (op != HC_OP_I) ref++;
-            c++;
-        }
-        L.ref = ref; L.tc = tc; *prob0 = p0;
-        set_cur(L, side, seg, c);
-    }
-};
-
 // Shared memory (bytes): 4*tab_words table | programs | 16*32*4 column headers | maxw*128 tile | nwarps*2*(64+abuf) row
 // buffers | nwarps*2*8 barriers | 64 statistics | 16 control.  hc_gpu.cu: tile2_geometry() computes the same sum.
 template <bool SPLIT, bool MAP>

@@ -187,17 +187,17 @@ int hc_score_band(hc_ctx* ctx, int32_t row_begin, int32_t row_end, uint32_t* adj
 int hc_score_band_detail(hc_ctx* ctx, int32_t row_begin, int32_t row_end, uint32_t* adj, hc_pair_result* detail,
                          int64_t n_words, hc_band_stats* stats);
 
-/* Which band kernel hc_score_band uses. AUTO: a tiled kernel (shared-memory column tiles, TMA-fed rows) when the batch
- * is eligible -- the tables plus the longest read fit a CTA's shared memory -- else the generic one-lane-per-pair
- * walker. Of the two tiled kernels AUTO prefers TILED2 (operands stored as table-address addends; 9-row table of
- * 72*K*K bytes for K quality codes; walks the tail columns when the context has an allele-frequency map) and falls
- * back to TILED (16-bit op records, 16*K*K bytes of tables; contexts without allele-frequency map only) when K is
- * too large for TILED2. When the reads are too long or K too large for either tile (super-read rounds: reads of
- * thousands of columns, 60-94 quality codes) AUTO takes STREAMED: the same work decomposition and lock-step loop as
- * TILED with both op streams read in place from global memory (shared memory: 16*K*K bytes of tables only; no
- * allele-frequency map). GENERIC / TILED / TILED2 / STREAMED force one; a forced kernel fails with HC_E_STATE when
- * not eligible. All four produce identical results. hc_last_kernel: the kernel the last hc_score_band call launched
- * (0 = none). */
+/* Which band kernel hc_score_band uses. AUTO takes the first eligible of
+ *   TILED2   operands stored as table-address addends, 32 column reads staged in a shared-memory tile, rows fed by TMA;
+ *            9-row table of 72*K*K bytes for K quality codes (K up to ~47 beside a tile of 2x250-column reads);
+ *   TILED    16-bit op records, the same tile, 16*K*K bytes of tables (more quality codes than TILED2 can hold);
+ *   STREAMED the work decomposition and lock-step loop of TILED with both op streams read in place from global
+ *            memory, tables only in shared memory: reads too long or K too large for a tile (super-read rounds:
+ *            thousands of columns, 60-94 quality codes); K <= 118, reads below 65536 ops;
+ *   GENERIC  one lane per pair (what hc_score_pairs runs); as a band kernel only the cross-check of the others.
+ * With an allele-frequency map every band kernel walks the tail columns instead of evaluating them in O(1).
+ * GENERIC / TILED / TILED2 / STREAMED force one; a forced kernel fails with HC_E_STATE when the batch is not eligible.
+ * All four produce identical results. hc_last_kernel: the kernel the last hc_score_band call launched (0 = none). */
 enum { HC_KERNEL_AUTO = 0, HC_KERNEL_GENERIC = 1, HC_KERNEL_TILED = 2, HC_KERNEL_TILED2 = 3, HC_KERNEL_STREAMED = 4 };
 int hc_set_kernel(hc_ctx* ctx, int32_t mode);
 int hc_last_kernel(const hc_ctx* ctx);

@@ -326,24 +326,34 @@ def test_super_read_round_C5_shape(noprob0):
     assert int(orc["edge"].sum()) > (50 if noprob0 else 0)      # with prob0 the tail penalty leaves a handful
 
 
+@pytest.mark.parametrize("kernel", TILED_KERNELS)
 @pytest.mark.parametrize("noprob0", [False, True])
-def test_tiled2_with_an_allele_frequency_map(noprob0):
+def test_band_kernels_with_an_allele_frequency_map(noprob0, kernel):
     """With a SIMPSON_MAP prob0 is a running sum over the tail columns in column order (computeProb0, :133-143): the
-    second-generation tiled kernel then walks the tails (MAP variant) instead of using the ladder; every band slot
-    against the oracle, and the same words from the generic walker."""
+    band kernels then walk the tails (MAP variants) instead of using the ladder; every band slot against the oracle,
+    and the same words from the generic walker."""
     b = synth.quasispecies(1200, genome_len=1800, seed=33, indel_err=2e-3, clip_frac=0.1)
     rng = np.random.default_rng(3)
     simpson = {int(p): float(np.log10(rng.uniform(0.3, 1.0))) for p in rng.choice(np.arange(1, 1800), 900, replace=False)}
     kw = dict(noProb0=noprob0, simpson_map=simpson, maxPosition=max(b.max_position(), max(simpson)), edge_quasi_cutoff_single=0.9)
-    det, orc = _tiled_detail_vs_oracle(b, kw, "tiled2-simpson", edge.KERNEL_TILED2)
+    det, orc = _tiled_detail_vs_oracle(b, kw, "band-simpson", kernel)
     assert int(orc["edge"].sum()) > 100 and int((orc["tc"] > 0).sum()) > 1000
-    calc = edge.NewEdgeCalculator(**kw)
-    calc.upload(b)
-    with pytest.raises(edge.HcError):                      # the first-generation kernel needs the ladder
-        calc.set_kernel(edge.KERNEL_TILED)
-        calc.score_band()
     z = synth.zoo(200, seed=77, wide_qual=(20, 42))
     zs = {int(p): float(np.log10(rng.uniform(0.3, 1.0))) for p in rng.choice(np.arange(1, 700), 300, replace=False)}
     kwz = dict(noProb0=noprob0, simpson_map=zs, maxPosition=max(z.max_position(), max(zs)), edge_quasi_cutoff_single=0.8,
                edge_quasi_cutoff_mixed=0.85, edge_quasi_cutoff=0.9, overlap=0.3, overlap_single=0.2)
-    _tiled_detail_vs_oracle(z, kwz, "tiled2-simpson-zoo", edge.KERNEL_TILED2)
+    _tiled_detail_vs_oracle(z, kwz, "band-simpson-zoo", kernel)
+
+
+def test_super_read_round_with_an_allele_frequency_map():
+    """Super-reads (too long and too many quality codes for a tile) plus a map: AUTO takes the streamed MAP variant."""
+    b = synth.super_reads(120, seed=99)
+    rng = np.random.default_rng(8)
+    simpson = {int(p): float(np.log10(rng.uniform(0.3, 1.0))) for p in rng.choice(np.arange(1, 9700), 5000, replace=False)}
+    kw = dict(noProb0=False, simpson_map=simpson, maxPosition=max(b.max_position(), 9700) + 10, edge_quasi_cutoff=0.9,
+              edge_quasi_cutoff_mixed=0.9, edge_quasi_cutoff_single=0.85, overlap=0.5, overlap_single=0.3)
+    calc = edge.NewEdgeCalculator(**kw)
+    calc.scoreBatch(b)
+    assert calc.last_kernel() == edge.KERNEL_STREAMED
+    det, orc = _tiled_detail_vs_oracle(b, kw, "C5-simpson", edge.KERNEL_STREAMED)
+    assert int((orc["tc"] > 1000).sum()) > 500
