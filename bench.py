@@ -203,8 +203,10 @@ def main():
         raise SystemExit("bench.py: no CUDA device; the scored path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"              # keep rank 0's stdout to the one JSON line
+        # keep rank 0's stdout to the one JSON line: NCCL writes its version banner (and any debug output) to stdout
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            del os.environ["NCCL_DEBUG"]
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     t0 = time.perf_counter()
