@@ -14,6 +14,17 @@
 
 namespace hc {
 
+// Released page-locked buffers are kept (a few, bounded) and handed to the next alloc of a similar size: the driver
+// packs one batch per iteration, and cudaHostAlloc of ~100 MB costs more than packing it.
+namespace {
+struct PoolSlot { void* p; size_t cap; };
+std::mutex g_pool_mu;
+std::vector<PoolSlot> g_pool;
+size_t g_pool_bytes = 0;
+constexpr size_t kPoolMaxSlots = 6;
+constexpr size_t kPoolMaxBytes = size_t(2) << 30;
+}  // namespace
+
 bool HostBuf::alloc(size_t bytes) {
     release();
     if (bytes == 0) bytes = 64;
@@ -23,17 +34,47 @@ bool HostBuf::alloc(size_t bytes) {
         have_gpu = (cudaGetDeviceCount(&n) == cudaSuccess && n > 0) ? 1 : 0;
         if (!have_gpu) cudaGetLastError();
     }
-    if (have_gpu && cudaHostAlloc(&p, bytes, cudaHostAllocDefault) == cudaSuccess) { pinned = true; return true; }
-    if (have_gpu) cudaGetLastError();
+    if (have_gpu) {
+        {
+            std::lock_guard<std::mutex> lk(g_pool_mu);
+            int best = -1;
+            for (int k = 0; k < (int)g_pool.size(); ++k)
+                if (g_pool[k].cap >= bytes && g_pool[k].cap <= 2 * bytes + (size_t(1) << 20) && (best < 0 || g_pool[k].cap < g_pool[best].cap)) best = k;
+            if (best >= 0) {
+                p = g_pool[best].p; cap = g_pool[best].cap; pinned = true;
+                g_pool_bytes -= cap;
+                g_pool.erase(g_pool.begin() + best);
+                return true;
+            }
+        }
+        const size_t want = bytes + bytes / 8;                 // head room so that the next, slightly larger batch fits
+        if (cudaHostAlloc(&p, want, cudaHostAllocDefault) == cudaSuccess) { pinned = true; cap = want; return true; }
+        cudaGetLastError();
+    }
     p = std::malloc(bytes);
     pinned = false;
+    cap = bytes;
     return p != nullptr;
 }
 
 void HostBuf::release() {
     if (!p) return;
-    if (pinned) cudaFreeHost(p); else std::free(p);
+    if (pinned) {
+        bool kept = false;
+        {
+            std::lock_guard<std::mutex> lk(g_pool_mu);
+            if (g_pool.size() < kPoolMaxSlots && g_pool_bytes + cap <= kPoolMaxBytes) {
+                g_pool.push_back({p, cap});
+                g_pool_bytes += cap;
+                kept = true;
+            }
+        }
+        if (!kept) cudaFreeHost(p);
+    } else {
+        std::free(p);
+    }
     p = nullptr;
+    cap = 0;
 }
 
 static std::mutex g_err_mu;
@@ -129,7 +170,7 @@ int hc_pack(const hc_reads* rd, hc_packed** out) {
 
     // pass 1: which quality chars occur -> dense codes; where each read's op stream starts.
     // Every read's op stream starts on a 16-byte boundary (8 records) so that one TMA bulk copy moves it.
-    // Both passes run on up to 8 host threads (reads are independent once the start offsets are known).
+    // Both passes run on up to 16 host threads (reads are independent once the start offsets are known).
     std::vector<int64_t> start(static_cast<size_t>(n) + 1, 0);
     for (int r = 0; r < n; ++r) {
         int64_t ops = 0;
@@ -170,6 +211,16 @@ int hc_pack(const hc_reads* rd, hc_packed** out) {
         }
         p->qual_chars[K] = static_cast<uint8_t>(c);
         code_of[c] = K++;
+    }
+    struct Lut { uint16_t op[256]; uint16_t base[256]; uint8_t cons[256]; uint8_t bad[256]; } lut;
+    uint16_t qual_lut[256];
+    for (int c = 0; c < 256; ++c) {
+        const int oc = op_code(static_cast<uint8_t>(c));
+        lut.bad[c] = oc < 0;
+        lut.op[c] = static_cast<uint16_t>((oc < 0 ? 0 : oc) << HC_OP_SHIFT);
+        lut.cons[c] = (oc == HC_OP_M || oc == HC_OP_I || oc == HC_OP_S) ? 1 : 0;
+        lut.base[c] = static_cast<uint16_t>(base_code(static_cast<uint8_t>(c)) << HC_BASE_SHIFT);
+        qual_lut[c] = static_cast<uint16_t>((code_of[c] < 0 ? 0 : code_of[c]) << HC_QUAL_SHIFT);
     }
     if (total_ops >= (int64_t(1) << 32) - 64) {
         hc::set_global_error("hc_pack: more than 2^32 CIGAR ops in one batch; split the batch");
@@ -217,25 +268,51 @@ int hc_pack(const hc_reads* rd, hc_packed** out) {
                 h.ext[2 * s + 1] = rd->seg_end[k] + trail;
                 h.ops_off[s] = static_cast<uint32_t>(w);
                 h.n_ops[s] = nc;
-                int qi = 0;
-                bool ins = false, plain = true;      // plain: only M between the leading and the trailing clip run
-                for (int t = 0; t < nc; ++t) {
-                    const int op = op_code(cg[t]);
-                    if (op < 0) {
-                        my_error = std::string("hc_pack: CIGAR op '") + static_cast<char>(cg[t]) +
-                                   "' is outside MIDSH (the reference's walk does not define it)";
-                        break;
-                    }
-                    uint16_t rec = static_cast<uint16_t>(op << HC_OP_SHIFT);
-                    if (op == HC_OP_M || op == HC_OP_I || op == HC_OP_S) {
-                        if (qi >= nq) { my_error = "hc_pack: CIGAR consumes more query bases than the read has"; break; }
-                        rec |= static_cast<uint16_t>(base_code(sq[qi]) << HC_BASE_SHIFT) | static_cast<uint16_t>(code_of[ql[qi]] << HC_QUAL_SHIFT);
-                        ++qi;
-                    }
-                    ins |= (op == HC_OP_I);
-                    if (t >= lead && t < nc - trail && op != HC_OP_M) plain = false;
-                    ops_out[static_cast<size_t>(w++)] = rec;
+                // branch-free record build from look-up tables; the usual segment (clips, M only, clips) takes the
+                // middle run without looking at the CIGAR again
+                int ncons = 0;
+                unsigned bad = 0, ins_acc = 0, nonm = 0;
+                for (int t = 0; t < nc; ++t) { ncons += lut.cons[cg[t]]; bad |= lut.bad[cg[t]]; }
+                if (bad) {
+                    for (int t = 0; t < nc; ++t)
+                        if (lut.bad[cg[t]]) {
+                            my_error = std::string("hc_pack: CIGAR op '") + static_cast<char>(cg[t]) +
+                                       "' is outside MIDSH (the reference's walk does not define it)";
+                            break;
+                        }
+                    break;
                 }
+                if (ncons > nq) { my_error = "hc_pack: CIGAR consumes more query bases than the read has"; break; }
+                uint16_t* dst = ops_out + static_cast<size_t>(w);
+                int qi = 0;
+                const int mid0 = std::min(lead, nc), mid1 = std::max(mid0, nc - trail);
+                auto generic_run = [&](int t0, int t1, bool count_nonm) {
+                    for (int t = t0; t < t1; ++t) {
+                        const uint8_t c = cg[t];
+                        const unsigned k = lut.cons[c];
+                        const int qc = qi < nq ? qi : (nq > 0 ? nq - 1 : 0);
+                        const uint16_t bq = nq > 0 ? static_cast<uint16_t>(lut.base[sq[qc]] | qual_lut[ql[qc]]) : uint16_t(0);
+                        dst[t] = static_cast<uint16_t>(lut.op[c] | (bq & static_cast<uint16_t>(0u - k)));
+                        qi += (int)k;
+                        ins_acc |= (c == 'I');
+                        if (count_nonm) nonm |= (c != 'M');
+                    }
+                };
+                generic_run(0, mid0, false);
+                bool all_m = true;
+                for (int t = mid0; t < mid1; ++t) all_m &= (cg[t] == 'M');
+                if (all_m) {
+                    const uint16_t opm = static_cast<uint16_t>(HC_OP_M << HC_OP_SHIFT);
+                    const int d = qi - mid0;
+                    for (int t = mid0; t < mid1; ++t) dst[t] = static_cast<uint16_t>(opm | lut.base[sq[t + d]] | qual_lut[ql[t + d]]);
+                    qi += mid1 - mid0;
+                } else {
+                    generic_run(mid0, mid1, true);
+                }
+                generic_run(mid1, nc, false);
+                w += nc;
+                const bool ins = ins_acc != 0;
+                bool plain = nonm == 0;
                 if (lead + trail > nc) plain = false;             // a segment made of clips only
                 h.seg_flags[s] = static_cast<uint16_t>((ins ? HC_SEG_HAS_INS : 0) | (plain ? 0 : HC_SEG_NOT_PLAIN));
                 read_ops += nc;

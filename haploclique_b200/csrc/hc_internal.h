@@ -26,16 +26,17 @@ void build_prob0_ladder(std::vector<double>& F, int n_max);
 // and plain malloc otherwise (packing itself never needs a GPU).
 struct HostBuf {
     void* p = nullptr;
+    size_t cap = 0;
     bool pinned = false;
     bool alloc(size_t bytes);
     void release();
     ~HostBuf() { release(); }
 };
 
-// f(begin, end) over [0, n) on up to 8 host threads (per-batch host work: packing, band layout, work items).
+// f(begin, end) over [0, n) on up to 16 host threads (per-batch host work: packing, band layout, work items).
 template <class F>
 void parallel_ranges(int n, int min_per_thread, F f) {
-    int T = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 8u);
+    int T = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
     T = std::max(1, std::min(T, n / std::max(1, min_per_thread)));
     if (T <= 1) { f(0, n); return; }
     std::vector<std::thread> pool;
