@@ -107,6 +107,7 @@ struct DevParams {
     double amb_tol;
     const double* table;       // [2][K][K]: equal-base block, then unequal-base block
     const double* simpson;     // dense map or nullptr
+    const double* simpson_q;   // the addend of a tail column at each position: the map's entry, log10(0.25) where it has none
     const double* ladder;      // F[n] = n sequential additions of log10(0.25)
     int K, KK;
     int simpson_len;
@@ -477,7 +478,7 @@ struct hc_ctx {
     hc_read_hdr* d_hdr = nullptr;
     uint16_t* d_ops = nullptr;
     double* d_table = nullptr;
-    double* d_simpson = nullptr;
+    double* d_simpson = nullptr; double* d_simpson_q = nullptr;
     double* d_ladder = nullptr;
     int ladder_len = 0;
     std::vector<int32_t> cov_first, cov_last_pmax;   // host copies for the band layout
@@ -547,6 +548,7 @@ DevParams dev_params(const hc_ctx* c) {
     P.amb_tol = c->par.ambiguity_rel_tol > 0 ? c->par.ambiguity_rel_tol : 1e-12;
     P.table = c->d_table;
     P.simpson = c->d_simpson;
+    P.simpson_q = c->d_simpson_q;
     P.ladder = c->d_ladder;
     P.K = c->K;
     P.KK = c->K * c->K;
@@ -846,6 +848,11 @@ int hc_create(const hc_params* params, hc_ctx** out) {
         const size_t bytes = c->simpson_host.size() * sizeof(double);
         if ((e = cudaMalloc((void**)&c->d_simpson, bytes)) != cudaSuccess) return fail("cudaMalloc", e);
         if ((e = cudaMemcpy(c->d_simpson, c->simpson_host.data(), bytes, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("cudaMemcpy", e);
+        std::vector<double> addend(c->simpson_host);
+        const double lq = std::log10(0.25);
+        for (double& d : addend) if (d == 0.0) d = lq;
+        if ((e = cudaMalloc((void**)&c->d_simpson_q, bytes)) != cudaSuccess) return fail("cudaMalloc", e);
+        if ((e = cudaMemcpy(c->d_simpson_q, addend.data(), bytes, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("cudaMemcpy", e);
     }
     *out = c;
     return HC_OK;
@@ -854,7 +861,7 @@ int hc_create(const hc_params* params, hc_ctx** out) {
 void hc_destroy(hc_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaFree(c->d_hdr); cudaFree(c->d_ops); cudaFree(c->d_table); cudaFree(c->d_simpson); cudaFree(c->d_ladder);
+    cudaFree(c->d_hdr); cudaFree(c->d_ops); cudaFree(c->d_table); cudaFree(c->d_simpson); cudaFree(c->d_simpson_q); cudaFree(c->d_ladder);
     cudaFree(c->d_col0); cudaFree(c->d_word_off); cudaFree(c->d_adj); cudaFree(c->d_stats); cudaFree(c->d_amb);
     cudaFree(c->d_pi); cudaFree(c->d_pj); cudaFree(c->d_res); cudaFree(c->d_flush);
     cudaFree(c->d_aux); cudaFree(c->d_col2op); cudaFree(c->d_tprog); cudaFree(c->d_items); cudaFree(c->d_item_counter);

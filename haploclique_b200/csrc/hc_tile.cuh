@@ -175,13 +175,17 @@ __device__ __forceinline__ void cheap_with(const int* hA, const int* hB, uint32_
             else shape = 3;
             set_cur(L, 0, x, 0);
             set_cur(L, 1, y, 0);
-            if (shape < 2) { L.ref = xs1; tf(0, x, xs2, L); }
-            else { L.ref = xs2; tf(1, y, xs1, L); }
+            {   // one call site: lanes whose leading tail is on different sides walk them together
+                const bool first = shape < 2;
+                L.ref = first ? xs1 : xs2;
+                tf(first ? 0 : 1, first ? x : y, first ? xs2 : xs1, L);
+            }
             break;
         }
         case M_SPOST: {
-            if (shape == 0 || shape == 2) tf(1, y, hB[(5 + 2 * y) * 32] + 1, L);
-            else tf(0, x, hA[5 + 2 * x] + 1, L);
+            const bool onB = shape == 0 || shape == 2;
+            const int eA = hA[5 + 2 * x], eB = hB[(5 + 2 * y) * 32];
+            tf(onB ? 1 : 0, onB ? y : x, (onB ? eB : eA) + 1, L);
             break;
         }
         default: break;
@@ -198,10 +202,14 @@ __device__ __forceinline__ void cheap(const Args& a, const int* hA, const int* h
 }
 
 // A run of noOverlapCheckgap steps (:234-267) when an allele-frequency map is set: prob0 is a running sum in column
-// order (computeProb0, :133-143), so every tail column is visited (the O(1) evaluation of hc_tile.cuh needs the ladder).
-// Segments that are "clips, plain M, clips" need no record reads; the others read the raw records from global memory.
+// order (computeProb0, :133-143), so every tail column is visited (the O(1) evaluation above needs the ladder).
+// The walk goes from one run of M ops to the next: inside a run a column is one addend (the map's entry at that position,
+// or log10(0.25) where it has none -- tabulated in P.simpson_q) added in column order, with no record reads. Where the
+// runs end is known from the header for "clips, plain M, clips" segments and from the prefix counts (aux) otherwise:
+// ops [c, c+k) are all M iff both counters advance by k. Everything else (I, D, clips inside the range, positions
+// outside the map) takes the single-column step.
 struct TailWalk {
-    const Args& a; const int* hA; const int* hB; const uint16_t* rawA; const uint16_t* rawB; double* prob0;
+    const Args& a; const int* hA; const int* hB; const uint16_t* rawA; const uint16_t* rawB; double* prob0; int rA, rB;
     __device__ __forceinline__ void operator()(int side, int seg, int limit, Lane& L) const {
         if (limit - L.ref <= 0) return;
         const int* h = side ? hB : hA;
@@ -212,13 +220,47 @@ struct TailWalk {
         const int lead = h[(2 * seg) * st] - h[(4 + 2 * seg) * st];
         const int trail = h[(5 + 2 * seg) * st] - h[(1 + 2 * seg) * st];
         const uint16_t* raw = (side ? rawB : rawA) + (seg ? h[10 * st] : 0);
+        const uint32_t* ax = a.aux + (size_t)(unsigned)h[(8 + seg) * st] + 2u * (unsigned)(side ? rB : rA) + seg;
         int ref = L.ref, tc = L.tc;
         double p0 = *prob0;
         while (ref < limit) {
             if (c >= n) { L.undef = true; break; }
-            int op;
-            if (fl == 0) op = (c >= lead && c < n - trail) ? (int)HC_OP_M : (int)HC_OP_S;
-            else op = (int)HC_REC_OP((uint32_t)__ldg(raw + c));
+            int k;                                               // length of the run of M ops at c, cut at the limit
+            if (fl == 0) {
+                if (c < lead || c >= n - trail) {                // a clip run: columns pass, nothing is added
+                    const int s = min((c < lead ? lead : n) - c, limit - ref);
+                    c += s; ref += s;
+                    continue;
+                }
+                k = min(n - trail - c, limit - ref);
+            } else {
+                const int kmax = min(n - c, limit - ref);
+                const uint32_t x0 = __ldg(ax + c);
+                if (__ldg(ax + c + kmax) - x0 == (uint32_t)kmax * 0x10001u) k = kmax;
+                else {
+                    int lo = 0, hi = kmax;                       // ops [c, c+lo) are all M, [c, c+hi) are not
+                    while (hi - lo > 1) {
+                        const int mid = (lo + hi) >> 1;
+                        if (__ldg(ax + c + mid) - x0 == (uint32_t)mid * 0x10001u) lo = mid; else hi = mid;
+                    }
+                    k = lo;
+                }
+            }
+            if (k > 0 && ref >= 0 && ref + k <= a.P.simpson_len) {
+                const double* mq = a.P.simpson_q + ref;
+                int t = 0;
+                if (ref & 1) { p0 = __dadd_rn(p0, __ldg(mq)); t = 1; }          // 16-byte loads from here on
+                for (; t + 4 <= k; t += 4) {
+                    const double2 u = __ldg(reinterpret_cast<const double2*>(mq + t));
+                    const double2 v = __ldg(reinterpret_cast<const double2*>(mq + t + 2));
+                    p0 = __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(p0, u.x), u.y), v.x), v.y);
+                }
+                for (; t < k; ++t) p0 = __dadd_rn(p0, __ldg(mq + t));
+                tc += k; c += k; ref += k;
+                continue;
+            }
+            // one column, any op
+            const int op = fl == 0 ? (int)HC_OP_M : (int)HC_REC_OP((uint32_t)__ldg(raw + c));
             if (op == HC_OP_M || op == HC_OP_I) {
                 tc++;
                 double d = 0.0;
@@ -543,7 +585,7 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
                 L.ref = 0; L.cc = 0; L.tc = 0; L.probM = 1.0; L.curs = 0ull; L.gap = false; L.undef = false;
                 int shape = 0;
                 double prob0_run = 0.0;                             // MAP: the running sum of the tail columns
-                TailWalk tail_walk{a, hA, hB, a.ops + infA.ops_off, rawB, &prob0_run};
+                TailWalk tail_walk{a, hA, hB, a.ops + infA.ops_off, rawB, &prob0_run, i, j};
                 TailO1 tail_o1{a, hA, hB, i, j};
                 auto cheap = [&](const Args&, const int*, const int*, int, int, uint32_t mo_, Lane& L_, int& shape_) {
                     if (MAP) cheap_with(hA, hB, mo_, L_, shape_, tail_walk);

@@ -343,7 +343,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) score_tile2_kernel(const Ar
                 L.ref = 0; L.cc = 0; L.tc = 0; L.probM = 1.0; L.curs = 0ull; L.gap = false; L.undef = false;
                 int shape = 0;
                 double prob0_run = 0.0;                             // MAP: the running sum of the tail columns
-                TailWalk tail_walk{a, hA, hB, rawA, rawB, &prob0_run};
+                TailWalk tail_walk{a, hA, hB, rawA, rawB, &prob0_run, i, j};
                 TailO1 tail_o1{a, hA, hB, i, j};
                 auto cheap = [&](const Args2&, const int*, const int*, int, int, uint32_t mo_, Lane& L_, int& shape_) {
                     if (MAP) cheap_with(hA, hB, mo_, L_, shape_, tail_walk);

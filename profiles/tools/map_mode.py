@@ -11,11 +11,12 @@ simpson = {int(p): float(np.log10(rng.uniform(0.3, 1.0))) for p in range(1, 9720
 calc = edge.NewEdgeCalculator(maxPosition=b.max_position() + 2000, device=0, simpson_map=simpson, noProb0=False)
 calc.upload(b)
 out = {}
-for name, mode in (("tiled2_map", edge.KERNEL_TILED2), ("generic", edge.KERNEL_GENERIC)):
+for name, mode in (("tiled2_map", edge.KERNEL_TILED2), ("tiled_map", edge.KERNEL_TILED), ("streamed_map", edge.KERNEL_STREAMED),
+                   ("generic", edge.KERNEL_GENERIC)):
     calc.set_kernel(mode)
     calc.score_band(fetch=False, amb_cap=0)
     adj = calc.score_band(amb_cap=0)
     out[name] = {"kernel_ms": adj.stats["kernel_ms"], "edges": adj.stats["edges"], "pairs_scored": adj.stats["pairs_scored"],
                  "sum_cc": adj.stats["sum_cc"], "sum_tc": adj.stats["sum_tc"], "words_sha": __import__("hashlib").sha256(adj.words.tobytes()).hexdigest()[:16]}
-out["identical_words"] = out["tiled2_map"]["words_sha"] == out["generic"]["words_sha"]
+out["identical_words"] = len({out[k]["words_sha"] for k in ("tiled2_map", "tiled_map", "streamed_map", "generic")}) == 1
 print(json.dumps(out))
