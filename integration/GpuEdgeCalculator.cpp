@@ -101,6 +101,7 @@ void GpuEdgeCalculator::scoreBatch(const std::deque<AlignmentRecord*>& reads) {
 
 void GpuEdgeCalculator::scoreBatch(const std::vector<const AlignmentRecord*>& reads) {
     index_.clear();
+    reads_ = reads;
     for (size_t k = 0; k < reads.size(); ++k) index_[reads[k]] = (int)k;
     Flat f;
     flatten(reads, f);
@@ -149,6 +150,22 @@ bool GpuEdgeCalculator::edgeBetween(const AlignmentRecord& ap1, const AlignmentR
     }
     if (rc != HC_OK) fail("hc_score_pairs", rc);
     return res.edge != 0;
+}
+
+void GpuEdgeCalculator::neighbours(const AlignmentRecord& ap, std::vector<const AlignmentRecord*>& out) const {
+    out.clear();
+    const auto it = index_.find(&ap);
+    if (it == index_.end()) return;
+    const int i = it->second;
+    const int64_t w0 = word_off_[i], w1 = word_off_[(size_t)i + 1];
+    for (int64_t w = w0; w < w1; ++w) {
+        uint32_t bits = words_[(size_t)w];
+        while (bits) {
+            const int b = __builtin_ctz(bits);
+            bits &= bits - 1;
+            out.push_back(reads_[(size_t)col0_[i] + (size_t)(w - w0) * 32 + b]);
+        }
+    }
 }
 
 void GpuEdgeCalculator::getPartnerLengthRange(const AlignmentRecord&, unsigned int*, unsigned int*) const { assert(false); }

@@ -45,6 +45,10 @@ public:
      *  src/BronKerbosch.cpp:286). Two records outside the scored batch (the reference's unit tests call it that way)
      *  are packed as a two-read batch and scored on the GPU. */
     virtual bool edgeBetween(const AlignmentRecord& ap1, const AlignmentRecord& ap2) const;
+    /** The earlier arrivals of the scored batch that are adjacent to `ap`, in arrival order, read straight from the set
+     *  bits of its adjacency row: the row-consuming alternative to one edgeBetween call per active read in the finders'
+     *  edge-feeding loops (src/CLEVER.cpp:218-232, src/BronKerbosch.cpp:286-292). Same answers as edgeBetween. */
+    void neighbours(const AlignmentRecord& ap, std::vector<const AlignmentRecord*>& out) const;
     /** Not implemented by NewEdgeCalculator either (src/NewEdgeCalculator.cpp:1378-1380). */
     virtual void getPartnerLengthRange(const AlignmentRecord& ap, unsigned int* min, unsigned int* max) const;
     virtual void setOverlapCliques(double d);
@@ -63,6 +67,7 @@ private:
     std::vector<double> simpson_;
     hc_ctx* ctx_;
     std::unordered_map<const AlignmentRecord*, int> index_;   // record -> arrival index in the scored batch
+    std::vector<const AlignmentRecord*> reads_;              // arrival index -> record
     std::vector<int32_t> col0_;
     std::vector<int64_t> word_off_;
     std::vector<uint32_t> words_;

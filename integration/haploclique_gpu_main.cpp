@@ -103,6 +103,22 @@ int main(int argc, char* argv[]) {
         }
         calc->scoreBatch(kept);                            // <- the GPU pass: every edge of this iteration
         gpu_ms += calc->kernelMilliseconds();
+        if (std::getenv("HC_GPU_CHECK_ROWS")) {            // self-check of the row-consuming hook against the per-pair answers
+            long from_rows = 0, from_pairs = 0, mismatches = 0;
+            std::vector<const AlignmentRecord*> nb;
+            for (size_t i = 0; i < kept.size(); ++i) {
+                calc->neighbours(*kept[i], nb);
+                from_rows += (long)nb.size();
+                size_t k = 0;
+                for (size_t j = 0; j < i; ++j) {
+                    if (!calc->edgeBetween(*kept[i], *kept[j])) continue;
+                    from_pairs++;
+                    if (k >= nb.size() || nb[k] != kept[j]) mismatches++;
+                    k++;
+                }
+            }
+            cout << "\trows " << (mismatches == 0 && from_rows == from_pairs ? "ok" : "MISMATCH") << ": " << from_rows << " neighbours";
+        }
         for (AlignmentRecord* r : dropped) delete r;
         for (const AlignmentRecord* r : kept) {
             unique_ptr<AlignmentRecord> al(const_cast<AlignmentRecord*>(r));

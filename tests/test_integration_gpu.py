@@ -83,3 +83,12 @@ def test_cli_fasta_identical(tmp_path, finder):
                      [ln for ln in r.stdout.splitlines() if "edges:" in ln or ln.startswith("final")])
     assert outs["ref"][0] == outs["gpu"][0] and len(outs["ref"][0]) > 0
     assert outs["ref"][1] == outs["gpu"][1]
+    # the row-consuming hook (GpuEdgeCalculator::neighbours: the set bits of a read's adjacency row) gives the same
+    # neighbours, in the same order, as one edgeBetween call per earlier read -- checked by the CLI itself in every round
+    d = tmp_path / "rows"
+    d.mkdir()
+    cmd = [pyref.CLI_GPU] + ([finder] if finder == "bronkerbosch" else []) + flags + [bam]
+    r = subprocess.run(cmd, cwd=str(d), capture_output=True, text=True, timeout=300, env=dict(os.environ, HC_GPU_CHECK_ROWS="1"))
+    assert r.returncode == 0, r.stderr[-500:]
+    assert "rows ok" in r.stdout and "MISMATCH" not in r.stdout
+    assert open(d / "quasispecies.fasta", "rb").read() == outs["ref"][0]
