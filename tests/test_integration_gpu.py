@@ -59,19 +59,15 @@ def test_unit_expectations_through_the_adapter(golden):
         assert R.edge_gpu(case["ap1"], case["ap2"]) == case["expected"] == R.edge(case["ap1"], case["ap2"]), name
 
 
-@pytest.mark.parametrize("finder", ["clever", "bronkerbosch"])
-def test_cli_fasta_identical(tmp_path, finder):
-    if not (os.path.exists(pyref.CLI_REF) and os.path.exists(pyref.CLI_GPU)):
-        pytest.skip("CLI binaries not built")
-    # a synthetic BAM written with the reference's vendored BamWriter, then both CLIs on it
-    q = synth.quasispecies(300, genome_len=1200, seed=9, indel_err=1e-3, clip_frac=0.05)
+def _both_clis(tmp_path, batch, flags, finder, genome_len):
+    """Writes `batch` as a BAM with the reference's vendored BamWriter, runs the unmodified CLI and the GPU-backed CLI on
+    it: same per-round stdout lines (read and edge counts), byte-identical FASTA; then the GPU CLI once more with the
+    row-consuming hook's self-check on."""
     W = pyref.Reference()
     bam = str(tmp_path / "reads.bam")
-    W.bam_writer_open(bam, "ref", 1300)
-    W.add_batch(q)
+    W.bam_writer_open(bam, "ref", genome_len)
+    W.add_batch(batch)
     W.bam_writer_close()
-    # default cutoffs (the weak cram-test ones make CLEVER itself run for minutes on this input); 7 rounds, ~2 s on CPU
-    flags = ["--no_prob0", "--no_singletons", "--significance=4"]
     outs = {}
     for tag, exe in (("ref", pyref.CLI_REF), ("gpu", pyref.CLI_GPU)):
         d = tmp_path / tag
@@ -92,3 +88,25 @@ def test_cli_fasta_identical(tmp_path, finder):
     assert r.returncode == 0, r.stderr[-500:]
     assert "rows ok" in r.stdout and "MISMATCH" not in r.stdout
     assert open(d / "quasispecies.fasta", "rb").read() == outs["ref"][0]
+    return outs["ref"][1]
+
+
+@pytest.mark.parametrize("finder", ["clever", "bronkerbosch"])
+def test_cli_fasta_identical(tmp_path, finder):
+    if not (os.path.exists(pyref.CLI_REF) and os.path.exists(pyref.CLI_GPU)):
+        pytest.skip("CLI binaries not built")
+    q = synth.quasispecies(300, genome_len=1200, seed=9, indel_err=1e-3, clip_frac=0.05)
+    # default cutoffs (the weak cram-test ones make CLEVER itself run for minutes on this input); 7 rounds, ~2 s on CPU
+    _both_clis(tmp_path, q, ["--no_prob0", "--no_singletons", "--significance=4"], finder, 1300)
+
+
+@pytest.mark.parametrize("no_prob0", [False, True])
+def test_cli_fasta_identical_on_the_bundled_hiv_reads(tmp_path, no_prob0):
+    """BASELINE configs[0]: the records of the reference's bundled test/data/simulation/reads_HIV-1_50_01.bam (1836 after
+    mate merging, tests/golden/hiv50_records.npz), default NewEdgeCalculator parameters: BAM -> FASTA through both CLIs."""
+    if not (os.path.exists(pyref.CLI_REF) and os.path.exists(pyref.CLI_GPU)):
+        pytest.skip("CLI binaries not built")
+    b = common.load_batch("hiv50_records.npz")
+    flags = (["--no_prob0"] if no_prob0 else []) + ["--no_singletons", "--significance=4"]
+    lines = _both_clis(tmp_path, b, flags, "clever", b.max_position() + 100)
+    assert ("edges: 19233" if no_prob0 else "edges: 220") in lines[0]           # iteration 0 (SURVEY.md 8(c)(iv): 220)
