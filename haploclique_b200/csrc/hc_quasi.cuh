@@ -81,6 +81,16 @@ __device__ __forceinline__ void compute_offsets(int s1, int s2, int e1, int e2, 
     }
 }
 
+// exp() with gradual underflow. CUDA's exp(double) returns 0 once the result is subnormal; glibc (the reference) rounds
+// to the subnormal grid, and pow(subnormal, 1/n) is an ordinary number (1e-310 ^ (1/700) = 0.36), so the difference
+// decides edges at low cutoffs. Below log(DBL_MIN): exp(x + 128 ln 2) in the normal range, scaled by 2^-128 (one
+// rounding to the subnormal grid). The pairs are flagged HC_QUASI_SUBNORMAL either way.
+__device__ __forceinline__ double exp_gradual(double x) {
+    if (x >= -708.3964185322641) return exp(x);
+    if (x < -745.2) return 0.0;
+    return scalbn(exp(x + 88.722839111672999), -128);
+}
+
 __device__ __forceinline__ void add_simpson(const QParams& P, int pos, double& acc) {
     if (P.simpson_ln != nullptr && pos >= 0 && pos < P.simpson_len) acc = __dadd_rn(acc, __ldg(P.simpson_ln + pos));
 }
@@ -174,7 +184,7 @@ __device__ __forceinline__ bool single_overlap_fast(const SegV& A, const SegV& B
         }
     }
     if (acc < -708.3964185322641) subnormal = true;
-    result = pow(exp(acc), __ddiv_rn(1.0, total_size));
+    result = pow(exp_gradual(acc), __ddiv_rn(1.0, total_size));
     return true;
 }
 
@@ -279,7 +289,7 @@ __device__ double single_overlap(const SegV& A, const SegV& B, const QParams& P,
     }
     if (perfect) return 1.0;
     if (overlap_probability < -708.3964185322641) subnormal = true;                         // log(DBL_MIN)
-    return pow(exp(overlap_probability), __ddiv_rn(1.0, total_size));                       // :425
+    return pow(exp_gradual(overlap_probability), __ddiv_rn(1.0, total_size));                       // :425
 }
 
 __device__ __forceinline__ SegV seg_view(const hc_read_hdr& h, const uint16_t* ops, int s) {

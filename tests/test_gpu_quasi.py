@@ -99,6 +99,24 @@ def test_quasi_super_read_round(frameshift):
             assert adj.count() == int(e.sum()) and (ai == pi[e]).all() and (aj == pj[e]).all()
 
 
+def test_quasi_gradual_underflow_decides_edges():
+    """exp(sum) in the subnormal range is not 0 for the reference (glibc rounds to the subnormal grid) and
+    pow(subnormal, 1/n) is an ordinary number (1e-310 ^ (1/700) = 0.36): with low cutoffs such pairs ARE edges. The device
+    has to underflow gradually too (CUDA's exp alone returns 0 there). Found by profiles/tools/fuzz_parity.py."""
+    b = synth.super_reads(100, seed=5)
+    kw = dict(overlap_single=0.3, overlap=0.3, edge_quasi_cutoff_single=0.2, edge_quasi_cutoff_mixed=0.2, edge_quasi_cutoff=0.2,
+              maxPosition=b.max_position() + 10)
+    pi, pj = common.tri_pairs(b.n)
+    orc = pyoracle.QuasiOracle(b, **kw).pairs(pi, pj)
+    sub_edges = (orc["subnormal"] != 0) & (orc["status"] != 3) & (orc["edge"] == 1)
+    assert int(sub_edges.sum()) >= 10
+    calc = edge.QuasispeciesEdgeCalculator(**kw)
+    calc.upload(b)
+    dev = calc.score_pairs(pi, pj)
+    assert _compare(dev, orc, "quasi-underflow") == 0
+    assert (dev["edge"][sub_edges] == 1).all() and (dev["q"][sub_edges] > 0.2).all()
+
+
 def test_quasi_reference_interface():
     b = synth.quasispecies(300, genome_len=1500, seed=9)
     calc = edge.QuasispeciesEdgeCalculator(overlap_single=0.3, edge_quasi_cutoff_single=0.8, maxPosition=b.max_position())
