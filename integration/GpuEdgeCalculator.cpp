@@ -118,7 +118,19 @@ void GpuEdgeCalculator::scoreBatch(const std::vector<const AlignmentRecord*>& re
     int64_t n_words = 0;
     if ((rc = hc_band_layout(ctx_, 0, n, col0_.data(), word_off_.data(), &n_words)) != HC_OK) fail("hc_band_layout", rc);
     words_.assign((size_t)std::max<int64_t>(n_words, 1), 0u);
-    if ((rc = hc_score_band(ctx_, 0, n, words_.data(), n_words, nullptr, 0, &stats_)) != HC_OK) fail("hc_score_band", rc);
+    if ((rc = scoreResident(n, words_.data(), n_words, &stats_)) != HC_OK) fail("hc_score_band", rc);
+}
+
+int GpuEdgeCalculator::scoreResident(int n, uint32_t* words, int64_t n_words, hc_band_stats* stats) {
+    return hc_score_band(ctx_, 0, n, words, n_words, nullptr, 0, stats);
+}
+
+int GpuEdgeCalculator::scoreResidentPair(int i, int j, bool* edge) const {
+    hc_pair_result res;
+    const int32_t pi = i, pj = j;
+    const int rc = hc_score_pairs(ctx_, &pi, &pj, 1, &res);
+    if (rc == HC_OK) *edge = res.edge != 0;
+    return rc;
 }
 
 bool GpuEdgeCalculator::edgeBetween(const AlignmentRecord& ap1, const AlignmentRecord& ap2) const {
@@ -140,16 +152,15 @@ bool GpuEdgeCalculator::edgeBetween(const AlignmentRecord& ap1, const AlignmentR
     int rc = hc_pack(&view, &pk);
     if (rc != HC_OK) throw std::runtime_error(std::string("GpuEdgeCalculator: hc_pack failed: ") + hc_last_error(nullptr));
     rc = hc_upload(ctx_, pk);
-    hc_pair_result res;
-    const int32_t pi = 1, pj = 0;
-    if (rc == HC_OK) rc = hc_score_pairs(ctx_, &pi, &pj, 1, &res);
+    bool edge = false;
+    if (rc == HC_OK) rc = scoreResidentPair(1, 0, &edge);
     hc_packed_free(pk);
     if (resident_ != nullptr) {                            // put the scored batch back for later pair queries
         const int rc2 = hc_upload(ctx_, resident_);
         if (rc2 != HC_OK) fail("hc_upload", rc2);
     }
     if (rc != HC_OK) fail("hc_score_pairs", rc);
-    return res.edge != 0;
+    return edge;
 }
 
 void GpuEdgeCalculator::neighbours(const AlignmentRecord& ap, std::vector<const AlignmentRecord*>& out) const {
@@ -174,4 +185,38 @@ void GpuEdgeCalculator::setOverlapCliques(double d) {      // NewEdgeCalculator:
     par_.min_overlap_cliques = d;
     const int rc = hc_set_params(ctx_, &par_);
     if (rc != HC_OK) fail("hc_set_params", rc);
+}
+
+// ---- QuasispeciesEdgeCalculator behind the same binding -------------------------------------------------------------
+GpuQuasispeciesEdgeCalculator::GpuQuasispeciesEdgeCalculator(double Q, double edge_quasi_cutoff, double overlap, bool frameshift_merge,
+                                                             std::unordered_map<int, double>& simpson_map,
+                                                             double edge_quasi_cutoff_single, double overlap_single,
+                                                             double edge_quasi_cutoff_mixed, unsigned int maxPosition, int device)
+    : GpuEdgeCalculator(Q, edge_quasi_cutoff, overlap, frameshift_merge, simpson_map, edge_quasi_cutoff_single, overlap_single,
+                        edge_quasi_cutoff_mixed, maxPosition, false, device) {
+    std::memset(&qpar_, 0, sizeof qpar_);
+    qpar_.edge_quasi_cutoff_cliques = edge_quasi_cutoff;
+    qpar_.edge_quasi_cutoff_mixed = edge_quasi_cutoff_mixed;
+    qpar_.edge_quasi_cutoff_single = edge_quasi_cutoff_single;
+    qpar_.min_overlap_cliques = overlap;
+    qpar_.min_overlap_single = overlap_single;
+    qpar_.frameshift_merge = frameshift_merge ? 1 : 0;
+    qpar_.ambiguity_rel_tol = 1e-12;
+}
+
+bool GpuQuasispeciesEdgeCalculator::edgeBetween(const AlignmentRecord& ap1, const AlignmentRecord& ap2) const {
+    if (ap1.getName().compare(ap2.getName()) == 0) return true;          // src/QuasispeciesEdgeCalculator.cpp:56
+    return GpuEdgeCalculator::edgeBetween(ap1, ap2);
+}
+
+int GpuQuasispeciesEdgeCalculator::scoreResident(int n, uint32_t* words, int64_t n_words, hc_band_stats* stats) {
+    return hc_quasi_score_band(context(), &qpar_, 0, n, words, n_words, stats);
+}
+
+int GpuQuasispeciesEdgeCalculator::scoreResidentPair(int i, int j, bool* edge) const {
+    hc_quasi_result res;
+    const int32_t pi = i, pj = j;
+    const int rc = hc_quasi_score_pairs(context(), &qpar_, &pi, &pj, 1, &res);
+    if (rc == HC_OK) *edge = res.edge != 0;
+    return rc;
 }

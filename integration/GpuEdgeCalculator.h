@@ -58,6 +58,12 @@ public:
     long nearThresholdPairs() const { return stats_.ambiguous; }
     double kernelMilliseconds() const { return stats_.kernel_ms; }
 
+protected:
+    /** The scoring calls behind scoreBatch / the out-of-batch edgeBetween; GpuQuasispeciesEdgeCalculator swaps them. */
+    virtual int scoreResident(int n, uint32_t* words, int64_t n_words, hc_band_stats* stats);
+    virtual int scoreResidentPair(int i, int j, bool* edge) const;
+    hc_ctx* context() const { return ctx_; }
+
 private:
     struct Flat;                                           // SoA staging of AlignmentRecord fields (hc_reads)
     static void flatten(const std::vector<const AlignmentRecord*>& reads, Flat& f);
@@ -74,6 +80,28 @@ private:
     hc_band_stats stats_;
     mutable hc_packed* resident_;                          // the scored batch (re-uploaded after an out-of-batch query)
     mutable bool resident_dirty_;
+};
+
+/** The same binding for the reference's older scorer, QuasispeciesEdgeCalculator (src/QuasispeciesEdgeCalculator.h:57,
+ *  .cpp:55-70): constructor arguments in the reference's order plus maxPosition (sizes the dense copy of simpson_map,
+ *  whose values are frequencies here, not log10) and the device. scoreBatch / edgeBetween / neighbours as above, scored by
+ *  hc_quasi_score_band / hc_quasi_score_pairs. The reference's CLI never constructs this class; a maintainer who wants
+ *  it back plugs this one in the same way. Pairs on which the reference's walk would not terminate
+ *  (src/QuasispeciesEdgeCalculator.cpp:258-267) are no edges. */
+class GpuQuasispeciesEdgeCalculator : public GpuEdgeCalculator {
+public:
+    GpuQuasispeciesEdgeCalculator(double Q, double edge_quasi_cutoff, double overlap, bool frameshift_merge,
+                                  std::unordered_map<int, double>& simpson_map, double edge_quasi_cutoff_single,
+                                  double overlap_single, double edge_quasi_cutoff_mixed, unsigned int maxPosition, int device = 0);
+    virtual bool edgeBetween(const AlignmentRecord& ap1, const AlignmentRecord& ap2) const;
+    virtual void setOverlapCliques(double d) { qpar_.min_overlap_cliques = d; }
+
+protected:
+    virtual int scoreResident(int n, uint32_t* words, int64_t n_words, hc_band_stats* stats);
+    virtual int scoreResidentPair(int i, int j, bool* edge) const;
+
+private:
+    hc_quasi_params qpar_;
 };
 
 #endif /* GPUEDGECALCULATOR_H_ */

@@ -207,6 +207,24 @@ class Reference:
                                  C.c_double(edge_quasi_cutoff_mixed), _p(q), _p(e))
         return q, e
 
+    def quasi_gpu_pairs(self, pi, pj, edge_quasi_cutoff=0.99, overlap=0.9, frameshift_merge=False, simpson_map=None,
+                        edge_quasi_cutoff_single=0.95, overlap_single=0.6, edge_quasi_cutoff_mixed=0.97):
+        """The same pairs through integration/'s GpuQuasispeciesEdgeCalculator (needs gpu_adapter=True and a device)."""
+        pi = np.ascontiguousarray(pi, np.int32)
+        pj = np.ascontiguousarray(pj, np.int32)
+        sm = simpson_map or {}
+        pos = np.array(list(sm.keys()), np.int32)
+        val = np.array(list(sm.values()), np.float64)
+        e = np.zeros(pi.shape[0], np.uint8)
+        self.L.hcref_quasi_gpu_pairs.restype = C.c_long
+        n = self.L.hcref_quasi_gpu_pairs(self.h, _p(pi), _p(pj), C.c_long(pi.shape[0]), C.c_double(edge_quasi_cutoff),
+                                         C.c_double(overlap), C.c_int(int(frameshift_merge)), _p(pos), _p(val), C.c_int(len(sm)),
+                                         C.c_double(edge_quasi_cutoff_single), C.c_double(overlap_single),
+                                         C.c_double(edge_quasi_cutoff_mixed), _p(e))
+        if n < 0:
+            raise RuntimeError("hcref_quasi_gpu_pairs failed (%d): %s" % (n, self.L.hcref_error(self.h).decode()))
+        return e
+
     def time_pairs(self, pi, pj, threads: int = 1):
         pi = np.ascontiguousarray(pi, np.int32)
         pj = np.ascontiguousarray(pj, np.int32)

@@ -469,4 +469,36 @@ int hcref_edge_gpu(void* p, int i, int j) {
 #endif
 }
 
+// QuasispeciesEdgeCalculator through the product's binding (integration/: GpuQuasispeciesEdgeCalculator): all stored
+// records scored as one batch, then edgeBetween(records[pi], records[pj]) per pair. Returns the edge count, -1 / -2 as above.
+long hcref_quasi_gpu_pairs(void* p, const int* pi, const int* pj, long npairs, double cut_cliques, double ov_cliques,
+                           int frameshift, const int* simpson_pos, const double* simpson_val, int n_simpson, double cut_single,
+                           double ov_single, double cut_mixed, unsigned char* edge_out) {
+#ifdef HC_WITH_GPU_ADAPTER
+    RefCtx* c = static_cast<RefCtx*>(p);
+    try {
+        std::unordered_map<int, double> simpson;
+        for (int i = 0; i < n_simpson; ++i) simpson[simpson_pos[i]] = simpson_val[i];
+        GpuQuasispeciesEdgeCalculator calc(0.9, cut_cliques, ov_cliques, frameshift != 0, simpson, cut_single, ov_single, cut_mixed,
+                                           c->max_position);
+        std::vector<const AlignmentRecord*> all(c->recs.begin(), c->recs.end());
+        calc.scoreBatch(all);
+        long edges = 0;
+        for (long k = 0; k < npairs; ++k) {
+            const bool e = calc.edgeBetween(*c->recs[pi[k]], *c->recs[pj[k]]);
+            if (edge_out) edge_out[k] = e;
+            edges += e;
+        }
+        return edges;
+    } catch (const std::exception& e) {
+        c->err = e.what();
+        return -2;
+    }
+#else
+    (void)p; (void)pi; (void)pj; (void)npairs; (void)cut_cliques; (void)ov_cliques; (void)frameshift; (void)simpson_pos;
+    (void)simpson_val; (void)n_simpson; (void)cut_single; (void)ov_single; (void)cut_mixed; (void)edge_out;
+    return -1;
+#endif
+}
+
 }  // extern "C"

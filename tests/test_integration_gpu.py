@@ -110,3 +110,28 @@ def test_cli_fasta_identical_on_the_bundled_hiv_reads(tmp_path, no_prob0):
     flags = (["--no_prob0"] if no_prob0 else []) + ["--no_singletons", "--significance=4"]
     lines = _both_clis(tmp_path, b, flags, "clever", b.max_position() + 100)
     assert ("edges: 19233" if no_prob0 else "edges: 220") in lines[0]           # iteration 0 (220)
+
+
+@pytest.mark.parametrize("fixture", ["hiv50_records.npz", "arabis_records.npz"])
+def test_quasispecies_adapter_equals_the_reference_class(fixture):
+    """integration/'s GpuQuasispeciesEdgeCalculator (scoreBatch + edgeBetween answered from the adjacency words) against
+    the reference's own QuasispeciesEdgeCalculator::edgeBetween on the bundled reads. The reference does not terminate
+    on some clipped pairs (src/QuasispeciesEdgeCalculator.cpp:258-267): it is only asked about pairs the oracle walks to
+    the end; on the others the adapter must say "no edge"."""
+    from oracle import pyoracle
+    b = common.load_batch(fixture)
+    kw = dict(overlap_single=0.3, overlap=0.5, edge_quasi_cutoff_single=0.8, edge_quasi_cutoff_mixed=0.85, edge_quasi_cutoff=0.9)
+    pi, pj = common.quasi_pair_sample(b.n)
+    later = pi > pj                                     # the finders' call order: (new arrival, earlier arrival)
+    pi, pj = pi[later], pj[later]
+    orc = pyoracle.QuasiOracle(b, maxPosition=b.max_position(), **kw).pairs(pi, pj)
+    R = pyref.Reference(gpu_adapter=True)
+    R.add_batch(b)
+    R.set_params(maxPosition=b.max_position())
+    dev = R.quasi_gpu_pairs(pi, pj, **kw)
+    ok = orc["status"] != 3
+    assert not dev[~ok].any()
+    q, ref_edge = R.quasi_pairs(pi[ok], pj[ok], **kw)
+    near = np.abs(q - orc["cutoff"][ok]) <= 1e-12 * orc["cutoff"][ok]
+    assert ((dev[ok] == ref_edge) | near).all()
+    assert int(ref_edge.sum()) > 100 and int(ok.sum()) > 10000
