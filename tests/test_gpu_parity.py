@@ -238,10 +238,10 @@ def test_tiled_kernel_row_windows_concatenate(kernel):
     assert (fi == pi_).all() and (fj == pj_).all()
 
 
-def test_full_size_C2_three_kernels_agree():
+def test_full_size_C2_all_band_kernels_agree():
     """BASELINE configs[1] at full size (100k fragments, 4.7e8 scored pairs): the oracle cannot walk that many pairs in
-    test time, so the check is a size-independent property -- the three band kernels (generic one-lane-per-pair walker,
-    first- and second-generation tiled kernels; the walker shares no walking code with the tiled ones) produce the same
+    test time, so the check is a size-independent property -- the four band kernels (generic one-lane-per-pair walker,
+    first- and second-generation tiled kernels, streamed kernel; the walker shares no walking code with the others) produce the same
     adjacency words and the same column totals, row windows concatenate to the full run, and a sample of 200k band
     pairs matches the oracle bit for bit."""
     import bench
@@ -250,12 +250,13 @@ def test_full_size_C2_three_kernels_agree():
     calc = edge.NewEdgeCalculator(**kw)
     calc.upload(b)
     res = {}
-    for name, mode in (("tiled2", edge.KERNEL_TILED2), ("tiled", edge.KERNEL_TILED), ("generic", edge.KERNEL_GENERIC)):
+    for name, mode in (("tiled2", edge.KERNEL_TILED2), ("tiled", edge.KERNEL_TILED), ("streamed", edge.KERNEL_STREAMED),
+                       ("generic", edge.KERNEL_GENERIC)):
         calc.set_kernel(mode)
         res[name] = calc.score_band(amb_cap=0)
         assert calc.last_kernel() == mode
     ref = res["generic"]
-    for name in ("tiled2", "tiled"):
+    for name in ("tiled2", "tiled", "streamed"):
         assert (res[name].words == ref.words).all(), name
         for k in ("pairs_scored", "pairs_walked", "edges", "sum_cc", "sum_tc", "undefined"):
             assert res[name].stats[k] == ref.stats[k], (name, k)
