@@ -991,7 +991,7 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
         if ((rc = grow(c, c->d_opsA, c->cap_opsA, (size_t)nrec)) != HC_OK) return rc;
         if ((rc = grow(c, c->d_opsF, c->cap_opsF, (size_t)nrec)) != HC_OK) return rc;
         c->have_formats = true;
-        tile2::build_formats_kernel<<<(unsigned)((nrec + 255) / 256), 256, 0, c->stream>>>(c->d_ops, nrec, tile2_row_bytes(K), tile2_entry_bytes(K), ord, c->d_opsA, c->d_opsF);
+        tile2::build_formats_kernel<<<(unsigned)((nrec / 8 + 255) / 256), 256, 0, c->stream>>>(c->d_ops, nrec, tile2_row_bytes(K), tile2_entry_bytes(K), ord, c->d_opsA, c->d_opsF);
         CU_TRY(c, cudaGetLastError());
     }
     c->cov_first.resize(p->n_reads);

@@ -46,15 +46,35 @@ constexpr int kRows = 9;
 // ---- row / column formats, built on the device once per upload ---------------------------------------
 struct ColumnOrder { uint8_t slot[128]; };   // position of quality code q inside a table row (a permutation of 0..K-1)
 
-__global__ void build_formats_kernel(const uint16_t* __restrict__ ops, long long n, uint32_t ROW, uint32_t ESZ, ColumnOrder ord,
-                                     uint32_t* __restrict__ opsA, uint16_t* __restrict__ opsF) {
-    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n) return;
-    const uint32_t r = ops[t];
-    const uint32_t base = HC_REC_BASE(r), op = HC_REC_OP(r), q = HC_REC_QUAL(r);
-    const bool esc = op != HC_OP_M || base > 4u;
-    opsA[t] = esc ? A_ESC : ROW * (q * 9u + 4u - base);
-    opsF[t] = (uint16_t)(esc ? B_ESC : ROW * base + ESZ * ord.slot[q]);
+// Eight records per thread (one 16-byte load, three 16-byte stores); the slot table sits in shared memory -- indexed
+// per thread from the kernel parameters it would serialise in the constant cache. n is a multiple of 8 (streams are padded).
+__global__ void __launch_bounds__(256) build_formats_kernel(const uint16_t* __restrict__ ops, long long n, uint32_t ROW, uint32_t ESZ, ColumnOrder ord,
+                                                            uint32_t* __restrict__ opsA, uint16_t* __restrict__ opsF) {
+    __shared__ uint32_t slot_sm[128];
+    if (threadIdx.x < 128) slot_sm[threadIdx.x] = ESZ * ord.slot[threadIdx.x];
+    __syncthreads();
+    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g * 8 >= n) return;
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(ops) + g);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t A[8], F[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        uint32_t f2 = 0;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const uint32_t r = (w[k] >> (16 * h)) & 0xffffu;
+            const uint32_t base = HC_REC_BASE(r), op = HC_REC_OP(r), q = HC_REC_QUAL(r);
+            const bool esc = op != HC_OP_M || base > 4u;
+            A[2 * k + h] = esc ? A_ESC : ROW * (q * 9u + 4u - base);
+            f2 |= ((esc ? B_ESC : ROW * base + slot_sm[q]) & 0xffffu) << (16 * h);
+        }
+        F[k] = f2;
+    }
+    uint4* oa = reinterpret_cast<uint4*>(opsA) + 2 * g;
+    oa[0] = make_uint4(A[0], A[1], A[2], A[3]);
+    oa[1] = make_uint4(A[4], A[5], A[6], A[7]);
+    reinterpret_cast<uint4*>(opsF)[g] = make_uint4(F[0], F[1], F[2], F[3]);
 }
 
 // The lock-step loop of one slot (see tile::overlap for the contract; same results, different operand format).
