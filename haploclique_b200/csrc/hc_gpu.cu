@@ -623,28 +623,43 @@ void build_tile_programs(std::vector<uint32_t>& out) {
     two[SLOT_FINAL] = TILE_MOP(M_SPOST, 1, 1, 0, 0);
 }
 
-struct TileGeom { int maxw, abuf_bytes; size_t smem; };
+struct TileGeom { int maxw, abuf_bytes, nwarps; size_t smem; };
 
+// First-generation tiled kernel: the warp count shrinks (24 -> 8) until tables + column tile + row buffers fit a CTA.
 TileGeom tile_geometry(const hc_ctx* c) {
     TileGeom g;
     g.maxw = (c->max_ops + 1) / 2 + 4;
     g.abuf_bytes = ((c->max_ops * 2 + 15) & ~15) + 32;
-    size_t o = 0;
-    o += ((size_t)2 * c->K * c->K * 8 + 15) & ~(size_t)15;
-    o += (size_t)tile::TP_COUNT * tile::TP_WORDS * 4;
-    o += 16 * 32 * 4;
-    o += (size_t)g.maxw * 128;
-    o += (size_t)tile::kWarps * 2 * (64 + g.abuf_bytes);
-    o += tile::kWarps * 2 * 8;
-    o += 8 * 8;
-    o += 16;
-    g.smem = o;
+    g.nwarps = 0;
+    g.smem = ~size_t(0);
+    for (int w = tile::kWarps; w >= 8; w -= 4) {
+        size_t o = 0;
+        o += ((size_t)2 * c->K * c->K * 8 + 15) & ~(size_t)15;
+        o += (size_t)tile::TP_COUNT * tile::TP_WORDS * 4;
+        o += 16 * 32 * 4;
+        o += (size_t)g.maxw * 128;
+        o += (size_t)w * 2 * (64 + g.abuf_bytes);
+        o += (size_t)w * 2 * 8;
+        o += 8 * 8;
+        o += 16;
+        if (o <= c->smem_optin) { g.nwarps = w; g.smem = o; break; }
+    }
     return g;
+}
+
+// The instantiation of the first-generation kernel for (streamed, allele-frequency map, full 24-warp CTA).
+typedef void (*Tile1Kernel)(const tile::Args);
+Tile1Kernel tile1_kernel(bool stream, bool map, bool full) {
+    const constexpr int W = tile::kWarps;
+    if (stream) return map ? (full ? tile::score_tile_kernel<true, true, W> : tile::score_tile_kernel<true, true, 0>)
+                           : (full ? tile::score_tile_kernel<true, false, W> : tile::score_tile_kernel<true, false, 0>);
+    return map ? (full ? tile::score_tile_kernel<false, true, W> : tile::score_tile_kernel<false, true, 0>)
+               : (full ? tile::score_tile_kernel<false, false, W> : tile::score_tile_kernel<false, false, 0>);
 }
 
 // The tiled kernel needs a column tile that fits (with an allele-frequency map its MAP variant walks the tails).
 bool tile_eligible(const hc_ctx* c) {
-    return tile_geometry(c).smem <= c->smem_optin;
+    return tile_geometry(c).nwarps > 0;
 }
 
 // Streamed variant of the first-generation kernel: only the two probability tables, the programs and the headers live in
@@ -654,6 +669,7 @@ TileGeom stream_geometry(const hc_ctx* c) {
     TileGeom g;
     g.maxw = 0;
     g.abuf_bytes = 0;
+    g.nwarps = tile::kWarps;
     size_t o = 0;
     o += ((size_t)2 * c->K * c->K * 8 + 15) & ~(size_t)15;
     o += (size_t)tile::TP_COUNT * tile::TP_WORDS * 4;
@@ -1073,7 +1089,7 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
         const TileGeom g = use_stream ? stream_geometry(c) : tile_geometry(c);
         const Tile2Geom g2 = tile2_geometry(c);
         const size_t smem_bytes = use_tile2 ? g2.smem : g.smem;
-        const int threads = use_tile2 ? g2.nwarps * 32 : tile::kThreads;
+        const int threads = (use_tile2 ? g2.nwarps : g.nwarps) * 32;
         int per_sm = 0;
         const bool split = c->K <= split_max_k();
         if (use_tile2) {
@@ -1084,8 +1100,7 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
             CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem_bytes));
         } else {
             const bool map = c->d_simpson != nullptr;
-            auto kern = use_stream ? (map ? tile::score_tile_kernel<true, true> : tile::score_tile_kernel<true, false>)
-                                   : (map ? tile::score_tile_kernel<false, true> : tile::score_tile_kernel<false, false>);
+            auto kern = tile1_kernel(use_stream, map, g.nwarps == tile::kWarps);
             CU_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
             CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem_bytes));
         }
@@ -1119,10 +1134,7 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
             else if (use_tile2 && split) tile2::score_tile2_kernel<true, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
             else if (use_tile2 && map) tile2::score_tile2_kernel<false, true><<<blocks, threads, smem_bytes, c->stream>>>(a);
             else if (use_tile2) tile2::score_tile2_kernel<false, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
-            else if (use_stream && map) tile::score_tile_kernel<true, true><<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
-            else if (use_stream) tile::score_tile_kernel<true, false><<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
-            else if (map) tile::score_tile_kernel<false, true><<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
-            else tile::score_tile_kernel<false, false><<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
+            else tile1_kernel(use_stream, map, g.nwarps == tile::kWarps)<<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
             CU_TRY(c, cudaGetLastError());
             launches = 1;
             c->last_kernel = use_tile2 ? HC_KERNEL_TILED2 : (use_stream ? HC_KERNEL_STREAMED : HC_KERNEL_TILED);

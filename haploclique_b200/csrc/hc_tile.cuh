@@ -463,10 +463,13 @@ __device__ __forceinline__ bool tile_layout_reject(const int* hA, const int* hB,
 // G = true: the streamed variant -- no column tile and no row op buffers (a.maxw = 0, a.abuf_bytes = 0); the lock-step loop
 // reads both op streams in place. Everything else (work items, headers, programs, tails, decision) is the same code.
 // MAP = true: an allele-frequency map is set, the tails are walked (TailWalk) instead of evaluated in O(1).
-template <bool G, bool MAP>
+// NW: warps per CTA as a compile-time constant (24, the usual launch) or 0 = read from the launch (a shrunken CTA).
+template <bool G, bool MAP, int NW>
 __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel(const Args a) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nwarps = NW ? NW : (int)(blockDim.x >> 5);          // the host shrinks the CTA (24 -> 8 warps) until it fits
+    const int nthreads = nwarps * 32;
     const int K = a.P.K;
     // ---- shared memory carve-up (every piece a multiple of 16 bytes)
     size_t o = 0;
@@ -474,13 +477,13 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
     uint32_t* progsm = reinterpret_cast<uint32_t*>(smem + o);     o += TP_COUNT * TP_WORDS * 4;
     int* hBsm = reinterpret_cast<int*>(smem + o);                 o += 16 * 32 * 4;
     uint32_t* tileB = reinterpret_cast<uint32_t*>(smem + o);      o += (size_t)a.maxw * 128;
-    unsigned char* rowbuf = smem + o;                             o += (size_t)kWarps * 2 * (64 + a.abuf_bytes);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + o);       o += kWarps * 2 * 8;
+    unsigned char* rowbuf = smem + o;                             o += (size_t)nwarps * 2 * (64 + a.abuf_bytes);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + o);       o += (size_t)nwarps * 2 * 8;
     unsigned long long* cstat = reinterpret_cast<unsigned long long*>(smem + o); o += 8 * 8;
     int* ctl = reinterpret_cast<int*>(smem + o);
 
-    for (int k = tid; k < 2 * K * K; k += kThreads) Tsm[k] = a.P.table[k];
-    for (int k = tid; k < TP_COUNT * TP_WORDS; k += kThreads) progsm[k] = a.prog[k];
+    for (int k = tid; k < 2 * K * K; k += nthreads) Tsm[k] = a.P.table[k];
+    for (int k = tid; k < TP_COUNT * TP_WORDS; k += nthreads) progsm[k] = a.prog[k];
     if (tid < 8) cstat[tid] = 0ull;
     unsigned a_total = 0, a_scored = 0, a_walked = 0, a_edges = 0, a_undef = 0;   // per-lane totals, reduced once at the end
     unsigned long long a_cc = 0, a_tc = 0;
@@ -526,8 +529,7 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
         const int blk = it.x, r0 = it.y, r1 = it.z;
         const int jmine = __ldg(a.colidx + (size_t)blk * 32 + lane);       // this lane's column read (every warp agrees)
         // ---- stage the 32 column reads: headers transposed, op streams interleaved word-wise
-        static_assert(kWarps >= 16, "one thread per (header field, lane)");
-        if (warp < 16) hBsm[warp * 32 + lane] = jmine >= 0 ? __ldg(reinterpret_cast<const int*>(a.hdr + jmine) + warp) : 0;
+        for (int f = warp; f < 16; f += nwarps) hBsm[f * 32 + lane] = jmine >= 0 ? __ldg(reinterpret_cast<const int*>(a.hdr + jmine) + f) : 0;
         const uint32_t* opsB = tileB + lane;
         const uint16_t* rawB = a.ops + (jmine >= 0 ? (unsigned)__ldg(reinterpret_cast<const int*>(a.hdr + jmine) + 8) : 0u);
         if (G) {
@@ -539,7 +541,7 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
                 const int4 h2 = __ldg(reinterpret_cast<const int4*>(a.hdr + j) + 2);
                 const int nchunk = (h2.z + h2.w + 7) >> 3;
                 const uint4* src = reinterpret_cast<const uint4*>(a.ops + (unsigned)h2.x);
-                for (int c = tid >> 5; c < nchunk; c += kWarps) {
+                for (int c = tid >> 5; c < nchunk; c += nwarps) {
                     const uint4 v = __ldg(src + c);
                     uint32_t* d = tileB + (size_t)(4 * c) * 32 + l;
                     d[0] = v.x; d[32] = v.y; d[64] = v.z; d[96] = v.w;

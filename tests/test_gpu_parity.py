@@ -191,6 +191,21 @@ def test_tiled_kernel_matches_oracle_on_golden_sets(golden, label, kernel):
     assert adj.count() == g["edges"]
 
 
+def test_first_generation_tile_shrinks_its_cta_to_fit():
+    """Early super-read rounds: reads of a few hundred columns with ~75 quality codes. Too many codes for the
+    second-generation kernel's 9-row table; the first-generation kernel's tables + tile + 24 warps' row buffers exceed a
+    CTA's shared memory by a little -- it runs with fewer warps instead of handing the batch to the streamed kernel."""
+    b = synth.super_reads(500, genome_len=2500, read_len=450, frag_mean=700.0, frag_sd=120.0, frag_min=300, frag_max=880, seed=31)
+    assert len(np.unique(b.qual)) > 70 and int(b.cig_len.reshape(-1, 2).sum(1).max()) > 870      # 243 KB at 24 warps, 228 KB at 20
+    kw = dict(noProb0=True, maxPosition=b.max_position() + 10, edge_quasi_cutoff=0.9, edge_quasi_cutoff_mixed=0.9,
+              edge_quasi_cutoff_single=0.9, overlap=0.5, overlap_single=0.5)
+    calc = edge.NewEdgeCalculator(**kw)
+    calc.scoreBatch(b)
+    assert calc.last_kernel() == edge.KERNEL_TILED
+    det, orc = _tiled_detail_vs_oracle(b, kw, "tile1-shrunk", edge.KERNEL_TILED)
+    assert int(orc["edge"].sum()) > 100
+
+
 def test_auto_prefers_the_second_generation_tiled_kernel():
     b = synth.quasispecies(300, genome_len=1500, seed=2)
     calc = edge.NewEdgeCalculator(noProb0=True, maxPosition=b.max_position())
