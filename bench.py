@@ -347,7 +347,8 @@ def main():
                        "sharding": "single GPU" if world == 1 else ("%d equal-area row blocks of the replicated set, no collective" % world) if wname == "C5"
                                    else ("%d genome-position windows + %d-column left halo, no collective" % (world, HALO))},
             "pairs": {"scored": scored, "examined": total, "walked": walked, "edges": edges, "sum_cc": sum_cc, "sum_tc": sum_tc,
-                      "rows": rows, "ambiguous_within_1e-12": amb, "undefined": undef},
+                      "rows": rows, "all_pairs": rows * (rows - 1) // 2, "ambiguous_within_1e-12": amb, "undefined": undef},
+            "all_pairs_per_s": rows * (rows - 1) / 2 / secs,
             "column_steps_per_s": (sum_cc + sum_tc) / secs,
             "wall_ms_per_step": ms_wall,
             "e2e": {"value": scored / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
