@@ -146,7 +146,7 @@ __device__ __forceinline__ void tail(const Args& a, const int* hA, const int* hB
 
 // One of the cheap (non-loop) micro-ops. `shape` carries checkGapsSingle's case between SPRE/SOVL/SPOST.
 // TF: how a run of noOverlapCheckgap steps is evaluated -- tf(side, seg, exclusive limit, L).
-template <class TF>
+template <bool MERGE = true, class TF>
 __device__ __forceinline__ void cheap_with(const int* hA, const int* hB, uint32_t m, Lane& L, int& shape, TF& tf) {
     const uint32_t op = m & 15u;
     if (op == M_NOP || L.gap || L.undef) return;
@@ -175,17 +175,21 @@ __device__ __forceinline__ void cheap_with(const int* hA, const int* hB, uint32_
             else shape = 3;
             set_cur(L, 0, x, 0);
             set_cur(L, 1, y, 0);
-            {   // one call site: lanes whose leading tail is on different sides walk them together
+            if (MERGE) {   // one call site: lanes whose leading tail is on different sides walk them together
                 const bool first = shape < 2;
                 L.ref = first ? xs1 : xs2;
                 tf(first ? 0 : 1, first ? x : y, first ? xs2 : xs1, L);
-            }
+            } else if (shape < 2) { L.ref = xs1; tf(0, x, xs2, L); }
+            else { L.ref = xs2; tf(1, y, xs1, L); }
             break;
         }
         case M_SPOST: {
-            const bool onB = shape == 0 || shape == 2;
-            const int eA = hA[5 + 2 * x], eB = hB[(5 + 2 * y) * 32];
-            tf(onB ? 1 : 0, onB ? y : x, (onB ? eB : eA) + 1, L);
+            if (MERGE) {
+                const bool onB = shape == 0 || shape == 2;
+                const int eA = hA[5 + 2 * x], eB = hB[(5 + 2 * y) * 32];
+                tf(onB ? 1 : 0, onB ? y : x, (onB ? eB : eA) + 1, L);
+            } else if (shape == 0 || shape == 2) tf(1, y, hB[(5 + 2 * y) * 32] + 1, L);
+            else tf(0, x, hA[5 + 2 * x] + 1, L);
             break;
         }
         default: break;
@@ -591,7 +595,7 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
                 TailO1 tail_o1{a, hA, hB, i, j};
                 auto cheap = [&](const Args&, const int*, const int*, int, int, uint32_t mo_, Lane& L_, int& shape_) {
                     if (MAP) cheap_with(hA, hB, mo_, L_, shape_, tail_walk);
-                    else cheap_with(hA, hB, mo_, L_, shape_, tail_o1);
+                    else cheap_with<false>(hA, hB, mo_, L_, shape_, tail_o1);
                 };
                 if (__all_sync(FULL, pid == TP_SINGLE00 || pid == TP_NOP)) {
                     // the common case, checkGapsSingle on segments 1/1 for every lane: straight-line code
