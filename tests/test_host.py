@@ -34,7 +34,7 @@ def test_struct_sizes_match_header():
 def _python_pack(b: ReadBatch, qual_chars: bytes):
     code = {c: k for k, c in enumerate(qual_chars)}
     opc = {ord("M"): 0, ord("I"): 1, ord("D"): 2, ord("S"): 3, ord("H"): 4}
-    bc = {ord("A"): 0, ord("C"): 1, ord("G"): 2, ord("T"): 3}
+    bc = {ord(ch): v for v, pair in enumerate(("Aa", "Cc", "Gg", "Tt")) for ch in pair}   # toupper, else 'N' (src/ShortDnaSequence.cpp:38-49)
     out = []
     for r in range(b.n):
         for s in range(1 if b.single_end[r] else 2):
@@ -74,6 +74,42 @@ def test_pack_matches_python_restatement(fixture):
         core = cig[lead:len(cig) - trail]
         assert ((h["seg_flags"][r, 0] >> 1) & 1) == (0 if core == b"M" * len(core) else 1)
         assert h["ops_off"][r, 0] % 8 == 0 and h["ops_off"][r, 1] == h["ops_off"][r, 0] + h["n_ops"][r, 0]
+
+
+def test_pack_adversarial_cigars_match_python_restatement():
+    """The packer's look-up-table record build against the plain restatement on CIGARs the synthetic sets do not hold:
+    hard clips outside soft clips, insertions and deletions next to the clips, lower-case and ambiguous bases, every quality character 33..126."""
+    rng = np.random.default_rng(11)
+    recs = []
+    for k in range(300):
+        lead = b"H" * int(rng.integers(0, 3)) + b"S" * int(rng.integers(0, 5))
+        trail = b"S" * int(rng.integers(0, 5)) + b"H" * int(rng.integers(0, 3))
+        core = b"".join(rng.choice([b"M", b"M", b"M", b"M", b"I", b"D"]) for _ in range(int(rng.integers(0, 60))))
+        if core.count(b"M") == 0:
+            core += b"M"                                                   # a record without an M op covers nothing: not a read
+        cig = lead + core + trail
+        nq = sum(cig.count(c) for c in (b"M", b"I", b"S"))
+        seq = bytes(rng.choice(list(b"ACGTNacgtRY"), nq).tolist())
+        qual = bytes(rng.integers(33, 127, nq).astype(np.uint8).tolist())
+        ref_len = cig.count(b"M") + cig.count(b"D")
+        start = int(rng.integers(1, 500))
+        recs.append(AlignmentRecord("Clique_%d" % k if k % 3 == 0 else "read_%d" % k, True, start, start + max(ref_len, 1) - 1, cig, seq, qual))
+    b = ReadBatch.from_records(recs)
+    pk = edge.pack_only(b)
+    qc = bytes(pk.c.qual_chars[:pk.c.n_qual_codes])
+    assert qc == bytes(sorted(set(b.qual.tolist())))
+    assert (pk.ops() == _python_pack(b, qc)).all()
+    h = pk.headers()
+    assert pk.c.max_ops_per_read == int(b.cig_len.reshape(-1, 2).sum(1).max())
+    for r in range(b.n):
+        cig = recs[r].cigar1_unrolled
+        lead = len(cig) - len(cig.lstrip(b"SH"))
+        trail = len(cig) - len(cig.rstrip(b"SH"))
+        assert h["ext"][r, 0] == b.seg_start[2 * r] - lead and h["ext"][r, 1] == b.seg_end[2 * r] + trail
+        assert (h["seg_flags"][r, 0] & 1) == (1 if b"I" in cig else 0)
+        core = cig[lead:len(cig) - trail] if lead + trail <= len(cig) else b"?"
+        assert ((h["seg_flags"][r, 0] >> 1) & 1) == (0 if core == b"M" * len(core) else 1), (r, cig)
+        assert h["n_ops"][r, 0] == len(cig) and h["ops_off"][r, 0] % 8 == 0
 
 
 def test_pack_rejects_malformed_reads():
