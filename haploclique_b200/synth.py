@@ -265,3 +265,29 @@ def zoo(n_reads: int, genome_len: int = 400, seed: int = 1, max_seg: int = 120, 
         recs.append(rec)
     recs.sort(key=lambda x: x.start1)
     return ReadBatch.from_records(recs)
+
+
+def hard_clipped(n_reads: int, genome_len: int = 300, seed: int = 1) -> ReadBatch:
+    """Single-end reads whose CIGARs carry hard clips outside soft clips (H S core S H) and insertions / deletions right
+    behind or in front of the clip runs -- legal BAM that the other generators do not produce. The core starts and ends
+    on M. Sorted by start like readBamFile's output."""
+    from .records import AlignmentRecord
+    rng = np.random.default_rng(seed)
+    recs = []
+    for k in range(n_reads):
+        lead = b"H" * int(rng.integers(0, 3)) + b"S" * int(rng.integers(0, 6))
+        trail = b"S" * int(rng.integers(0, 6)) + b"H" * int(rng.integers(0, 3))
+        inner = [rng.choice([b"M", b"M", b"M", b"M", b"M", b"M", b"I", b"D"]) for _ in range(int(rng.integers(8, 90)))]
+        if rng.random() < 0.5:
+            inner = [b"M"] * len(inner)
+        core = b"M" + b"".join(inner) + b"M"
+        cig = lead + core + trail
+        nq = sum(cig.count(c) for c in (b"M", b"I", b"S"))
+        seq = bytes(rng.choice(list(b"ACGT" * 6 + b"N"), nq).tolist())
+        qual = bytes(rng.integers(35, 75, nq).astype(np.uint8).tolist())
+        ref_len = cig.count(b"M") + cig.count(b"D")
+        start = int(rng.integers(1, genome_len - 100))
+        name = ("Clique_%d" if rng.random() < 0.3 else "read_%d") % k
+        recs.append(AlignmentRecord(name, True, start, start + ref_len - 1, cig, seq, qual))
+    recs.sort(key=lambda r: r.start1)
+    return ReadBatch.from_records(recs)

@@ -1,5 +1,5 @@
 """Randomised parity sweep (not part of the test suite; run on a B200 when kernels change): many seeds of the adversarial
-zoo, small quasispecies sets with heavy indels/clips and super-read-shaped sets, random parameters, with and without an
+zoo, small quasispecies sets with heavy indels/clips, super-read-shaped sets and hard-clipped reads, random parameters, with and without an
 allele-frequency map, through every band kernel and both QuasispeciesEdgeCalculator walks, each against the oracle
 (tests/test_gpu_parity.py:_tiled_detail_vs_oracle, tests/test_gpu_quasi.py:_compare). Prints one JSON line."""
 import json
@@ -24,7 +24,7 @@ done = {"band_cases": 0, "band_skipped_not_eligible": 0, "quasi_cases": 0, "pair
 seed = seed0
 while time.time() - t0 < budget_s:
     rng = np.random.default_rng(seed)
-    kind = seed % 3
+    kind = seed % 4
     if kind == 0:
         lo = int(rng.integers(2, 40))
         b = synth.zoo(int(rng.integers(60, 260)), seed=seed, wide_qual=(lo, int(rng.integers(lo + 3, 95))),
@@ -35,9 +35,12 @@ while time.time() - t0 < budget_s:
                                indel_err=float(rng.choice([1e-4, 2e-3, 1e-2])), clip_frac=float(rng.uniform(0, 0.3)),
                                n_frac=float(rng.choice([0, 5e-4, 5e-2])))
         span = 2600
-    else:
+    elif kind == 2:
         b = synth.super_reads(int(rng.integers(40, 120)), seed=seed, clique_frac=float(rng.uniform(0, 1)))
         span = 9800
+    else:
+        b = synth.hard_clipped(int(rng.integers(80, 300)), genome_len=int(rng.integers(150, 500)), seed=seed)
+        span = 700
     kw = dict(noProb0=bool(rng.integers(0, 2)), edge_quasi_cutoff=float(rng.uniform(0.8, 0.995)),
               edge_quasi_cutoff_mixed=float(rng.uniform(0.8, 0.99)), edge_quasi_cutoff_single=float(rng.uniform(0.7, 0.97)),
               overlap=float(rng.uniform(0.1, 0.95)), overlap_single=float(rng.uniform(0.1, 0.8)))

@@ -191,6 +191,18 @@ def test_tiled_kernel_matches_oracle_on_golden_sets(golden, label, kernel):
     assert adj.count() == g["edges"]
 
 
+@pytest.mark.parametrize("kernel", TILED_KERNELS)
+@pytest.mark.parametrize("seed", [1, 2])
+def test_hard_clipped_reads(seed, kernel):
+    """Hard clips outside soft clips (H S core S H) and indels next to the clip runs: every band slot of every band
+    kernel against the oracle (itself checked against the reference on the same generator, test_oracle_vs_reference)."""
+    b = synth.hard_clipped(220, seed=seed)
+    for noprob0 in (False, True):
+        kw = dict(common.WEAK, noProb0=noprob0, maxPosition=b.max_position() + 64)
+        det, orc = _tiled_detail_vs_oracle(b, kw, "hardclip%d" % seed, kernel)
+        assert int((orc["status"] == 2).sum()) > 2000 and int(orc["gap"].sum()) > 100
+
+
 def test_first_generation_tile_shrinks_its_cta_to_fit():
     """Early super-read rounds: reads of a few hundred columns with ~75 quality codes. Too many codes for the
     second-generation kernel's 9-row table; the first-generation kernel's tables + tile + 24 warps' row buffers exceed a

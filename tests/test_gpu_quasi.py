@@ -99,6 +99,19 @@ def test_quasi_super_read_round(frameshift):
             assert adj.count() == int(e.sum()) and (ai == pi[e]).all() and (aj == pj[e]).all()
 
 
+@pytest.mark.parametrize("seed", [1, 2])
+def test_quasi_hard_clipped_reads(seed):
+    b = synth.hard_clipped(220, seed=seed)
+    kw = dict(overlap_single=0.2, overlap=0.2, edge_quasi_cutoff_single=0.5, edge_quasi_cutoff_mixed=0.5, edge_quasi_cutoff=0.5,
+              frameshift_merge=bool(seed % 2), maxPosition=b.max_position())
+    pi, pj = common.tri_pairs(b.n)
+    orc = pyoracle.QuasiOracle(b, **kw).pairs(pi, pj)
+    calc = edge.QuasispeciesEdgeCalculator(**kw)
+    calc.upload(b)
+    _compare(calc.score_pairs(pi, pj), orc, "quasi-hardclip%d" % seed)
+    assert int((orc["q"] > 0).sum()) > 1000
+
+
 def test_quasi_gradual_underflow_decides_edges():
     """exp(sum) in the subnormal range is not 0 for the reference (glibc rounds to the subnormal grid) and
     pow(subnormal, 1/n) is an ordinary number (1e-310 ^ (1/700) = 0.36): with low cutoffs such pairs ARE edges. The device

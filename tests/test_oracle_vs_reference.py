@@ -59,3 +59,23 @@ def test_allele_frequency_map():
     R = pyref.Reference()
     R.add_batch(q)
     _compare(R, dict(simpson_map=simpson, maxPosition=q.max_position() + 64), "simpson")
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_hard_clipped_reads(seed):
+    """Hard clips outside soft clips and indels next to the clip runs (synth.hard_clipped): the restatements against the
+    reference's NewEdgeCalculator on every pair, and against its QuasispeciesEdgeCalculator on the pairs it terminates on."""
+    z = synth.hard_clipped(150, seed=seed)
+    R = pyref.Reference()
+    R.add_batch(z)
+    for noprob0 in (False, True):
+        b, n = _compare(R, dict(common.WEAK, noProb0=noprob0, maxPosition=z.max_position() + 64), "hardclip%d" % seed)
+        assert n > 1000
+    pi, pj = common.tri_pairs(b.n)
+    kw = dict(overlap_single=0.2, overlap=0.2, edge_quasi_cutoff_single=0.5, edge_quasi_cutoff_mixed=0.5, edge_quasi_cutoff=0.5,
+              frameshift_merge=bool(seed % 2))
+    orc = pyoracle.QuasiOracle(b, maxPosition=b.max_position(), **kw).pairs(pi, pj)
+    ok = orc["status"] != 3
+    q, e = R.quasi_pairs(pi[ok], pj[ok], **kw)
+    assert (q.view(np.uint64) == orc["q"][ok].view(np.uint64)).all() and (e == orc["edge"][ok]).all()
+    assert int((q > 0).sum()) > 500
