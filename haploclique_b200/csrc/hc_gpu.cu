@@ -1,4 +1,8 @@
 // hc_gpu.cu -- sm_100a kernels and the CUDA half of the C ABI (include/hc_edge.h).
+// This file: the phase programs, the one-lane-per-pair walker (pair lists; cross-check of the band kernels), work-item
+// construction, and the host side of every entry point. The band kernels hc_score_band runs are in hc_tile2.cuh
+// (address-addend formats, the default), hc_tile.cuh (16-bit records; tiled and streamed) -- the
+// QuasispeciesEdgeCalculator kernels in hc_quasi.cuh.
 //
 // What one "pair" is: the decision NewEdgeCalculator::edgeBetween(ap1, ap2) makes
 // (reference src/NewEdgeCalculator.cpp:1247-1376) for ap1 = the later arrival, ap2 = an earlier read.
@@ -498,11 +502,11 @@ struct hc_ctx {
     double* d_logsum = nullptr; double* d_simpson_ln = nullptr; hc_quasi_result* d_qres = nullptr; size_t qres_cap = 0;
     int4* d_qseg = nullptr; size_t qseg_cap = 0; bool have_qseg = false;
     // second-generation tiled kernel (hc_tile2.cuh): row / column operand formats and the 9-row table
-    uint32_t* d_opsA = nullptr; uint16_t* d_opsF = nullptr; uint32_t* d_tab7 = nullptr;
+    uint32_t* d_opsA = nullptr; uint16_t* d_opsF = nullptr; uint32_t* d_tab9 = nullptr;
     bool have_formats = false;
     // capacities (elements) of the per-batch device buffers: they only grow, so a steady stream of hc_upload calls does
     // no cudaMalloc / cudaFree (both synchronise the device and would serialise the copies with the host-side layout work)
-    size_t cap_hdr = 0, cap_ops = 0, cap_table = 0, cap_ladder = 0, cap_aux = 0, cap_col2op = 0, cap_opsA = 0, cap_opsF = 0, cap_tab7 = 0;
+    size_t cap_hdr = 0, cap_ops = 0, cap_table = 0, cap_ladder = 0, cap_aux = 0, cap_col2op = 0, cap_opsA = 0, cap_opsF = 0, cap_tab9 = 0;
     int4* d_items = nullptr; size_t items_cap = 0; int* d_item_counter = nullptr;
     hc_pair_result* d_detail = nullptr; size_t detail_cap = 0;
     int kernel_mode = HC_KERNEL_AUTO;
@@ -881,7 +885,7 @@ void hc_destroy(hc_ctx* c) {
     cudaFree(c->d_col0); cudaFree(c->d_word_off); cudaFree(c->d_adj); cudaFree(c->d_stats); cudaFree(c->d_amb);
     cudaFree(c->d_pi); cudaFree(c->d_pj); cudaFree(c->d_res); cudaFree(c->d_flush);
     cudaFree(c->d_aux); cudaFree(c->d_col2op); cudaFree(c->d_tprog); cudaFree(c->d_items); cudaFree(c->d_item_counter);
-    cudaFree(c->d_opsA); cudaFree(c->d_opsF); cudaFree(c->d_tab7);
+    cudaFree(c->d_opsA); cudaFree(c->d_opsF); cudaFree(c->d_tab9);
     cudaFree(c->d_logsum); cudaFree(c->d_simpson_ln); cudaFree(c->d_qres); cudaFree(c->d_qseg);
     cudaFree(c->d_detail); cudaFree(c->d_colidx);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -969,9 +973,9 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     // operand formats of the second-generation tiled kernel (hc_tile2.cuh): A-words, B-records, and the table as
     // 9 rows per first quality (un x4, EQ, un x4), low words then high words. Skipped when the table alone
     // would not fit a CTA's shared memory (the kernel is then not eligible).
-    std::vector<uint32_t> tab7;
+    std::vector<uint32_t> tab9;
     if (tile2_table_words(K) * 4 + 65536 <= c->smem_optin) {
-        tab7.assign(tile2_table_words(K), 0u);
+        tab9.assign(tile2_table_words(K), 0u);
         // order of the quality codes inside a table row (HC_T2_PERM, experiments on bank conflicts): 0 identity,
         // 1 even codes first, 2 reversed, 3 stride 5
         tile2::ColumnOrder ord{};
@@ -993,17 +997,17 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
                     std::memcpy(&bits, &v, 8);
                     const size_t row = (size_t)a * tile2::kRows + r;
                     if (split) {                       // 32 low words, then 32 high words
-                        tab7[row * 64 + ord.slot[b]] = (uint32_t)bits;
-                        tab7[row * 64 + 32 + ord.slot[b]] = (uint32_t)(bits >> 32);
+                        tab9[row * 64 + ord.slot[b]] = (uint32_t)bits;
+                        tab9[row * 64 + 32 + ord.slot[b]] = (uint32_t)(bits >> 32);
                     } else {                           // K doubles
                         const size_t Kp = tile2_row_bytes(K) / 8;
-                        tab7[(row * Kp + ord.slot[b]) * 2] = (uint32_t)bits;
-                        tab7[(row * Kp + ord.slot[b]) * 2 + 1] = (uint32_t)(bits >> 32);
+                        tab9[(row * Kp + ord.slot[b]) * 2] = (uint32_t)bits;
+                        tab9[(row * Kp + ord.slot[b]) * 2 + 1] = (uint32_t)(bits >> 32);
                     }
                 }
         const long long nrec = (long long)p->n_ops_total + 64;
-        if ((rc = grow(c, c->d_tab7, c->cap_tab7, tab7.size())) != HC_OK) return rc;
-        CU_TRY(c, cudaMemcpyAsync(c->d_tab7, tab7.data(), tab7.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+        if ((rc = grow(c, c->d_tab9, c->cap_tab9, tab9.size())) != HC_OK) return rc;
+        CU_TRY(c, cudaMemcpyAsync(c->d_tab9, tab9.data(), tab9.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
         if ((rc = grow(c, c->d_opsA, c->cap_opsA, (size_t)nrec)) != HC_OK) return rc;
         if ((rc = grow(c, c->d_opsF, c->cap_opsF, (size_t)nrec)) != HC_OK) return rc;
         c->have_formats = true;
@@ -1118,7 +1122,7 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
         if (detail) CU_TRY(c, cudaMemsetAsync(c->d_detail, 0, (size_t)total * 32 * sizeof(hc_pair_result), c->stream));
         tile2::Args2 a{};
         a.P = dev_params(c);
-        a.opsA = c->d_opsA; a.opsF = c->d_opsF; a.tab7 = c->d_tab7; a.tab_words = (int)tile2_table_words(c->K);
+        a.opsA = c->d_opsA; a.opsF = c->d_opsF; a.tab9 = c->d_tab9; a.tab_words = (int)tile2_table_words(c->K);
         a.row_bytes = tile2_row_bytes(c->K); a.entry_bytes = tile2_entry_bytes(c->K);
         a.hdr = c->d_hdr; a.ops = c->d_ops; a.aux = c->d_aux; a.col2op = c->d_col2op; a.prog = c->d_tprog;
         a.n_reads = c->n_reads; a.row_begin = row_begin; a.col0 = c->d_col0; a.word_off = c->d_word_off;

@@ -36,7 +36,7 @@ constexpr int kSplitMaxK = 0;    // split-word layout off by default: measured 6
 struct Args2 : tile::Args {
     const uint32_t* opsA;       // row format, one 32-bit word per op (same indexing as ops)
     const uint16_t* opsF;       // column format, one 16-bit record per op (same indexing as ops), table base not yet added
-    const uint32_t* tab7;       // the 9-row table image as it sits in shared memory (32-bit words)
+    const uint32_t* tab9;       // the 9-row table image as it sits in shared memory (32-bit words)
     int tab_words;              // its size in 32-bit words
     uint32_t row_bytes;         // ROW: 256 (split) or 8*K (pair)
     uint32_t entry_bytes;       // ESZ: 4 (split) or 8 (pair)
@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) score_tile2_kernel(const Ar
     unsigned long long* cstat = reinterpret_cast<unsigned long long*>(smem + o); o += 8 * 8;
     int* ctl = reinterpret_cast<int*>(smem + o);
 
-    for (int k = tid; k < a.tab_words; k += nthreads) Tsm[k] = a.tab7[k];
+    for (int k = tid; k < a.tab_words; k += nthreads) Tsm[k] = a.tab9[k];
     for (int k = tid; k < TP_COUNT * TP_WORDS; k += nthreads) progsm[k] = a.prog[k];
     if (tid < 8) cstat[tid] = 0ull;
     unsigned a_total = 0, a_scored = 0, a_walked = 0, a_edges = 0, a_undef = 0;
