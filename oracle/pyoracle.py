@@ -47,7 +47,7 @@ QUASI_RESULT_DTYPE = np.dtype([("status", np.int32), ("edge", np.int32), ("n_sin
 
 def build(force: bool = False) -> str:
     """Compiles the C restatement (gcc). Building the checker is not using it."""
-    srcs = [os.path.join(_HERE, f) for f in ("edge_oracle.c", "quasi_oracle.c", "orc_types.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("edge_oracle.c", "quasi_oracle.c", "merge_oracle.c", "orc_types.h")]
     if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-s", "-C", _HERE, "oracle"])
     return _LIB
@@ -160,3 +160,26 @@ def tri_pairs(n: int):
     """(i, j) index arrays of all ordered pairs i>j in the row-major order all_pairs uses."""
     i, j = np.tril_indices(n, -1)
     return i.astype(np.int32), j.astype(np.int32)
+
+
+# ---- single-end super-read merge (SURVEY.md 8(f) N2; oracle/merge_oracle.c) -----------------------------------
+def compute_entry(b1: int, q1: int, b2: int, q2: int):
+    """computeEntry (src/AlignmentRecord.cpp:169-184): (base char, quality char) of one merged column."""
+    out = (C.c_uint8 * 2)()
+    lib().orc_compute_entry(C.c_uint8(b1), C.c_uint8(q1), C.c_uint8(b2), C.c_uint8(q2), out)
+    return out[0], out[1]
+
+
+def merge_clique_se(batch, members):
+    """AlignmentRecord(alignments, id) for single-end members (read indices into `batch`, fold order).
+    Returns (status, start1, end1, cigar_unrolled bytes, sequence bytes, quality bytes)."""
+    mem = np.ascontiguousarray(members, np.int32)
+    cap = int(batch.cig_len[2 * mem].sum()) + 1
+    oc, os_, oq = (np.zeros(cap, np.uint8) for _ in range(3))
+    info = np.zeros(5, np.int32)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    lib().orc_merge_clique_se(p(batch.seg_start), p(batch.seg_end), p(batch.cig_off), p(batch.cig_len), p(batch.seq_off),
+                              p(batch.seq_len), p(batch.cig), p(batch.seq), p(batch.qual), p(mem), C.c_int32(mem.size),
+                              p(oc), p(os_), p(oq), p(info))
+    st, s, e, no, ns = (int(x) for x in info)
+    return st, s, e, oc[:no].tobytes(), os_[:ns].tobytes(), oq[:ns].tobytes()

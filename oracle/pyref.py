@@ -180,6 +180,24 @@ class Reference:
     def edge(self, i: int, j: int) -> bool:
         return bool(self.L.hcref_edge(self.h, i, j))
 
+    # -- super-read construction ------------------------------------------------
+    def compute_entry(self, b1: int, q1: int, b2: int, q2: int):
+        out = C.create_string_buffer(2)
+        self.L.hcref_compute_entry(C.c_char(bytes([b1])), C.c_char(bytes([q1])), C.c_char(bytes([b2])), C.c_char(bytes([q2])), out)
+        return out.raw[0], out.raw[1]
+
+    def merge_clique(self, members, clique_id: int = 0):
+        """AlignmentRecord(alignments, clique_id) over records[members]; returns (single_end, start1, end1, cigar, seq, qual)."""
+        mem = np.ascontiguousarray(members, np.int32)
+        i = self.L.hcref_merge_clique(self.h, _p(mem), C.c_int(mem.size), C.c_uint(clique_id))
+        info = (C.c_int * 12)()
+        name = C.create_string_buffer(512)
+        self.L.hcref_record_info(self.h, i, info, name, 512)
+        se, s1, e1, _, _, nc1, nq1 = list(info)[:7]
+        bufs = [C.create_string_buffer(max(k, 1)) for k in (nc1, nq1, nq1, 1, 1, 1)]
+        self.L.hcref_record_data(self.h, i, *bufs)
+        return bool(se), s1, e1, bufs[0].raw[:nc1], bufs[1].raw[:nq1], bufs[2].raw[:nq1]
+
     def score_all(self):
         n = self.n
         npairs = n * (n - 1) // 2

@@ -34,6 +34,8 @@
 #include <cstring>
 #include <thread>
 
+std::pair<char, char> computeEntry(const char& base1, const char& qual1, const char& base2, const char& qual2);   // src/AlignmentRecord.cpp:169
+
 namespace {
 
 struct RefCtx {
@@ -207,6 +209,23 @@ int hcref_restore_fixture(void* p, const char* path) {
     r->restoreCompleteAlignmentRecord(path);
     c->recs.push_back(r);
     return (int)c->recs.size() - 1;
+}
+
+// Super-read construction: AlignmentRecord(alignments, clique_id) (src/AlignmentRecord.cpp:211-249) over
+// records[members[0..m)], appended to the record list like hcref_restore_fixture does. Returns the new record's index.
+int hcref_merge_clique(void* p, const int* members, int m, unsigned clique_id) {
+    RefCtx* c = static_cast<RefCtx*>(p);
+    std::unique_ptr<std::vector<const AlignmentRecord*>> al(new std::vector<const AlignmentRecord*>());
+    for (int k = 0; k < m; ++k) al->push_back(c->recs[members[k]]);
+    c->recs.push_back(new AlignmentRecord(al, clique_id));
+    return (int)c->recs.size() - 1;
+}
+
+// computeEntry (src/AlignmentRecord.cpp:169-184): consensus base and updated quality char of one merged column.
+void hcref_compute_entry(char b1, char q1, char b2, char q2, char* out2) {
+    std::pair<char, char> r = computeEntry(b1, q1, b2, q2);
+    out2[0] = r.first;
+    out2[1] = r.second;
 }
 
 int hcref_n(void* p) { return (int)static_cast<RefCtx*>(p)->recs.size(); }
