@@ -96,6 +96,8 @@ def load_library():
         L.hc_get_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.hc_quasi_score_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
         L.hc_quasi_score_band.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]
+        L.hc_merge_layout.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.hc_merge_cliques_se.argtypes = [C.c_int32, C.c_void_p, C.c_int32] + [C.c_void_p] * 8
         assert C.sizeof(_BandStats) == 72 and HDR_DTYPE.itemsize == 64
         _lib = L
     return _lib
@@ -471,3 +473,56 @@ def measure_peaks(device: int = 0):
 
 def device_count() -> int:
     return int(load_library().hc_device_count())
+
+
+# ---- super-read construction, single-end cliques (include/hc_edge.h hc_merge_*) --------------
+MERGED_INFO_DTYPE = np.dtype([("status", np.int32), ("start", np.int32), ("end", np.int32), ("n_ops", np.int32),
+                              ("n_seq", np.int32)])
+HC_MERGE_OK, HC_MERGE_UNDEFINED, HC_MERGE_OVERRUN = 0, 1, 2
+
+
+class MergedCliques:
+    """Result of merge_cliques_se: per clique the super-read's start1/end1, unrolled CIGAR, bases and quality chars."""
+
+    def __init__(self, info, out_off, cig, seq, qual, kernel_ms):
+        self.info, self.out_off, self.cig, self.seq, self.qual, self.kernel_ms = info, out_off, cig, seq, qual, kernel_ms
+
+    def __len__(self):
+        return self.info.shape[0]
+
+    def record(self, c: int, clique_id: Optional[int] = None) -> Optional[AlignmentRecord]:
+        """The super-read as an AlignmentRecord named like the reference names it (src/AlignmentRecord.cpp:246);
+        None where the reference's merge is undefined (info['status'] != 0)."""
+        r = self.info[c]
+        if r["status"] != HC_MERGE_OK:
+            return None
+        o = int(self.out_off[c])
+        return AlignmentRecord("Clique_%d" % (c if clique_id is None else clique_id), True, int(r["start"]), int(r["end"]),
+                               self.cig[o:o + r["n_ops"]].tobytes(), self.seq[o:o + r["n_seq"]].tobytes(),
+                               self.qual[o:o + r["n_seq"]].tobytes())
+
+
+def merge_cliques_se(reads: ReadBatch, cliques: Sequence[Sequence[int]], device: int = 0) -> MergedCliques:
+    """AlignmentRecord(alignments, clique_id) (src/AlignmentRecord.cpp:211-249) for a batch of single-end cliques, on the
+    GPU: `cliques[c]` lists read indices into `reads` in the order of the reference's `alignments` vector."""
+    L = load_library()
+    member_off = np.zeros(len(cliques) + 1, np.int64)
+    member_off[1:] = np.cumsum([len(c) for c in cliques])
+    members = np.ascontiguousarray(np.concatenate([np.asarray(c, np.int32) for c in cliques]) if len(cliques) else np.zeros(0, np.int32))
+    keep = [np.ascontiguousarray(getattr(reads, k)) for k in (
+        "single_end", "is_clique", "ncov", "cov_first", "cov_last", "seg_start", "seg_end", "cig_off", "cig_len",
+        "seq_off", "seq_len", "cig", "seq", "qual")]
+    rd = _Reads(reads.n, *[_ptr(a) for a in keep])
+    out_off = np.zeros(len(cliques) + 1, np.int64)
+    rc = L.hc_merge_layout(C.byref(rd), C.c_int32(len(cliques)), _ptr(member_off), _ptr(members), _ptr(out_off))
+    if rc != HC_OK:
+        raise HcError("hc_merge_layout failed (%d): %s" % (rc, L.hc_last_error(None).decode()))
+    total = max(int(out_off[-1]), 1)
+    cig, seq, qual = (np.zeros(total, np.uint8) for _ in range(3))
+    info = np.zeros(len(cliques), MERGED_INFO_DTYPE)
+    ms = C.c_float(0.0)
+    rc = L.hc_merge_cliques_se(C.c_int32(device), C.byref(rd), C.c_int32(len(cliques)), _ptr(member_off), _ptr(members),
+                               _ptr(out_off), _ptr(cig), _ptr(seq), _ptr(qual), _ptr(info), C.byref(ms))
+    if rc != HC_OK:
+        raise HcError("hc_merge_cliques_se failed (%d): %s" % (rc, L.hc_last_error(None).decode()))
+    return MergedCliques(info, out_off, cig, seq, qual, float(ms.value))

@@ -264,6 +264,39 @@ int hc_measure_peaks(int32_t device, double* lds_gbs, double* dmul_per_s);
 /* The two 127x127 match-probability tables the context uploaded (row-major [q1][q2], doubles). */
 int hc_get_tables(const hc_ctx* ctx, double* eq127x127, double* uneq127x127);
 
+/* ---- Super-read construction, single-end cliques (first slice) --------------------------------
+ * Replaces AlignmentRecord::AlignmentRecord(unique_ptr<vector<const AlignmentRecord*>>& alignments, unsigned clique_id)
+ * (src/AlignmentRecord.cpp:211-249; call site Clique -> super-read in src/CliqueCollector.h) for cliques whose members
+ * are all single-end: the fold of mergeAlignmentRecordsSingle(ar,1,1) (:581-734) over the members in the given order.
+ * The caller keeps name ("Clique_<id>"), readNames and cov_pos, which are set unions / derived fields (:243-248).
+ * Paired-end members are refused with HC_E_INVALID (mergeAlignmentRecordsPaired / Mixed are not built yet).
+ * There is no CPU merging path: without a CUDA device the call fails with HC_E_CUDA. */
+#define HC_MERGE_OK 0
+#define HC_MERGE_UNDEFINED 1            /* an op pair overlapMerge does not list (:1671 assert(false): the Release build of
+                                           the reference never leaves that loop) */
+#define HC_MERGE_OVERRUN 2              /* a cursor ran past its CIGAR (start/end disagree with the CIGAR: the reference
+                                           reads past the vector there) */
+typedef struct {
+    int32_t status;                     /* HC_MERGE_* */
+    int32_t start;                      /* start1 of the super-read (:686) */
+    int32_t end;                        /* end1 (:687) */
+    int32_t n_ops;                      /* length of cigar1_unrolled: M / I / D only, clips are dropped by the merge */
+    int32_t n_seq;                      /* length of sequence1 and of its quality string */
+} hc_merged_info;
+
+/* Clique c holds reads members[member_off[c] .. member_off[c+1]) in fold order (the order of the reference's
+ * `alignments` vector). Fills out_off[n_cliques+1]: clique c's result occupies [out_off[c], out_off[c+1]) of each of the
+ * three output streams (an upper bound: the members' CIGAR lengths summed, rounded up to 16). */
+int hc_merge_layout(const hc_reads* reads, int32_t n_cliques, const int64_t* member_off, const int32_t* members,
+                    int64_t* out_off);
+
+/* Merges every clique on `device`. out_cig / out_seq / out_qual: host buffers of out_off[n_cliques] bytes each; the
+ * first info[c].n_ops / n_seq bytes at out_off[c] are the super-read's unrolled CIGAR, bases and quality chars.
+ * kernel_ms (optional): device time of the merge kernel alone. */
+int hc_merge_cliques_se(int32_t device, const hc_reads* reads, int32_t n_cliques, const int64_t* member_off,
+                        const int32_t* members, const int64_t* out_off, uint8_t* out_cig, uint8_t* out_seq,
+                        uint8_t* out_qual, hc_merged_info* info, float* kernel_ms);
+
 #ifdef __cplusplus
 }
 #endif

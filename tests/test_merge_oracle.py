@@ -1,0 +1,89 @@
+"""CPU: oracle/merge_oracle.c (single-end super-read merge) against the reference's golden digests
+(tests/golden/merge_golden.json, made by tests/golden/make_merge_golden.py from the compiled reference) and, where
+oracle/_ref/libhcref.so is present, against the reference directly."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle, pyref
+from tests import merge_cases
+from tests.common import GOLDEN
+
+
+def _golden():
+    with open(os.path.join(GOLDEN, "merge_golden.json")) as fh:
+        return json.load(fh)
+
+
+def _digest(rows):
+    h = hashlib.sha256()
+    for start, end, cig, seq, qual in rows:
+        h.update(np.array([start, end, len(cig), len(seq)], "<i4").tobytes())
+        h.update(cig); h.update(seq); h.update(qual)
+    return h.hexdigest()
+
+
+def test_compute_entry_table_matches_reference_digest():
+    tab = bytearray()
+    for q1 in range(33, 127):
+        for q2 in range(33, 127):
+            for b2 in (65, 67):
+                tab += bytes(pyoracle.compute_entry(65, q1, b2, q2))
+    assert hashlib.sha256(bytes(tab)).hexdigest() == _golden()["compute_entry_sha256"]
+
+
+def test_compute_entry_known_values():
+    # equal bases raise the quality, unequal bases keep the better base and lower it; 126 is the cap (:173-180)
+    assert pyoracle.compute_entry(ord("A"), 33 + 30, ord("A"), 33 + 30) == (ord("A"), 33 + 65)
+    assert pyoracle.compute_entry(ord("A"), 33 + 30, ord("C"), 33 + 10)[0] == ord("A")
+    assert pyoracle.compute_entry(ord("A"), 33 + 10, ord("C"), 33 + 30)[0] == ord("C")
+    assert pyoracle.compute_entry(ord("G"), 126, ord("G"), 126) == (ord("G"), 126)
+
+
+@pytest.mark.parametrize("case", ["hiv50", "hiv50_large_cliques", "clipped"])
+def test_merge_oracle_matches_reference_digest(case):
+    g = _golden()[case]
+    name, batch, seed, n_cl, span, mm = next(c for c in merge_cases.CASES() if c[0] == case)
+    rows, undefined = [], []
+    for t, mem in enumerate(merge_cases.windows(batch.n, n_cl, seed, span, mm)):
+        st, s, e, cig, seq, qual = pyoracle.merge_clique_se(batch, mem)
+        if st:
+            undefined.append(t)
+        else:
+            rows.append((s, e, cig, seq, qual))
+    assert undefined == g["undefined"]
+    assert _digest(rows) == g["sha256"]
+
+
+@pytest.mark.skipif(not pyref.available(), reason="oracle/_ref/libhcref.so not built (needs /root/reference)")
+def test_merge_oracle_matches_reference_directly():
+    batch = merge_cases.clipped_batch(seed=9, n=250)
+    R = pyref.Reference()
+    R.add_batch(batch)
+    n = 0
+    for t, mem in enumerate(merge_cases.windows(batch.n, 600, 3, 8, 6)):
+        o = pyoracle.merge_clique_se(batch, mem)
+        if o[0]:
+            continue
+        r = R.merge_clique(mem, t)
+        assert r[0] and r[1:] == o[1:], "clique %d %s" % (t, mem)
+        n += 1
+    assert n > 400
+
+
+def test_merge_refuses_paired_members_and_has_no_cpu_path():
+    """Host-side argument checks of hc_merge_* need no GPU; the merge itself fails with HC_E_CUDA without one."""
+    import torch
+    from haploclique_b200 import edge
+    from tests.common import load_batch
+    b = load_batch("arabis_records.npz")
+    paired = int(np.flatnonzero(b.single_end == 0)[0])
+    with pytest.raises(edge.HcError, match="paired-end"):
+        edge.merge_cliques_se(b, [[paired, paired + 1]])
+    if not torch.cuda.is_available():
+        h = load_batch("hiv50_records.npz")
+        with pytest.raises(edge.HcError, match="no CPU merging path"):
+            edge.merge_cliques_se(h, [[0, 1]])
