@@ -92,9 +92,14 @@ __device__ __forceinline__ int shared_column(const Seg& a, const Seg& b, Out& o,
         const uint8_t b1 = a.seq[q1], b2 = b.seq[q2];
         const int k1 = a.qual[q1] - 33, k2 = b.qual[q2] - 33;
         uint8_t base, qual;
-        if (b1 == b2) { base = b1; qual = tab[k1 * NQ + k2]; }
-        else if (k1 >= k2) { base = b1; qual = tab[NQ * NQ + k1 * NQ + k2]; }
-        else { base = b2; qual = tab[NQ * NQ + k2 * NQ + k1]; }
+        const int i1 = max(k1, 0), i2 = max(k2, 0);
+        if (b1 == b2) { base = b1; qual = tab[i1 * NQ + i2]; }
+        else if (k1 >= k2) { base = b1; qual = tab[NQ * NQ + i1 * NQ + i2]; }
+        else { base = b2; qual = tab[NQ * NQ + i2 * NQ + i1]; }
+        // computeEntry itself can hand back a char below '!': agreement of Q0 with Q62, 64, 68, 70, 73 rounds to -1..-4
+        // (29..32). When such a column is merged again the reference indexes table rows 0..32, which its builders never
+        // fill (:68-86 start at 33); they sit in zero-initialised static storage, so the update reads 0 -> '!'.
+        if ((k1 | k2) < 0) qual = 33;
         emit(o, x, base, qual);
         ref += (x == 'M');
         ++q1; ++q2; ++c1; ++c2;

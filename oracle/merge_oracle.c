@@ -39,6 +39,9 @@ static int disagreement(int q1, int q2) {
     return (int)post;
 }
 
+/* Rows / columns 0..32 are never filled by the reference's builders (:68-86 start at 33) and sit in zero-initialised static
+ * storage there as here. They ARE reached: agreement(Q62|64|68|70|73, Q0) rounds to -1..-4, so computeEntry can emit the
+ * chars 29..32, and a later fold indexes the table with them, reading 0 -> '!'. */
 static int tab_ready;
 static int tab_agree[127][127], tab_dis[127][127];
 static void tables(void) {

@@ -41,6 +41,9 @@ def test_compute_entry_known_values():
     assert pyoracle.compute_entry(ord("A"), 33 + 30, ord("C"), 33 + 10)[0] == ord("A")
     assert pyoracle.compute_entry(ord("A"), 33 + 10, ord("C"), 33 + 30)[0] == ord("C")
     assert pyoracle.compute_entry(ord("G"), 126, ord("G"), 126) == (ord("G"), 126)
+    # float rounding pushes agreement(Q70, Q0) to -4: a char below '!' (29), which later folds index the tables with
+    assert pyoracle.compute_entry(ord("T"), 33 + 70, ord("T"), 33) == (ord("T"), 29)
+    assert pyoracle.compute_entry(ord("T"), 29, ord("T"), 33 + 40) == (ord("T"), 33)
 
 
 @pytest.mark.parametrize("case", ["hiv50", "hiv50_large_cliques", "clipped"])
