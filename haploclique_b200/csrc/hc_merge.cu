@@ -14,6 +14,7 @@
 
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -315,7 +316,12 @@ int hc_merge_cliques_se(int32_t device, const hc_reads* reads, int32_t n_cliques
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     MG_TRY(cudaEventCreate(&e0));
     MG_TRY(cudaEventCreate(&e1));
-    const int blocks = std::max(1, std::min((n_cliques + 127) / 128, 148 * 8));
+    // Resident CTAs per SM bound the number of cliques in flight, hence the ping-pong working set that has to live in L2
+    // (HC_MERGE_BLOCKS_PER_SM overrides, 1..16; measurements in DESIGN.md 4.5).
+    int sm_count = 148, per_sm = 8;
+    MG_TRY(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
+    if (const char* e = std::getenv("HC_MERGE_BLOCKS_PER_SM")) per_sm = std::max(1, std::min(16, std::atoi(e)));
+    const int blocks = std::max(1, std::min((n_cliques + 127) / 128, sm_count * per_sm));
     MG_TRY(cudaEventRecord(e0, stream));
     merge_cliques_kernel<<<blocks, 128, 0, stream>>>(B);
     MG_TRY(cudaGetLastError());
