@@ -48,6 +48,12 @@ def main():
             rows.append((s, e, cig, seq, qual))
         out[name] = {"n_cliques": n_cl, "undefined": undefined, "sha256": digest(rows)}
         print(name, n_cl, "undefined", len(undefined))
+    # The reference's own known-answer test for this path: test/unit/unit3.cpp:33-60 (mergeAlignmentRecordsMatch) merges
+    # fixtures sample00 + sample10 and expects sample11 -- all three single-end. Their fields travel as a small npz.
+    R = pyref.Reference()
+    for k in (0, 10, 11):
+        R.restore_fixture(os.path.join(pyref.REFERENCE_ROOT, "test/data/simulation/unit_data/alignment_sample%02d.txt" % k))
+    R.to_batch().save(os.path.join(ROOT, "tests", "golden", "unit3_merge_fixtures.npz"))
     with open(os.path.join(ROOT, "tests", "golden", "merge_golden.json"), "w") as fh:
         json.dump(out, fh, indent=1)
 

@@ -48,6 +48,14 @@ def test_merge_matches_oracle_and_reference_digest(case):
     assert _digest(rows) == g["sha256"]
 
 
+def test_merge_reproduces_the_references_unit3_vector():
+    """test/unit/unit3.cpp:33-60: sample00 merged with sample10 equals sample11."""
+    from tests.test_merge_oracle import unit3_expected
+    b, members, exp = unit3_expected()
+    rec = edge.merge_cliques_se(b, [members]).record(0)
+    assert (rec.start1, rec.end1, rec.cigar1_unrolled, rec.sequence1, rec.qualities1) == exp
+
+
 def test_merge_fold_order_and_single_member():
     from tests.common import load_batch
     b = load_batch("hiv50_records.npz")

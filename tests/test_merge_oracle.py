@@ -46,6 +46,24 @@ def test_compute_entry_known_values():
     assert pyoracle.compute_entry(ord("T"), 29, ord("T"), 33 + 40) == (ord("T"), 33)
 
 
+def unit3_expected():
+    """(batch, members, expected fields): the reference's own test vector test/unit/unit3.cpp:33-60 -- sample00 merged with
+    sample10 must equal sample11 (rows 0, 1, 2 of tests/golden/unit3_merge_fixtures.npz)."""
+    from tests.common import load_batch
+    b = load_batch("unit3_merge_fixtures.npz")
+    k = 4
+    exp = (int(b.seg_start[k]), int(b.seg_end[k]), b.cig[b.cig_off[k]:b.cig_off[k] + b.cig_len[k]].tobytes(),
+           b.seq[b.seq_off[k]:b.seq_off[k] + b.seq_len[k]].tobytes(), b.qual[b.seq_off[k]:b.seq_off[k] + b.seq_len[k]].tobytes())
+    return b, [0, 1], exp
+
+
+def test_merge_oracle_reproduces_the_references_unit3_vector():
+    b, members, exp = unit3_expected()
+    assert b.single_end.all() and b.names[2].startswith("Clique")
+    st, *got = pyoracle.merge_clique_se(b, members)
+    assert st == 0 and tuple(got) == exp
+
+
 @pytest.mark.parametrize("case", ["hiv50", "hiv50_large_cliques", "clipped"])
 def test_merge_oracle_matches_reference_digest(case):
     g = _golden()[case]
