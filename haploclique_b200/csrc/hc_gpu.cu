@@ -445,7 +445,7 @@ __global__ void __launch_bounds__(256) score_band_kernel(DevParams P, const hc_r
                 if (amb != nullptr && slot < (unsigned long long)amb_cap) {
                     hc_ambiguous a;
                     a.i = i; a.j = j; a.cc = o.cc; a.tc = o.tc; a.probM = o.probM; a.prob0 = o.prob0;
-                    a.score = o.score; a.cutoff = o.cutoff;
+                    a.score = o.score; a.cutoff = o.cutoff; a.edge = o.edge; a.edge_device = o.edge;
                     amb[slot] = a;
                 }
             }
@@ -487,12 +487,14 @@ struct hc_ctx {
     int ladder_len = 0;
     std::vector<int32_t> cov_first, cov_last_pmax;   // host copies for the band layout
     // band scratch (grown on demand)
-    int32_t* d_col0 = nullptr; long long* d_word_off = nullptr; size_t rows_cap = 0;
+    int32_t* d_col0 = nullptr; long long* d_word_off = nullptr; size_t col0_cap = 0, word_off_cap = 0;
     uint32_t* d_adj = nullptr; size_t adj_cap = 0;
     BandStatsDev* d_stats = nullptr;
-    hc_ambiguous* d_amb = nullptr; int amb_cap = 0;
+    hc_ambiguous* d_amb = nullptr; size_t amb_cap = 0;
     // pair-list scratch
-    int32_t* d_pi = nullptr; int32_t* d_pj = nullptr; hc_pair_result* d_res = nullptr; size_t pairs_cap = 0;
+    // every buffer has its own capacity: hc_score_pairs and hc_quasi_score_pairs share d_pi / d_pj but not the results
+    int32_t* d_pi = nullptr; int32_t* d_pj = nullptr; hc_pair_result* d_res = nullptr;
+    size_t pi_cap = 0, pj_cap = 0, res_cap = 0;
     std::vector<int32_t> lay_col0; std::vector<long long> lay_off; int lay_begin = -1, lay_end = -1;
     void* d_flush = nullptr; size_t flush_bytes = 0;
     // tiled band kernel (hc_tile.cuh)
@@ -512,7 +514,14 @@ struct hc_ctx {
     int kernel_mode = HC_KERNEL_AUTO;
     int last_kernel = 0;
     size_t smem_optin = 0;
-    std::vector<int4> items; std::vector<int32_t> colidx; int items_begin = -1, items_end = -1;
+    // scoring plan of the last range: row windows with their work items (build_plan)
+    struct Win { int r0, r1; size_t item0, n_items; long long word0, n_words; };
+    std::vector<int4> items; std::vector<int32_t> colidx; std::vector<Win> wins;
+    int plan_begin = -1, plan_end = -1, plan_ctas = 0; bool plan_windows = false;
+    cudaStream_t copy_stream = nullptr;                     // D2H of finished row windows, beside the compute stream
+    cudaEvent_t win_ev[16] = {nullptr};                     // kernel of window k done
+    std::vector<uint32_t> ncov_flags;                       // host copy of the headers' flags word (host re-decision)
+    std::vector<hc_ambiguous> amb_host;                     // near-threshold pairs of the last pass, re-decided
     int32_t* d_colidx = nullptr; size_t colidx_cap = 0;
     std::vector<int32_t> cov_last, cov_first_smin; std::vector<uint8_t> is_single;
     std::string err;
@@ -738,75 +747,123 @@ int item_window_div() {
     return v;
 }
 
-// Work items of the tiled kernel for rows [row_begin,row_end).
+// Work items of the tiled kernels for rows [w0,w1) of the laid-out range (c->lay_begin .. c->lay_end).
 // Columns (the earlier reads j) are taken in windows of W consecutive reads; inside a window they are sorted by
 // (single/paired, last covered position) and cut into blocks of 32. For a later row read i the length of the
 // lock-step loop against j depends on min(end_i, end_j) but not on j's start (j starts first), so the 32 lanes of
 // a block run loops of nearly the same length; and a block stops being scheduled at the first row that starts
 // behind the block's furthest end, so lanes are not spent on the reference's first reject (:1252).
-// An item = (block, chunk of rows that can reach it).
-void build_items(hc_ctx* c, int row_begin, int row_end, int n_ctas) {
-    if (c->items_begin == row_begin && c->items_end == row_end) return;
+// An item = (block, chunk of rows that can reach it). Items and blocks are appended to `items` / `colidx`.
+void build_items_range(hc_ctx* c, int w0, int w1, int n_ctas, std::vector<int4>& items, std::vector<int32_t>& colidx) {
+    const int nrows = w1 - w0;
+    if (nrows <= 0 || w1 < 2) return;
+    const int32_t* col0 = c->lay_col0.data() + (w0 - c->lay_begin);
+    int32_t jlo = INT32_MAX;
+    long long band = 0;
+    for (int k = 0; k < nrows; ++k) { jlo = std::min(jlo, col0[k]); band += (w0 + k) - col0[k]; }
+    const int jhi = w1 - 1;                                        // columns [jlo, jhi)
+    int W = (int)(band / nrows / item_window_div());
+    W = std::max(32, std::min(4096, (W + 16) / 32 * 32));
+    struct Blk { int first_j; int maxend; };
+    // windows are independent: block / colidx positions follow from the window sizes, so threads write in place
+    const int nwin = jhi > jlo ? (jhi - jlo + W - 1) / W : 0;
+    std::vector<size_t> blk0((size_t)nwin + 1, 0);
+    for (int w = 0; w < nwin; ++w) {
+        const int c0 = jlo + w * W, c1 = std::min(c0 + W, jhi);
+        blk0[w + 1] = blk0[w] + (size_t)(c1 - c0 + 31) / 32;
+    }
+    std::vector<Blk> blks(blk0[nwin]);
+    const size_t base_blk = colidx.size() / 32;
+    colidx.resize((base_blk + blk0[nwin]) * 32, -1);
+    int32_t* cix = colidx.data() + base_blk * 32;
+    parallel_ranges(nwin, 16, [&](int wa, int wb) {
+        std::vector<uint64_t> order;                 // key = single/paired, last covered position, read index
+        for (int w = wa; w < wb; ++w) {
+            const int c0 = jlo + w * W, c1 = std::min(c0 + W, jhi);
+            order.resize(c1 - c0);
+            for (int j = c0; j < c1; ++j)
+                order[j - c0] = ((uint64_t)(c->is_single[j] ? 0 : 1) << 63) |
+                                ((uint64_t)(uint32_t)(c->cov_last[j] + (1 << 30)) << 32) | (uint32_t)j;
+            std::sort(order.begin(), order.end());
+            for (size_t p = 0; p < order.size(); p += 32) {
+                Blk b{INT32_MAX, INT32_MIN};
+                const size_t bi = blk0[w] + p / 32;
+                for (size_t q = p; q < p + 32 && q < order.size(); ++q) {
+                    const int j = (int)(uint32_t)order[q];
+                    cix[bi * 32 + (q - p)] = j;
+                    b.first_j = std::min(b.first_j, j);
+                    b.maxend = std::max(b.maxend, c->cov_last[j]);
+                }
+                blks[bi] = b;
+            }
+        }
+    });
+    // rows that can reach a block: i > first_j and cov_first[i] <= maxend; cov_first_smin is the suffix minimum of
+    // cov_first (monotone), so the admissible rows are a prefix
+    std::vector<int> first(blks.size()), last(blks.size());
+    long long total = 0;
+    for (size_t b = 0; b < blks.size(); ++b) {
+        first[b] = std::max(w0, blks[b].first_j + 1);
+        last[b] = std::min(w1, (int)(std::upper_bound(c->cov_first_smin.begin(), c->cov_first_smin.end(), blks[b].maxend) -
+                                     c->cov_first_smin.begin())) - 1;
+        if (last[b] >= first[b]) total += last[b] - first[b] + 1;
+    }
+    long long chunk = (total + (long long)n_ctas * 16 - 1) / ((long long)n_ctas * 16);
+    chunk = std::max<long long>(32, std::min<long long>(chunk, 4096));
+    for (size_t b = 0; b < blks.size(); ++b)
+        for (long long r = first[b]; r <= last[b]; r += chunk)
+            items.push_back(make_int4((int)(base_blk + b), (int)r, (int)std::min<long long>(r + chunk, (long long)last[b] + 1), 0));
+}
+
+// Adjacency words per row window (HC_WINDOW_WORDS overrides): the rows of a band are scored in windows so that the words
+// of a finished window can travel to the host while the next window is scored.
+long long window_words() {
+    static const long long v = [] { const char* e = std::getenv("HC_WINDOW_WORDS"); return e ? std::max(1ll, std::atoll(e)) : (4ll << 20); }();
+    return v;
+}
+constexpr int kMaxWindows = 16;
+
+// The scoring plan of rows [row_begin,row_end) (needs compute_layout of the same range): row windows of about equal
+// numbers of adjacency words, each with its own work items.
+void build_plan(hc_ctx* c, int row_begin, int row_end, int n_ctas, bool windows) {
+    if (c->plan_begin == row_begin && c->plan_end == row_end && c->plan_ctas == n_ctas && c->plan_windows == windows) return;
     c->items.clear();
     c->colidx.clear();
+    c->wins.clear();
     const int nrows = row_end - row_begin;
-    if (nrows > 0 && row_end >= 2) {
-        int32_t jlo = INT32_MAX;
-        long long band = 0;
-        for (int k = 0; k < nrows; ++k) { jlo = std::min(jlo, c->lay_col0[k]); band += (row_begin + k) - c->lay_col0[k]; }
-        const int jhi = row_end - 1;                                   // columns [jlo, jhi)
-        int W = (int)(band / nrows / item_window_div());
-        W = std::max(32, std::min(4096, (W + 16) / 32 * 32));
-        struct Blk { int first_j; int maxend; };
-        // windows are independent: block / colidx positions follow from the window sizes, so threads write in place
-        const int nwin = jhi > jlo ? (jhi - jlo + W - 1) / W : 0;
-        std::vector<size_t> blk0((size_t)nwin + 1, 0);
-        for (int w = 0; w < nwin; ++w) {
-            const int w0 = jlo + w * W, w1 = std::min(w0 + W, jhi);
-            blk0[w + 1] = blk0[w] + (size_t)(w1 - w0 + 31) / 32;
+    const long long total = nrows > 0 ? c->lay_off[nrows] : 0;
+    int nw = 1;
+    if (windows) nw = (int)std::max<long long>(1, std::min<long long>(kMaxWindows, (total + window_words() - 1) / window_words()));
+    int r = row_begin;
+    for (int w = 0; w < nw && r < row_end; ++w) {
+        int r1 = row_end;
+        if (w + 1 < nw) {
+            const long long want = total * (w + 1) / nw;
+            r1 = row_begin + (int)(std::lower_bound(c->lay_off.begin(), c->lay_off.begin() + nrows + 1, want) - c->lay_off.begin());
+            r1 = std::min(std::max(r1, r + 1), row_end);
         }
-        std::vector<Blk> blks(blk0[nwin]);
-        c->colidx.assign(blk0[nwin] * 32, -1);
-        parallel_ranges(nwin, 16, [&](int wa, int wb) {
-            std::vector<uint64_t> order;             // key = single/paired, last covered position, read index
-            for (int w = wa; w < wb; ++w) {
-                const int w0 = jlo + w * W, w1 = std::min(w0 + W, jhi);
-                order.resize(w1 - w0);
-                for (int j = w0; j < w1; ++j)
-                    order[j - w0] = ((uint64_t)(c->is_single[j] ? 0 : 1) << 63) |
-                                    ((uint64_t)(uint32_t)(c->cov_last[j] + (1 << 30)) << 32) | (uint32_t)j;
-                std::sort(order.begin(), order.end());
-                for (size_t p = 0; p < order.size(); p += 32) {
-                    Blk b{INT32_MAX, INT32_MIN};
-                    const size_t bi = blk0[w] + p / 32;
-                    for (size_t q = p; q < p + 32 && q < order.size(); ++q) {
-                        const int j = (int)(uint32_t)order[q];
-                        c->colidx[bi * 32 + (q - p)] = j;
-                        b.first_j = std::min(b.first_j, j);
-                        b.maxend = std::max(b.maxend, c->cov_last[j]);
-                    }
-                    blks[bi] = b;
-                }
-            }
-        });
-        // rows that can reach a block: i > first_j and cov_first[i] <= maxend; cov_first_smin is the suffix minimum of
-        // cov_first (monotone), so the admissible rows are a prefix
-        std::vector<int> first(blks.size()), last(blks.size());
-        long long total = 0;
-        for (size_t b = 0; b < blks.size(); ++b) {
-            first[b] = std::max(row_begin, blks[b].first_j + 1);
-            last[b] = std::min(row_end, (int)(std::upper_bound(c->cov_first_smin.begin(), c->cov_first_smin.end(), blks[b].maxend) -
-                                              c->cov_first_smin.begin())) - 1;
-            if (last[b] >= first[b]) total += last[b] - first[b] + 1;
-        }
-        long long chunk = (total + (long long)n_ctas * 16 - 1) / ((long long)n_ctas * 16);
-        chunk = std::max<long long>(32, std::min<long long>(chunk, 4096));
-        for (size_t b = 0; b < blks.size(); ++b)
-            for (long long r = first[b]; r <= last[b]; r += chunk)
-                c->items.push_back(make_int4((int)b, (int)r, (int)std::min<long long>(r + chunk, (long long)last[b] + 1), 0));
+        hc_ctx::Win win;
+        win.r0 = r; win.r1 = r1;
+        win.item0 = c->items.size();
+        build_items_range(c, r, r1, n_ctas, c->items, c->colidx);
+        win.n_items = c->items.size() - win.item0;
+        win.word0 = c->lay_off[r - row_begin];
+        win.n_words = c->lay_off[r1 - row_begin] - win.word0;
+        c->wins.push_back(win);
+        r = r1;
     }
-    c->items_begin = row_begin;
-    c->items_end = row_end;
+    c->plan_begin = row_begin; c->plan_end = row_end; c->plan_ctas = n_ctas; c->plan_windows = windows;
+}
+
+// similarityCriterion's last lines (src/NewEdgeCalculator.cpp:1132-1140) on the host, with glibc's log10: the decision for
+// a pair the device flagged as within ambiguity_rel_tol of the threshold. (probM, prob0, cc, tc) are bit-exact.
+bool host_decide(const hc_ctx* c, double probM, double prob0, int cc, int tc, double log_cutoff, double* score_out) {
+    double prob, potence;
+    if (c->par.no_prob0) { prob = std::log10(probM); potence = 1.0 / cc; }
+    else { prob = std::log10(probM) + prob0; potence = 1.0 / (cc + tc); }
+    const double score = prob * potence;
+    if (score_out) *score_out = score;
+    return score >= log_cutoff;
 }
 
 }  // namespace
@@ -858,9 +915,12 @@ int hc_create(const hc_params* params, hc_ctx** out) {
         build_tile_programs(tp);
         if ((e = cudaMalloc((void**)&c->d_tprog, tp.size() * sizeof(uint32_t))) != cudaSuccess) return fail("cudaMalloc", e);
         if ((e = cudaMemcpy(c->d_tprog, tp.data(), tp.size() * sizeof(uint32_t), cudaMemcpyHostToDevice)) != cudaSuccess) return fail("cudaMemcpy", e);
-        if ((e = cudaMalloc((void**)&c->d_item_counter, sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
+        if ((e = cudaMalloc((void**)&c->d_item_counter, kMaxWindows * sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
     }
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    if ((e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    for (int k = 0; k < kMaxWindows; ++k)
+        if ((e = cudaEventCreateWithFlags(&c->win_ev[k], cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaMalloc((void**)&c->d_stats, 2 * sizeof(BandStatsDev))) != cudaSuccess) return fail("cudaMalloc", e);
@@ -888,6 +948,8 @@ void hc_destroy(hc_ctx* c) {
     cudaFree(c->d_opsA); cudaFree(c->d_opsF); cudaFree(c->d_tab9);
     cudaFree(c->d_logsum); cudaFree(c->d_simpson_ln); cudaFree(c->d_qres); cudaFree(c->d_qseg);
     cudaFree(c->d_detail); cudaFree(c->d_colidx);
+    for (int k = 0; k < kMaxWindows; ++k) if (c->win_ev[k]) cudaEventDestroy(c->win_ev[k]);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -937,7 +999,7 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     std::memcpy(c->qual_chars, p->qual_chars, sizeof(c->qual_chars));
     c->have_formats = false;
     int rc;
-    c->items_begin = c->items_end = -1;
+    c->plan_begin = c->plan_end = -1;
     c->n_reads = p->n_reads;
     c->K = std::max(p->n_qual_codes, 1);
     c->max_ops = p->max_ops_per_read;
@@ -1019,8 +1081,10 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     c->cov_last.resize(p->n_reads);
     c->is_single.resize(p->n_reads);
     c->cov_first_smin.resize(p->n_reads);
+    c->ncov_flags.resize(p->n_reads);
     int run = INT32_MIN;
     for (int r = 0; r < p->n_reads; ++r) {
+        c->ncov_flags[r] = p->hdr[r].ncov_flags;
         c->cov_first[r] = p->hdr[r].cov_first;
         c->cov_last[r] = p->hdr[r].cov_last;
         c->is_single[r] = (p->hdr[r].ncov_flags & HC_FLAG_SINGLE_END) ? 1 : 0;
@@ -1033,7 +1097,7 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     // the host, while the copies and the device-side builds above are in flight (hc_score_band(0, n) finds them cached)
     if (p->n_reads > 1 && (tile_eligible(c) || tile2_eligible(c) || stream_eligible(c))) {
         compute_layout(c, 0, p->n_reads);
-        build_items(c, 0, p->n_reads, c->sm_count);
+        build_plan(c, 0, p->n_reads, c->sm_count, true);
     }
     CU_TRY(c, cudaStreamSynchronize(c->stream));
     return HC_OK;
@@ -1051,11 +1115,37 @@ int hc_band_layout(hc_ctx* c, int32_t row_begin, int32_t row_end, int32_t* col0,
     return HC_OK;
 }
 
+// Host side of the near-threshold pairs: fetch the device's list, re-decide each pair with glibc's log10, patch the
+// adjacency bit on the host (`adj`, may be null) and on the device, and fix the edge count. n = pairs in c->amb_host.
+static int redecide_ambiguous(hc_ctx* c, int row_begin, uint32_t* adj, long long* edge_delta) {
+    *edge_delta = 0;
+    for (hc_ambiguous& a : c->amb_host) {
+        double score = a.score;
+        const bool host_edge = host_decide(c, a.probM, a.prob0, a.cc, a.tc, a.cutoff, &score);
+        a.edge_device = a.edge;
+        a.score = score;
+        a.edge = host_edge ? 1 : 0;
+        if (a.edge == a.edge_device) continue;
+        *edge_delta += a.edge - a.edge_device;
+        const int k = a.i - row_begin;
+        const int rel = a.j - c->lay_col0[k];
+        const long long w = c->lay_off[k] + (rel >> 5);
+        const uint32_t bit = 1u << (rel & 31);
+        uint32_t word = 0;
+        CU_TRY(c, cudaMemcpy(&word, c->d_adj + w, sizeof(word), cudaMemcpyDeviceToHost));
+        word = host_edge ? (word | bit) : (word & ~bit);
+        CU_TRY(c, cudaMemcpy(c->d_adj + w, &word, sizeof(word), cudaMemcpyHostToDevice));
+        if (adj) adj[w] = word;
+    }
+    return HC_OK;
+}
+
 static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32_t* adj, int64_t n_words, hc_ambiguous* amb,
                            int32_t amb_cap, hc_band_stats* stats, hc_pair_result* detail) {
     if (!c) return HC_E_INVALID;
     if (!c->d_hdr) { c->err = "hc_score_band: no batch uploaded"; return HC_E_STATE; }
     if (row_begin < 0 || row_end < row_begin || row_end > c->n_reads) { c->err = "hc_score_band: bad row range"; return HC_E_INVALID; }
+    if (amb_cap < 0 || (amb_cap > 0 && !amb)) { c->err = "hc_score_band: bad near-threshold list"; return HC_E_INVALID; }
     CU_TRY(c, cudaSetDevice(c->device));
     compute_layout(c, row_begin, row_end);
     const int nrows = row_end - row_begin;
@@ -1074,112 +1164,131 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
     const bool use_tile = use_tile1 || use_tile2 || use_stream;
     if (detail && !use_tile) { c->err = "hc_score_band_detail: only the tiled kernels write per-slot detail; use hc_score_pairs"; return HC_E_STATE; }
     int rc;
-    size_t cap2 = c->rows_cap;
-    if ((rc = grow(c, c->d_col0, c->rows_cap, (size_t)nrows + 1)) != HC_OK) return rc;
-    if ((rc = grow(c, c->d_word_off, cap2, (size_t)nrows + 1)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_col0, c->col0_cap, (size_t)nrows + 1)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_word_off, c->word_off_cap, (size_t)nrows + 1)) != HC_OK) return rc;
     if ((rc = grow(c, c->d_adj, c->adj_cap, (size_t)std::max<long long>(total, 1))) != HC_OK) return rc;
     if (detail && (rc = grow(c, c->d_detail, c->detail_cap, (size_t)std::max<long long>(total, 1) * 32)) != HC_OK) return rc;
-    if (amb_cap > c->amb_cap) {
-        cudaFree(c->d_amb); c->d_amb = nullptr; c->amb_cap = 0;
-        CU_TRY(c, cudaMalloc((void**)&c->d_amb, (size_t)amb_cap * sizeof(hc_ambiguous)));
-        c->amb_cap = amb_cap;
-    }
+    // the device always lists the near-threshold pairs: they are re-decided on the host whether or not the caller wants the report
+    if ((rc = grow(c, c->d_amb, c->amb_cap, (size_t)std::max(amb_cap, 4096))) != HC_OK) return rc;
     CU_TRY(c, cudaMemcpyAsync(c->d_col0, c->lay_col0.data(), sizeof(int32_t) * nrows, cudaMemcpyHostToDevice, c->stream));
     CU_TRY(c, cudaMemcpyAsync(c->d_word_off, c->lay_off.data(), sizeof(long long) * ((size_t)nrows + 1), cudaMemcpyHostToDevice, c->stream));
-    CU_TRY(c, cudaMemsetAsync(c->d_stats, 0, 2 * sizeof(BandStatsDev), c->stream));    // [1]: HC_T2_PROFILE counters
-    int launches = 0;
-    c->last_kernel = 0;
-    if (use_tile && total > 0) {
-        const TileGeom g = use_stream ? stream_geometry(c) : tile_geometry(c);
-        const Tile2Geom g2 = tile2_geometry(c);
-        const size_t smem_bytes = use_tile2 ? g2.smem : g.smem;
-        const int threads = (use_tile2 ? g2.nwarps : g.nwarps) * 32;
-        int per_sm = 0;
-        const bool split = c->K <= split_max_k();
-        if (use_tile2) {
-            const bool map = c->d_simpson != nullptr;
-            auto kern = split ? (map ? tile2::score_tile2_kernel<true, true> : tile2::score_tile2_kernel<true, false>)
-                              : (map ? tile2::score_tile2_kernel<false, true> : tile2::score_tile2_kernel<false, false>);
-            CU_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-            CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem_bytes));
-        } else {
-            const bool map = c->d_simpson != nullptr;
-            auto kern = tile1_kernel(use_stream, map, g.nwarps == tile::kWarps);
-            CU_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-            CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem_bytes));
-        }
-        if (per_sm < 1) { c->err = "hc_score_band: tiled kernel does not fit on an SM"; return HC_E_CUDA; }
-        const int n_ctas = c->sm_count * per_sm;
-        build_items(c, row_begin, row_end, n_ctas);
-        const size_t n_items = c->items.size();
-        if ((rc = grow(c, c->d_items, c->items_cap, std::max<size_t>(n_items, 1))) != HC_OK) return rc;
-        CU_TRY(c, cudaMemcpyAsync(c->d_items, c->items.data(), sizeof(int4) * n_items, cudaMemcpyHostToDevice, c->stream));
-        if ((rc = grow(c, c->d_colidx, c->colidx_cap, std::max<size_t>(c->colidx.size(), 32))) != HC_OK) return rc;
-        CU_TRY(c, cudaMemcpyAsync(c->d_colidx, c->colidx.data(), sizeof(int32_t) * c->colidx.size(), cudaMemcpyHostToDevice, c->stream));
-        CU_TRY(c, cudaMemsetAsync(c->d_item_counter, 0, sizeof(int), c->stream));
-        // words of rows whose band holds no scored column block stay zero
-        CU_TRY(c, cudaMemsetAsync(c->d_adj, 0, (size_t)total * sizeof(uint32_t), c->stream));
-        if (detail) CU_TRY(c, cudaMemsetAsync(c->d_detail, 0, (size_t)total * 32 * sizeof(hc_pair_result), c->stream));
-        tile2::Args2 a{};
-        a.P = dev_params(c);
-        a.opsA = c->d_opsA; a.opsF = c->d_opsF; a.tab9 = c->d_tab9; a.tab_words = (int)tile2_table_words(c->K);
-        a.row_bytes = tile2_row_bytes(c->K); a.entry_bytes = tile2_entry_bytes(c->K);
-        a.hdr = c->d_hdr; a.ops = c->d_ops; a.aux = c->d_aux; a.col2op = c->d_col2op; a.prog = c->d_tprog;
-        a.n_reads = c->n_reads; a.row_begin = row_begin; a.col0 = c->d_col0; a.word_off = c->d_word_off;
-        a.colidx = c->d_colidx; a.items = c->d_items; a.n_items = (int)n_items; a.item_counter = c->d_item_counter;
-        a.adj = c->d_adj; a.stats = c->d_stats; a.amb = amb ? c->d_amb : nullptr; a.amb_cap = amb ? amb_cap : 0;
-        a.detail = detail ? c->d_detail : nullptr;
-        a.maxw = use_tile2 ? g2.maxw : g.maxw; a.abuf_bytes = use_tile2 ? g2.abuf_bytes : g.abuf_bytes;
-        CU_TRY(c, cudaEventRecord(c->ev0, c->stream));
-        if (n_items > 0) {
-            const int blocks = (int)std::min<size_t>(n_items, (size_t)n_ctas);
-            const bool map = c->d_simpson != nullptr;
-            if (use_tile2 && split && map) tile2::score_tile2_kernel<true, true><<<blocks, threads, smem_bytes, c->stream>>>(a);
-            else if (use_tile2 && split) tile2::score_tile2_kernel<true, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
-            else if (use_tile2 && map) tile2::score_tile2_kernel<false, true><<<blocks, threads, smem_bytes, c->stream>>>(a);
-            else if (use_tile2) tile2::score_tile2_kernel<false, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
-            else tile1_kernel(use_stream, map, g.nwarps == tile::kWarps)<<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
-            CU_TRY(c, cudaGetLastError());
-            launches = 1;
-            c->last_kernel = use_tile2 ? HC_KERNEL_TILED2 : (use_stream ? HC_KERNEL_STREAMED : HC_KERNEL_TILED);
-        }
-        CU_TRY(c, cudaEventRecord(c->ev1, c->stream));
-    } else {
-        CU_TRY(c, cudaEventRecord(c->ev0, c->stream));
-        if (total > 0) {
-            const int threads = 256;
-            const long long want = (total + (threads / 32) - 1) / (threads / 32);
-            const int blocks = (int)std::min<long long>(want, (long long)c->sm_count * 8);
-            score_band_kernel<<<blocks, threads, 0, c->stream>>>(dev_params(c), c->d_hdr, c->d_ops, row_begin, nrows, c->d_col0,
-                                                                 c->d_word_off, total, c->d_adj, c->d_stats,
-                                                                 amb ? c->d_amb : nullptr, amb ? amb_cap : 0);
-            CU_TRY(c, cudaGetLastError());
-            launches = 1;
-            c->last_kernel = HC_KERNEL_GENERIC;
-        }
-        CU_TRY(c, cudaEventRecord(c->ev1, c->stream));
-    }
     BandStatsDev hs{};
-    CU_TRY(c, cudaMemcpyAsync(&hs, c->d_stats, sizeof(hs), cudaMemcpyDeviceToHost, c->stream));
+    int launches = 0;
+    for (int attempt = 0;; ++attempt) {
+        CU_TRY(c, cudaMemsetAsync(c->d_stats, 0, 2 * sizeof(BandStatsDev), c->stream));    // [1]: HC_T2_PROFILE counters
+        launches = 0;
+        c->last_kernel = 0;
+        if (use_tile && total > 0) {
+            const TileGeom g = use_stream ? stream_geometry(c) : tile_geometry(c);
+            const Tile2Geom g2 = tile2_geometry(c);
+            const size_t smem_bytes = use_tile2 ? g2.smem : g.smem;
+            const int threads = (use_tile2 ? g2.nwarps : g.nwarps) * 32;
+            int per_sm = 0;
+            const bool split = c->K <= split_max_k();
+            const bool map = c->d_simpson != nullptr;
+            if (use_tile2) {
+                auto kern = split ? (map ? tile2::score_tile2_kernel<true, true> : tile2::score_tile2_kernel<true, false>)
+                                  : (map ? tile2::score_tile2_kernel<false, true> : tile2::score_tile2_kernel<false, false>);
+                CU_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+                CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem_bytes));
+            } else {
+                auto kern = tile1_kernel(use_stream, map, g.nwarps == tile::kWarps);
+                CU_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+                CU_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem_bytes));
+            }
+            if (per_sm < 1) { c->err = "hc_score_band: tiled kernel does not fit on an SM"; return HC_E_CUDA; }
+            const int n_ctas = c->sm_count * per_sm;
+            build_plan(c, row_begin, row_end, n_ctas, detail == nullptr);
+            const size_t n_items = c->items.size();
+            if ((rc = grow(c, c->d_items, c->items_cap, std::max<size_t>(n_items, 1))) != HC_OK) return rc;
+            CU_TRY(c, cudaMemcpyAsync(c->d_items, c->items.data(), sizeof(int4) * n_items, cudaMemcpyHostToDevice, c->stream));
+            if ((rc = grow(c, c->d_colidx, c->colidx_cap, std::max<size_t>(c->colidx.size(), 32))) != HC_OK) return rc;
+            CU_TRY(c, cudaMemcpyAsync(c->d_colidx, c->colidx.data(), sizeof(int32_t) * c->colidx.size(), cudaMemcpyHostToDevice, c->stream));
+            CU_TRY(c, cudaMemsetAsync(c->d_item_counter, 0, kMaxWindows * sizeof(int), c->stream));
+            CU_TRY(c, cudaEventRecord(c->ev0, c->stream));
+            // words of rows whose band holds no scored column block stay zero
+            CU_TRY(c, cudaMemsetAsync(c->d_adj, 0, (size_t)total * sizeof(uint32_t), c->stream));
+            if (detail) CU_TRY(c, cudaMemsetAsync(c->d_detail, 0, (size_t)total * 32 * sizeof(hc_pair_result), c->stream));
+            tile2::Args2 a{};
+            a.P = dev_params(c);
+            a.opsA = c->d_opsA; a.opsF = c->d_opsF; a.tab9 = c->d_tab9; a.tab_words = (int)tile2_table_words(c->K);
+            a.row_bytes = tile2_row_bytes(c->K); a.entry_bytes = tile2_entry_bytes(c->K);
+            a.hdr = c->d_hdr; a.ops = c->d_ops; a.aux = c->d_aux; a.col2op = c->d_col2op; a.prog = c->d_tprog;
+            a.n_reads = c->n_reads; a.row_begin = row_begin; a.col0 = c->d_col0; a.word_off = c->d_word_off;
+            a.colidx = c->d_colidx;
+            a.adj = c->d_adj; a.stats = c->d_stats; a.amb = c->d_amb; a.amb_cap = (int)std::min<size_t>(c->amb_cap, (size_t)INT32_MAX);
+            a.detail = detail ? c->d_detail : nullptr;
+            a.maxw = use_tile2 ? g2.maxw : g.maxw; a.abuf_bytes = use_tile2 ? g2.abuf_bytes : g.abuf_bytes;
+            for (size_t k = 0; k < c->wins.size(); ++k) {
+                const hc_ctx::Win& w = c->wins[k];
+                if (w.n_items > 0) {
+                    a.items = c->d_items + w.item0; a.n_items = (int)w.n_items; a.item_counter = c->d_item_counter + k;
+                    const int blocks = (int)std::min<size_t>(w.n_items, (size_t)n_ctas);
+                    if (use_tile2 && split && map) tile2::score_tile2_kernel<true, true><<<blocks, threads, smem_bytes, c->stream>>>(a);
+                    else if (use_tile2 && split) tile2::score_tile2_kernel<true, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
+                    else if (use_tile2 && map) tile2::score_tile2_kernel<false, true><<<blocks, threads, smem_bytes, c->stream>>>(a);
+                    else if (use_tile2) tile2::score_tile2_kernel<false, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
+                    else tile1_kernel(use_stream, map, g.nwarps == tile::kWarps)<<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
+                    CU_TRY(c, cudaGetLastError());
+                    launches++;
+                    c->last_kernel = use_tile2 ? HC_KERNEL_TILED2 : (use_stream ? HC_KERNEL_STREAMED : HC_KERNEL_TILED);
+                }
+                CU_TRY(c, cudaEventRecord(c->win_ev[k], c->stream));
+            }
+            CU_TRY(c, cudaEventRecord(c->ev1, c->stream));
+            // the words of a finished window go to the host while the later windows are scored
+            if (adj)
+                for (size_t k = 0; k < c->wins.size(); ++k) {
+                    const hc_ctx::Win& w = c->wins[k];
+                    if (w.n_words <= 0) continue;
+                    CU_TRY(c, cudaStreamWaitEvent(c->copy_stream, c->win_ev[k], 0));
+                    CU_TRY(c, cudaMemcpyAsync(adj + w.word0, c->d_adj + w.word0, (size_t)w.n_words * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->copy_stream));
+                }
+        } else {
+            CU_TRY(c, cudaEventRecord(c->ev0, c->stream));
+            if (total > 0) {
+                const int threads = 256;
+                const long long want = (total + (threads / 32) - 1) / (threads / 32);
+                const int blocks = (int)std::min<long long>(want, (long long)c->sm_count * 8);
+                score_band_kernel<<<blocks, threads, 0, c->stream>>>(dev_params(c), c->d_hdr, c->d_ops, row_begin, nrows, c->d_col0,
+                                                                     c->d_word_off, total, c->d_adj, c->d_stats, c->d_amb,
+                                                                     (int)std::min<size_t>(c->amb_cap, (size_t)INT32_MAX));
+                CU_TRY(c, cudaGetLastError());
+                launches = 1;
+                c->last_kernel = HC_KERNEL_GENERIC;
+            }
+            CU_TRY(c, cudaEventRecord(c->ev1, c->stream));
+            if (adj && total > 0) CU_TRY(c, cudaMemcpyAsync(adj, c->d_adj, (size_t)total * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+        }
+        CU_TRY(c, cudaMemcpyAsync(&hs, c->d_stats, sizeof(hs), cudaMemcpyDeviceToHost, c->stream));
 #ifdef HC_T2_PROFILE
-    {
-        BandStatsDev pr{};
-        CU_TRY(c, cudaMemcpy(&pr, c->d_stats + 1, sizeof(pr), cudaMemcpyDeviceToHost));
-        std::fprintf(stderr, "[HC_T2_PROFILE] 8-column iterations: first pass %llu (%.2f lanes), later passes %llu (%.2f lanes)\n",
-                     pr.pairs_total, pr.pairs_total ? (double)pr.pairs_scored / pr.pairs_total : 0.0, pr.pairs_walked,
-                     pr.pairs_walked ? (double)pr.edges / pr.pairs_walked : 0.0);
-    }
+        {
+            BandStatsDev pr{};
+            CU_TRY(c, cudaMemcpy(&pr, c->d_stats + 1, sizeof(pr), cudaMemcpyDeviceToHost));
+            std::fprintf(stderr, "[HC_T2_PROFILE] 8-column iterations: first pass %llu (%.2f lanes), later passes %llu (%.2f lanes)\n",
+                         pr.pairs_total, pr.pairs_total ? (double)pr.pairs_scored / pr.pairs_total : 0.0, pr.pairs_walked,
+                         pr.pairs_walked ? (double)pr.edges / pr.pairs_walked : 0.0);
+        }
 #endif
-    if (adj && total > 0) CU_TRY(c, cudaMemcpyAsync(adj, c->d_adj, (size_t)total * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
-    if (detail && total > 0) CU_TRY(c, cudaMemcpyAsync(detail, c->d_detail, (size_t)total * 32 * sizeof(hc_pair_result), cudaMemcpyDeviceToHost, c->stream));
-    CU_TRY(c, cudaStreamSynchronize(c->stream));
-    if (amb && amb_cap > 0 && hs.ambiguous > 0) {
-        const size_t k = (size_t)std::min<unsigned long long>(hs.ambiguous, (unsigned long long)amb_cap);
-        CU_TRY(c, cudaMemcpy(amb, c->d_amb, k * sizeof(hc_ambiguous), cudaMemcpyDeviceToHost));
+        if (detail && total > 0) CU_TRY(c, cudaMemcpyAsync(detail, c->d_detail, (size_t)total * 32 * sizeof(hc_pair_result), cudaMemcpyDeviceToHost, c->stream));
+        CU_TRY(c, cudaStreamSynchronize(c->stream));
+        CU_TRY(c, cudaStreamSynchronize(c->copy_stream));
+        if (hs.ambiguous <= (unsigned long long)c->amb_cap || attempt > 0) break;
+        // more near-threshold pairs than the list holds (a wide tolerance): a larger list, and the pass again
+        if ((rc = grow(c, c->d_amb, c->amb_cap, (size_t)hs.ambiguous)) != HC_OK) return rc;
+    }
+    long long edge_delta = 0;
+    c->amb_host.resize((size_t)std::min<unsigned long long>(hs.ambiguous, (unsigned long long)c->amb_cap));
+    if (!c->amb_host.empty()) {
+        CU_TRY(c, cudaMemcpy(c->amb_host.data(), c->d_amb, c->amb_host.size() * sizeof(hc_ambiguous), cudaMemcpyDeviceToHost));
+        // the device lists them in completion order: sort by (i, j) so that the report does not depend on the schedule
+        std::sort(c->amb_host.begin(), c->amb_host.end(), [](const hc_ambiguous& x, const hc_ambiguous& y) { return x.i != y.i ? x.i < y.i : x.j < y.j; });
+        if ((rc = redecide_ambiguous(c, row_begin, adj, &edge_delta)) != HC_OK) return rc;
+        if (amb) std::memcpy(amb, c->amb_host.data(), std::min<size_t>(c->amb_host.size(), (size_t)amb_cap) * sizeof(hc_ambiguous));
     }
     if (stats) {
         stats->pairs_total = (int64_t)hs.pairs_total; stats->pairs_scored = (int64_t)hs.pairs_scored;
-        stats->pairs_walked = (int64_t)hs.pairs_walked; stats->edges = (int64_t)hs.edges;
+        stats->pairs_walked = (int64_t)hs.pairs_walked; stats->edges = (int64_t)hs.edges + edge_delta;
         stats->sum_cc = (int64_t)hs.sum_cc; stats->sum_tc = (int64_t)hs.sum_tc; stats->undefined = (int64_t)hs.undefined;
         stats->ambiguous = (int64_t)hs.ambiguous;
         float ms = 0.f;
@@ -1266,9 +1375,8 @@ int hc_quasi_score_pairs(hc_ctx* c, const hc_quasi_params* qp, const int32_t* pi
     if (npairs == 0) return HC_OK;
     for (int64_t k = 0; k < npairs; ++k)
         if (pi[k] < 0 || pi[k] >= c->n_reads || pj[k] < 0 || pj[k] >= c->n_reads) { c->err = "hc_quasi_score_pairs: read index out of range"; return HC_E_INVALID; }
-    size_t cap2 = c->pairs_cap;
-    if ((rc = grow(c, c->d_pi, c->pairs_cap, (size_t)npairs)) != HC_OK) return rc;
-    if ((rc = grow(c, c->d_pj, cap2, (size_t)npairs)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_pi, c->pi_cap, (size_t)npairs)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_pj, c->pj_cap, (size_t)npairs)) != HC_OK) return rc;
     if ((rc = grow(c, c->d_qres, c->qres_cap, (size_t)npairs)) != HC_OK) return rc;
     CU_TRY(c, cudaMemcpyAsync(c->d_pi, pi, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, c->stream));
     CU_TRY(c, cudaMemcpyAsync(c->d_pj, pj, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, c->stream));
@@ -1291,9 +1399,8 @@ int hc_quasi_score_band(hc_ctx* c, const hc_quasi_params* qp, int32_t row_begin,
     const int nrows = row_end - row_begin;
     const long long total = c->lay_off[nrows];
     if (adj && n_words < total) { c->err = "hc_quasi_score_band: output buffer smaller than hc_band_layout's n_words"; return HC_E_INVALID; }
-    size_t cap2 = c->rows_cap;
-    if ((rc = grow(c, c->d_col0, c->rows_cap, (size_t)nrows + 1)) != HC_OK) return rc;
-    if ((rc = grow(c, c->d_word_off, cap2, (size_t)nrows + 1)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_col0, c->col0_cap, (size_t)nrows + 1)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_word_off, c->word_off_cap, (size_t)nrows + 1)) != HC_OK) return rc;
     if ((rc = grow(c, c->d_adj, c->adj_cap, (size_t)std::max<long long>(total, 1))) != HC_OK) return rc;
     CU_TRY(c, cudaMemcpyAsync(c->d_col0, c->lay_col0.data(), sizeof(int32_t) * nrows, cudaMemcpyHostToDevice, c->stream));
     CU_TRY(c, cudaMemcpyAsync(c->d_word_off, c->lay_off.data(), sizeof(long long) * ((size_t)nrows + 1), cudaMemcpyHostToDevice, c->stream));
@@ -1342,10 +1449,9 @@ int hc_score_pairs(hc_ctx* c, const int32_t* pi, const int32_t* pj, int64_t npai
     if (npairs == 0) return HC_OK;
     CU_TRY(c, cudaSetDevice(c->device));
     int rc;
-    size_t cap_i = c->pairs_cap, cap_j = c->pairs_cap;
-    if ((rc = grow(c, c->d_pi, cap_i, (size_t)npairs)) != HC_OK) return rc;
-    if ((rc = grow(c, c->d_pj, cap_j, (size_t)npairs)) != HC_OK) return rc;
-    if ((rc = grow(c, c->d_res, c->pairs_cap, (size_t)npairs)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_pi, c->pi_cap, (size_t)npairs)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_pj, c->pj_cap, (size_t)npairs)) != HC_OK) return rc;
+    if ((rc = grow(c, c->d_res, c->res_cap, (size_t)npairs)) != HC_OK) return rc;
     CU_TRY(c, cudaMemcpyAsync(c->d_pi, pi, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, c->stream));
     CU_TRY(c, cudaMemcpyAsync(c->d_pj, pj, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, c->stream));
     const int threads = 128;
@@ -1354,6 +1460,170 @@ int hc_score_pairs(hc_ctx* c, const int32_t* pi, const int32_t* pj, int64_t npai
     CU_TRY(c, cudaGetLastError());
     CU_TRY(c, cudaMemcpyAsync(out, c->d_res, sizeof(hc_pair_result) * npairs, cudaMemcpyDeviceToHost, c->stream));
     CU_TRY(c, cudaStreamSynchronize(c->stream));
+    // near-threshold pairs: the decision is the host's (glibc log10), as in hc_score_band
+    const DevParams P = dev_params(c);
+    for (int64_t k = 0; k < npairs; ++k) {
+        if (!out[k].ambiguous) continue;
+        const bool cl1 = c->ncov_flags[pi[k]] & HC_FLAG_IS_CLIQUE, cl2 = c->ncov_flags[pj[k]] & HC_FLAG_IS_CLIQUE;
+        const double cutoff = P.log_cutoff[(cl1 && cl2) ? 0 : ((cl1 || cl2) ? 1 : 2)];
+        out[k].edge = host_decide(c, out[k].probM, out[k].prob0, out[k].cc, out[k].tc, cutoff, &out[k].score) ? 1 : 0;
+    }
+    return HC_OK;
+}
+
+}  // extern "C"
+
+// ---- several GPUs behind one handle ------------------------------------------------------------------------------
+struct hc_multi {
+    std::vector<hc_ctx*> ctx;
+    std::vector<hc_packed*> part;              // slices of the resident batch (headers re-based), one per device
+    std::vector<int32_t> cuts, first;
+    std::vector<int32_t> col0; std::vector<int64_t> word_off;      // band layout of the whole batch
+    int n_reads = 0;
+    bool resident = false;
+    std::string err;
+};
+
+namespace {
+// f(k) for every device k on its own host thread (CUDA's current device is per thread); returns the first failure.
+template <class F>
+int for_each_device(hc_multi* m, F f) {
+    const int n = (int)m->ctx.size();
+    std::vector<int> rc((size_t)n, HC_OK);
+    if (n == 1) rc[0] = f(0);
+    else {
+        std::vector<std::thread> pool;
+        for (int k = 0; k < n; ++k) pool.emplace_back([&, k] { rc[k] = f(k); });
+        for (auto& t : pool) t.join();
+    }
+    for (int k = 0; k < n; ++k)
+        if (rc[k] != HC_OK) { m->err = "device " + std::to_string(k) + ": " + m->ctx[k]->err; return rc[k]; }
+    return HC_OK;
+}
+void free_parts(hc_multi* m) {
+    for (hc_packed* q : m->part) hc_packed_free(q);
+    m->part.clear();
+}
+}  // namespace
+
+extern "C" {
+
+int hc_multi_create(const hc_params* params, const int32_t* devices, int32_t n_devices, hc_multi** out) {
+    if (!params || !devices || !out || n_devices < 1 || n_devices > 64) { hc::set_global_error("hc_multi_create: bad argument"); return HC_E_INVALID; }
+    *out = nullptr;
+    hc_multi* m = new hc_multi();
+    for (int k = 0; k < n_devices; ++k) {
+        hc_params p = *params;
+        p.device = devices[k];
+        hc_ctx* c = nullptr;
+        const int rc = hc_create(&p, &c);
+        if (rc != HC_OK) { hc_multi_destroy(m); return rc; }
+        m->ctx.push_back(c);
+    }
+    *out = m;
+    return HC_OK;
+}
+
+void hc_multi_destroy(hc_multi* m) {
+    if (!m) return;
+    free_parts(m);
+    for (hc_ctx* c : m->ctx) hc_destroy(c);
+    delete m;
+}
+
+const char* hc_multi_last_error(const hc_multi* m) { return m ? m->err.c_str() : hc::global_error(); }
+int hc_multi_n_devices(const hc_multi* m) { return m ? (int)m->ctx.size() : 0; }
+hc_ctx* hc_multi_context(hc_multi* m, int32_t k) { return (m && k >= 0 && k < (int)m->ctx.size()) ? m->ctx[k] : nullptr; }
+
+int hc_multi_set_params(hc_multi* m, const hc_params* params) {
+    if (!m || !params) return HC_E_INVALID;
+    for (hc_ctx* c : m->ctx) { const int rc = hc_set_params(c, params); if (rc != HC_OK) return rc; }
+    return HC_OK;
+}
+
+int hc_multi_upload(hc_multi* m, const hc_packed* p) {
+    if (!m || !p) return HC_E_INVALID;
+    const int n = p->n_reads, D = (int)m->ctx.size();
+    m->resident = false;
+    free_parts(m);
+    std::vector<int32_t> cf((size_t)std::max(n, 1)), cl((size_t)std::max(n, 1));
+    for (int r = 0; r < n; ++r) { cf[r] = p->hdr[r].cov_first; cl[r] = p->hdr[r].cov_last; }
+    m->cuts.assign((size_t)D + 1, 0);
+    m->first.assign((size_t)D, 0);
+    int rc = hc_partition_rows(cf.data(), cl.data(), n, D, m->cuts.data(), m->first.data());
+    if (rc != HC_OK) { m->err = hc::global_error(); return rc; }
+    m->part.assign((size_t)D, nullptr);
+    for (int k = 0; k < D; ++k)
+        if ((rc = hc_packed_slice(p, m->first[k], m->cuts[k + 1], &m->part[k])) != HC_OK) { m->err = hc::global_error(); return rc; }
+    if ((rc = for_each_device(m, [&](int k) { return hc_upload(m->ctx[k], m->part[k]); })) != HC_OK) return rc;
+    // the band layout of the whole batch = the parts' layouts shifted by first[k] (hc_partition_rows), concatenated
+    m->col0.assign((size_t)std::max(n, 1), 0);
+    m->word_off.assign((size_t)n + 1, 0);
+    int64_t acc = 0;
+    for (int k = 0; k < D; ++k) {
+        hc_ctx* c = m->ctx[k];
+        const int lo = m->cuts[k] - m->first[k], hi = m->cuts[k + 1] - m->first[k];
+        compute_layout(c, lo, hi);
+        for (int i = lo; i < hi; ++i) {
+            m->col0[(size_t)m->first[k] + i] = c->lay_col0[i - lo] + m->first[k];
+            m->word_off[(size_t)m->first[k] + i] = acc + c->lay_off[i - lo];
+        }
+        acc += c->lay_off[hi - lo];
+    }
+    m->word_off[n] = acc;
+    m->n_reads = n;
+    m->resident = true;
+    return HC_OK;
+}
+
+int hc_multi_partition(const hc_multi* m, int32_t* cuts, int32_t* first) {
+    if (!m || !m->resident) return HC_E_STATE;
+    if (cuts) std::memcpy(cuts, m->cuts.data(), m->cuts.size() * sizeof(int32_t));
+    if (first) std::memcpy(first, m->first.data(), m->first.size() * sizeof(int32_t));
+    return HC_OK;
+}
+
+int hc_multi_band_layout(hc_multi* m, int32_t* col0, int64_t* word_off, int64_t* n_words) {
+    if (!m) return HC_E_INVALID;
+    if (!m->resident) { m->err = "hc_multi_band_layout: no batch uploaded"; return HC_E_STATE; }
+    if (col0) std::memcpy(col0, m->col0.data(), sizeof(int32_t) * (size_t)m->n_reads);
+    if (word_off) std::memcpy(word_off, m->word_off.data(), sizeof(int64_t) * ((size_t)m->n_reads + 1));
+    if (n_words) *n_words = m->word_off[m->n_reads];
+    return HC_OK;
+}
+
+int hc_multi_score_band(hc_multi* m, uint32_t* adj, int64_t n_words, hc_ambiguous* amb, int32_t amb_cap, hc_band_stats* stats,
+                        hc_band_stats* per_device) {
+    if (!m) return HC_E_INVALID;
+    if (!m->resident) { m->err = "hc_multi_score_band: no batch uploaded"; return HC_E_STATE; }
+    if (adj && n_words < m->word_off[m->n_reads]) { m->err = "hc_multi_score_band: output buffer smaller than hc_multi_band_layout's n_words"; return HC_E_INVALID; }
+    if (amb_cap < 0 || (amb_cap > 0 && !amb)) { m->err = "hc_multi_score_band: bad near-threshold list"; return HC_E_INVALID; }
+    const int D = (int)m->ctx.size();
+    std::vector<hc_band_stats> st((size_t)D);
+    int rc = for_each_device(m, [&](int k) {
+        std::memset(&st[k], 0, sizeof(hc_band_stats));
+        const int lo = m->cuts[k] - m->first[k], hi = m->cuts[k + 1] - m->first[k];
+        const int64_t w0 = m->word_off[m->cuts[k]], w1 = m->word_off[m->cuts[k + 1]];
+        return score_band_impl(m->ctx[k], lo, hi, adj ? adj + w0 : nullptr, w1 - w0, nullptr, 0, &st[k], nullptr);
+    });
+    if (rc != HC_OK) return rc;
+    hc_band_stats tot;
+    std::memset(&tot, 0, sizeof(tot));
+    int32_t n_amb = 0;
+    for (int k = 0; k < D; ++k) {
+        tot.pairs_total += st[k].pairs_total; tot.pairs_scored += st[k].pairs_scored; tot.pairs_walked += st[k].pairs_walked;
+        tot.edges += st[k].edges; tot.sum_cc += st[k].sum_cc; tot.sum_tc += st[k].sum_tc; tot.undefined += st[k].undefined;
+        tot.ambiguous += st[k].ambiguous; tot.kernel_ms = std::max(tot.kernel_ms, st[k].kernel_ms); tot.launches += st[k].launches;
+        for (const hc_ambiguous& a : m->ctx[k]->amb_host) {             // the parts' reports, in global read indices
+            if (n_amb >= amb_cap) break;
+            amb[n_amb] = a;
+            amb[n_amb].i += m->first[k];
+            amb[n_amb].j += m->first[k];
+            n_amb++;
+        }
+    }
+    if (stats) *stats = tot;
+    if (per_device) std::memcpy(per_device, st.data(), sizeof(hc_band_stats) * (size_t)D);
     return HC_OK;
 }
 

@@ -1,7 +1,9 @@
 // Host side of libhcgpu.so: AlignmentRecord fields -> packed SoA (headers + 16-bit op records).
 // Reference for the fields: src/AlignmentRecord.h:54-77; clip-extended bounds: computeOffset /
 // computeRevOffset (src/AlignmentRecord.cpp:126-156) as used at src/NewEdgeCalculator.cpp:413-421.
+#include <climits>
 #include <cmath>
+#include <cstdint>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -344,6 +346,79 @@ void hc_packed_free(hc_packed* p) {
     if (!p) return;
     delete static_cast<hc::PackedOwner*>(p->owner);
     delete p;
+}
+
+// Rows -> parts for several GPUs: cuts at equal shares of the prefix sum of the band widths; a part's
+// halo starts at the smallest band start (col0) of its rows. col0 exactly as compute_layout() in hc_gpu.cu defines it.
+int hc_partition_rows(const int32_t* cov_first, const int32_t* cov_last, int32_t n, int32_t n_parts, int32_t* cuts, int32_t* first) {
+    if (!cov_first || !cov_last || !cuts || !first || n < 0 || n_parts < 1) {
+        hc::set_global_error("hc_partition_rows: bad argument");
+        return HC_E_INVALID;
+    }
+    std::vector<int32_t> pmax((size_t)n), col0((size_t)n);
+    int32_t run = INT32_MIN;
+    for (int r = 0; r < n; ++r) { run = std::max(run, cov_last[r]); pmax[r] = run; }
+    std::vector<int64_t> acc((size_t)n + 1, 0);
+    hc::parallel_ranges(n, 4096, [&](int k0, int k1) {
+        for (int i = k0; i < k1; ++i)
+            col0[i] = (int32_t)(std::lower_bound(pmax.begin(), pmax.begin() + i, cov_first[i]) - pmax.begin()) & ~31;
+    });
+    for (int i = 0; i < n; ++i) acc[i + 1] = acc[i] + (i - col0[i]);
+    cuts[0] = 0;
+    for (int p = 1; p < n_parts; ++p) {
+        const int64_t want = acc[n] / n_parts * p + acc[n] % n_parts * p / n_parts;
+        int32_t c = (int32_t)(std::lower_bound(acc.begin(), acc.end(), want) - acc.begin());
+        cuts[p] = std::min(std::max(c, cuts[p - 1]), n);
+    }
+    cuts[n_parts] = n;
+    for (int p = 0; p < n_parts; ++p) {
+        int32_t f = cuts[p];
+        for (int i = cuts[p]; i < cuts[p + 1]; ++i) f = std::min(f, col0[i]);
+        first[p] = f & ~31;
+    }
+    return HC_OK;
+}
+
+int hc_packed_slice(const hc_packed* p, int32_t first, int32_t end, hc_packed** out) {
+    if (!p || !out || first < 0 || end < first || end > p->n_reads) {
+        hc::set_global_error("hc_packed_slice: bad range (0 <= first <= end <= n_reads)");
+        return HC_E_INVALID;
+    }
+    *out = nullptr;
+    hc_packed* q = nullptr;
+    hc::PackedOwner* own = nullptr;
+    try {
+        q = new hc_packed(*p);
+        own = new hc::PackedOwner();
+    } catch (const std::bad_alloc&) {
+        delete q;
+        hc::set_global_error("hc_packed_slice: out of memory");
+        return HC_E_NOMEM;
+    }
+    q->owner = own;
+    const int n = end - first;
+    if (!own->hdr.alloc(sizeof(hc_read_hdr) * (size_t)std::max(n, 1))) {
+        hc_packed_free(q);
+        hc::set_global_error("hc_packed_slice: out of memory");
+        return HC_E_NOMEM;
+    }
+    hc_read_hdr* h = static_cast<hc_read_hdr*>(own->hdr.p);
+    // a read's op stream starts on a 16-byte boundary, so the slice's stream does too
+    const uint32_t base = n > 0 ? p->hdr[first].ops_off[0] : 0u;
+    const int64_t stop = end < p->n_reads ? (int64_t)p->hdr[end].ops_off[0] : p->n_ops_total;
+    hc::parallel_ranges(n, 8192, [&](int k0, int k1) {
+        for (int k = k0; k < k1; ++k) {
+            h[k] = p->hdr[first + k];
+            h[k].ops_off[0] -= base;
+            h[k].ops_off[1] -= base;
+        }
+    });
+    q->n_reads = n;
+    q->hdr = h;
+    q->ops = p->ops + base;                 // behind the slice: the next reads' records or the parent's padding (>= 64 records)
+    q->n_ops_total = n > 0 ? stop - (int64_t)base : 0;
+    *out = q;
+    return HC_OK;
 }
 
 }  // extern "C"

@@ -199,6 +199,7 @@ __global__ void __launch_bounds__(128) merge_cliques_kernel(Batch B) {
         }
         if (m == 1) {   // the reference asserts size > 1 (:213); a lone member is copied through
             for (int k = 0; k < acc.n_ops; ++k) side[0].cig[k] = acc.cig[k];
+            acc.n_seq = min(acc.n_seq, acc.n_ops);      // the slot is sized from the CIGAR length
             for (int k = 0; k < acc.n_seq; ++k) { side[0].seq[k] = acc.seq[k]; side[0].qual[k] = acc.qual[k]; }
         }
         hc_merged_info r;
@@ -235,8 +236,14 @@ int check_batch(const hc_reads* reads, int32_t n_cliques, const int64_t* member_
             const int r = members[k];
             if (r < 0 || r >= reads->n) return fail(HC_E_INVALID, "hc_merge: member index out of range");
             if (!reads->single_end[r]) return fail(HC_E_INVALID, "hc_merge_cliques_se: paired-end member (only single-end cliques are built)");
+            const int nc = reads->cig_len[2 * r], nq = reads->seq_len[2 * r];
+            if (nc < 0 || nq < 0) return fail(HC_E_INVALID, "hc_merge: negative CIGAR / sequence length");
+            const uint8_t* cg = reads->cig + reads->cig_off[2 * r];
+            int consumed = 0;
+            for (int i = 0; i < nc; ++i) consumed += (cg[i] == 'M' || cg[i] == 'I' || cg[i] == 'S');
+            if (consumed > nq) return fail(HC_E_INVALID, "hc_merge: CIGAR consumes more query bases than the read has");
             const uint8_t* q = reads->qual + reads->seq_off[2 * r];
-            for (int i = 0; i < reads->seq_len[2 * r]; ++i)
+            for (int i = 0; i < nq; ++i)
                 if (q[i] < 33 || q[i] > 126) return fail(HC_E_INVALID, "hc_merge: quality char outside 33..126");
         }
     }
@@ -269,6 +276,13 @@ int hc_merge_cliques_se(int32_t device, const hc_reads* reads, int32_t n_cliques
     if (rc != HC_OK) return rc;
     if (n_cliques == 0) return HC_OK;
     if (!out_off || !out_cig || !out_seq || !out_qual || !info) return fail(HC_E_INVALID, "hc_merge_cliques_se: null output");
+    {   // the caller's out_off must leave every clique the room hc_merge_layout gives it
+        std::vector<int64_t> want((size_t)n_cliques + 1);
+        if ((rc = hc_merge_layout(reads, n_cliques, member_off, members, want.data())) != HC_OK) return rc;
+        for (int c = 0; c < n_cliques; ++c)
+            if (out_off[c] < 0 || out_off[c + 1] - out_off[c] < want[c + 1] - want[c])
+                return fail(HC_E_INVALID, "hc_merge_cliques_se: out_off leaves a clique less room than hc_merge_layout");
+    }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
         return fail(HC_E_CUDA, "hc_merge_cliques_se: no such CUDA device (there is no CPU merging path)");

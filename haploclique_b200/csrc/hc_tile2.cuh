@@ -427,7 +427,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) score_tile2_kernel(const Ar
                     if (a.amb != nullptr && slot < (unsigned long long)a.amb_cap) {
                         hc_ambiguous am;
                         am.i = i; am.j = j; am.cc = L.cc; am.tc = L.tc; am.probM = L.probM; am.prob0 = prob0;
-                        am.score = score; am.cutoff = cutoff;
+                        am.score = score; am.cutoff = cutoff; am.edge = edge; am.edge_device = edge;
                         a.amb[slot] = am;
                     }
                 }

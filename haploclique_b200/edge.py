@@ -58,7 +58,7 @@ PAIR_RESULT_DTYPE = np.dtype([("status", np.int32), ("edge", np.int32), ("gap", 
                               ("prob0", np.float64), ("score", np.float64)], align=True)
 AMBIGUOUS_DTYPE = np.dtype([("i", np.int32), ("j", np.int32), ("cc", np.int32), ("tc", np.int32),
                             ("probM", np.float64), ("prob0", np.float64), ("score", np.float64),
-                            ("cutoff", np.float64)], align=True)
+                            ("cutoff", np.float64), ("edge", np.int32), ("edge_device", np.int32)], align=True)
 HDR_DTYPE = np.dtype([("raw", np.int32, 4), ("ext", np.int32, 4), ("ops_off", np.uint32, 2), ("n_ops", np.int32, 2),
                       ("ncov_flags", np.uint32), ("cov_first", np.int32), ("cov_last", np.int32),
                       ("seg_flags", np.uint16, 2)], align=True)
@@ -96,9 +96,23 @@ def load_library():
         L.hc_get_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.hc_quasi_score_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
         L.hc_quasi_score_band.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]
+        L.hc_partition_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
+        L.hc_packed_slice.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
+        L.hc_multi_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
+        L.hc_multi_destroy.argtypes = [C.c_void_p]
+        L.hc_multi_last_error.restype = C.c_char_p
+        L.hc_multi_last_error.argtypes = [C.c_void_p]
+        L.hc_multi_n_devices.argtypes = [C.c_void_p]
+        L.hc_multi_context.restype = C.c_void_p
+        L.hc_multi_context.argtypes = [C.c_void_p, C.c_int32]
+        L.hc_multi_set_params.argtypes = [C.c_void_p, C.c_void_p]
+        L.hc_multi_upload.argtypes = [C.c_void_p, C.c_void_p]
+        L.hc_multi_partition.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.hc_multi_band_layout.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.hc_multi_score_band.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
         L.hc_merge_layout.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
         L.hc_merge_cliques_se.argtypes = [C.c_int32, C.c_void_p, C.c_int32] + [C.c_void_p] * 8
-        assert C.sizeof(_BandStats) == 72 and HDR_DTYPE.itemsize == 64
+        assert C.sizeof(_BandStats) == 72 and HDR_DTYPE.itemsize == 64 and AMBIGUOUS_DTYPE.itemsize == 56
         _lib = L
     return _lib
 
@@ -242,8 +256,11 @@ class NewEdgeCalculator(EdgeCalculator):
                  frameshift_merge: bool = False, simpson_map: Optional[Dict[int, float]] = None,
                  edge_quasi_cutoff_single: float = 0.95, overlap_single: float = 0.6,
                  edge_quasi_cutoff_mixed: float = 0.97, maxPosition: int = 0, noProb0: bool = False,
-                 device: int = 0, ambiguity_rel_tol: float = 1e-12):
+                 device: int = 0, ambiguity_rel_tol: float = 1e-12, devices: Optional[Sequence[int]] = None):
         self.L = load_library()
+        self._multi = None
+        self._ctx = None
+        self._aux = None
         self.Q, self.FRAMESHIFT_MERGE = Q, frameshift_merge       # stored, unused by the scorer (as in the reference)
         self._simpson = None
         if simpson_map:
@@ -254,16 +271,33 @@ class NewEdgeCalculator(EdgeCalculator):
                             overlap_single, int(bool(noProb0)), 0 if self._simpson is None else self._simpson.shape[0],
                             None if self._simpson is None else self._simpson.ctypes.data, device, 0, ambiguity_rel_tol)
         self._ctx = C.c_void_p()
-        rc = self.L.hc_create(C.byref(self._par), C.byref(self._ctx))
-        if rc != HC_OK:
-            raise HcError("hc_create failed (%d): %s" % (rc, self.L.hc_last_error(None).decode()))
+        self.devices = None if devices is None else [int(d) for d in devices]
+        if self.devices is not None:
+            # several GPUs behind one handle (hc_multi_*): rows partitioned by pair count, halo from the covered intervals
+            dv = np.asarray(self.devices, np.int32)
+            self._multi = C.c_void_p()
+            rc = self.L.hc_multi_create(C.byref(self._par), _ptr(dv), dv.shape[0], C.byref(self._multi))
+            if rc != HC_OK:
+                self._multi = None
+                raise HcError("hc_multi_create failed (%d): %s" % (rc, self.L.hc_last_error(None).decode()))
+            self._ctx = C.c_void_p(self.L.hc_multi_context(self._multi, 0))
+        else:
+            rc = self.L.hc_create(C.byref(self._par), C.byref(self._ctx))
+            if rc != HC_OK:
+                raise HcError("hc_create failed (%d): %s" % (rc, self.L.hc_last_error(None).decode()))
         self._packed: Optional[PackedBatch] = None
         self._index: Dict[int, int] = {}
         self._adj: Optional[Adjacency] = None
 
     def __del__(self):
         try:
-            if self._ctx:
+            if self._aux:
+                self.L.hc_destroy(self._aux)
+                self._aux = None
+            if self._multi:
+                self.L.hc_multi_destroy(self._multi)
+                self._multi, self._ctx = None, None
+            elif self._ctx:
                 self.L.hc_destroy(self._ctx)
                 self._ctx = None
         except Exception:
@@ -271,12 +305,29 @@ class NewEdgeCalculator(EdgeCalculator):
 
     def _check(self, rc: int, what: str):
         if rc != HC_OK:
-            raise HcError("%s failed (%d): %s" % (what, rc, self.L.hc_last_error(self._ctx).decode()))
+            msg = self.L.hc_multi_last_error(self._multi) if (self._multi and what.startswith("hc_multi")) else self.L.hc_last_error(self._ctx)
+            raise HcError("%s failed (%d): %s" % (what, rc, msg.decode()))
+
+    def contexts(self):
+        """The per-device contexts (one unless `devices` was given)."""
+        if self._multi:
+            return [C.c_void_p(self.L.hc_multi_context(self._multi, k)) for k in range(len(self.devices))]
+        return [self._ctx]
+
+    def partition(self):
+        """(cuts, first) of the resident batch over the devices (hc_multi_partition)."""
+        cuts = np.zeros(len(self.devices) + 1, np.int32)
+        first = np.zeros(len(self.devices), np.int32)
+        self._check(self.L.hc_multi_partition(self._multi, _ptr(cuts), _ptr(first)), "hc_multi_partition")
+        return cuts, first
 
     # -- reference interface ---------------------------------------------------------------------------
     def setOverlapCliques(self, d: float) -> None:            # src/NewEdgeCalculator.cpp:1382
         self._par.min_overlap_cliques = d
-        self._check(self.L.hc_set_params(self._ctx, C.byref(self._par)), "hc_set_params")
+        if self._multi:
+            self._check(self.L.hc_multi_set_params(self._multi, C.byref(self._par)), "hc_multi_set_params")
+        else:
+            self._check(self.L.hc_set_params(self._ctx, C.byref(self._par)), "hc_set_params")
         self._adj = None
 
     def getOverlapCliques(self) -> float:
@@ -291,19 +342,32 @@ class NewEdgeCalculator(EdgeCalculator):
         i, j = self._index.get(id(ap1)), self._index.get(id(ap2))
         if i is not None and j is not None and self._adj is not None and j < i:
             return self._adj.edge(i, j)
-        if i is not None and j is not None and self._packed is not None:
-            return bool(self.score_pairs([i], [j])["edge"][0])
-        # records outside the resident batch (the reference's unit tests call it this way)
+        if i is not None and j is not None and self._packed is not None and not self._multi:
+            return bool(self.score_pairs([i], [j])["edge"][0])     # e.g. the reversed order: scored on the resident batch
+        # records outside the resident batch (the reference's unit tests call it this way): a two-read batch on a small
+        # second context, so that the resident batch stays where it is
+        if self._aux is None:
+            self._aux = C.c_void_p()
+            par = _Params.from_buffer_copy(self._par)
+            par.device = self._par.device if self.devices is None else self.devices[0]
+            rc = self.L.hc_create(C.byref(par), C.byref(self._aux))
+            if rc != HC_OK:
+                self._aux = None
+                raise HcError("hc_create failed (%d): %s" % (rc, self.L.hc_last_error(None).decode()))
+        self.L.hc_set_params(self._aux, C.byref(self._par))
         pair = PackedBatch(ReadBatch.from_records([ap2, ap1]))
-        try:
-            self._check(self.L.hc_upload(self._ctx, pair._h), "hc_upload")
-            pi, pj = np.array([1], np.int32), np.array([0], np.int32)
-            out = np.zeros(1, PAIR_RESULT_DTYPE)
-            self._check(self.L.hc_score_pairs(self._ctx, _ptr(pi), _ptr(pj), 1, _ptr(out)), "hc_score_pairs")
-            return bool(out["edge"][0])
-        finally:
-            if self._packed is not None:
-                self._check(self.L.hc_upload(self._ctx, self._packed._h), "hc_upload")
+        rc = self.L.hc_upload(self._aux, pair._h)
+        if rc != HC_OK:
+            raise HcError("hc_upload failed (%d): %s" % (rc, self.L.hc_last_error(self._aux).decode()))
+        return bool(self._score_pair_on(self._aux, 1, 0))
+
+    def _score_pair_on(self, ctx, i: int, j: int) -> int:
+        pi, pj = np.array([i], np.int32), np.array([j], np.int32)
+        out = np.zeros(1, PAIR_RESULT_DTYPE)
+        rc = self.L.hc_score_pairs(ctx, _ptr(pi), _ptr(pj), 1, _ptr(out))
+        if rc != HC_OK:
+            raise HcError("hc_score_pairs failed (%d): %s" % (rc, self.L.hc_last_error(ctx).decode()))
+        return int(out["edge"][0])
 
     # -- batch interface (the driver hook of SURVEY.md 8(b)) -------------------------------------------
     def upload(self, reads: Union[ReadBatch, Sequence[AlignmentRecord], PackedBatch]) -> PackedBatch:
@@ -315,7 +379,10 @@ class NewEdgeCalculator(EdgeCalculator):
                 self._index = {id(r): k for k, r in enumerate(recs)}
                 reads = ReadBatch.from_records(recs)
             packed = PackedBatch(reads)
-        self._check(self.L.hc_upload(self._ctx, packed._h), "hc_upload")
+        if self._multi:
+            self._check(self.L.hc_multi_upload(self._multi, packed._h), "hc_multi_upload")
+        else:
+            self._check(self.L.hc_upload(self._ctx, packed._h), "hc_upload")
         self._packed = packed
         self._adj = None
         return packed
@@ -326,8 +393,13 @@ class NewEdgeCalculator(EdgeCalculator):
         col0 = np.zeros(max(nrows, 1), np.int32)
         off = np.zeros(nrows + 1, np.int64)
         nw = C.c_int64(0)
-        self._check(self.L.hc_band_layout(self._ctx, row_begin, row_end, _ptr(col0), _ptr(off), C.byref(nw)),
-                    "hc_band_layout")
+        if self._multi:
+            if (row_begin, row_end) != (0, self._packed.n_reads):
+                raise HcError("several devices: the band is scored as a whole (rows are cut by the library)")
+            self._check(self.L.hc_multi_band_layout(self._multi, _ptr(col0), _ptr(off), C.byref(nw)), "hc_multi_band_layout")
+        else:
+            self._check(self.L.hc_band_layout(self._ctx, row_begin, row_end, _ptr(col0), _ptr(off), C.byref(nw)),
+                        "hc_band_layout")
         return col0[:nrows], off, int(nw.value)
 
     def score_band(self, row_begin: int = 0, row_end: Optional[int] = None, out: Optional[np.ndarray] = None,
@@ -338,15 +410,22 @@ class NewEdgeCalculator(EdgeCalculator):
             out = np.zeros(max(nw, 1), np.uint32)
         amb = np.zeros(max(amb_cap, 1), AMBIGUOUS_DTYPE)
         st = _BandStats()
-        self._check(self.L.hc_score_band(self._ctx, row_begin, row_end, _ptr(out) if fetch else None, nw,
-                                         _ptr(amb) if amb_cap > 0 else None, amb_cap, C.byref(st)), "hc_score_band")
+        if self._multi:
+            per = (_BandStats * len(self.devices))()
+            self._check(self.L.hc_multi_score_band(self._multi, _ptr(out) if fetch else None, nw,
+                                                   _ptr(amb) if amb_cap > 0 else None, amb_cap, C.byref(st), per), "hc_multi_score_band")
+            self.per_device_stats = [{k: getattr(p, k) for k, _ in _BandStats._fields_} for p in per]
+        else:
+            self._check(self.L.hc_score_band(self._ctx, row_begin, row_end, _ptr(out) if fetch else None, nw,
+                                             _ptr(amb) if amb_cap > 0 else None, amb_cap, C.byref(st)), "hc_score_band")
         stats = {k: getattr(st, k) for k, _ in _BandStats._fields_}
         words = out[:nw] if fetch else np.zeros(0, np.uint32)
         return Adjacency(row_begin, row_end, col0, off, words, stats, amb[:min(int(st.ambiguous), amb_cap)].copy())
 
     def set_kernel(self, mode: int) -> None:
         """KERNEL_AUTO / KERNEL_GENERIC / KERNEL_TILED / KERNEL_TILED2 / KERNEL_STREAMED (include/hc_edge.h: hc_set_kernel)."""
-        self._check(self.L.hc_set_kernel(self._ctx, mode), "hc_set_kernel")
+        for ctx in self.contexts():
+            self._check(self.L.hc_set_kernel(ctx, mode), "hc_set_kernel")
 
     def last_kernel(self) -> int:
         return int(self.L.hc_last_kernel(self._ctx))
@@ -447,6 +526,14 @@ class QuasispeciesEdgeCalculator(NewEdgeCalculator):
     def score_band_detail(self, row_begin: int = 0, row_end: Optional[int] = None):
         raise HcError("QuasispeciesEdgeCalculator: per-slot detail comes from score_pairs")
 
+    def _score_pair_on(self, ctx, i: int, j: int) -> int:
+        pi, pj = np.array([i], np.int32), np.array([j], np.int32)
+        out = np.zeros(1, QUASI_RESULT_DTYPE)
+        rc = self.L.hc_quasi_score_pairs(ctx, C.byref(self._qpar), _ptr(pi), _ptr(pj), 1, _ptr(out))
+        if rc != HC_OK:
+            raise HcError("hc_quasi_score_pairs failed (%d): %s" % (rc, self.L.hc_last_error(ctx).decode()))
+        return int(out["edge"][0])
+
     def score_pairs(self, pi, pj) -> np.ndarray:
         pi = np.ascontiguousarray(pi, np.int32)
         pj = np.ascontiguousarray(pj, np.int32)
@@ -454,6 +541,18 @@ class QuasispeciesEdgeCalculator(NewEdgeCalculator):
         self._check(self.L.hc_quasi_score_pairs(self._ctx, C.byref(self._qpar), _ptr(pi), _ptr(pj), pi.shape[0], _ptr(out)),
                     "hc_quasi_score_pairs")
         return out
+
+
+def partition_rows(batch: ReadBatch, n_parts: int):
+    """hc_partition_rows: (cuts, first) -- part p scores rows [cuts[p], cuts[p+1]) and holds reads [first[p], cuts[p+1])."""
+    L = load_library()
+    cuts = np.zeros(n_parts + 1, np.int32)
+    first = np.zeros(n_parts, np.int32)
+    cf, cl = np.ascontiguousarray(batch.cov_first, np.int32), np.ascontiguousarray(batch.cov_last, np.int32)
+    rc = L.hc_partition_rows(_ptr(cf), _ptr(cl), batch.n, n_parts, _ptr(cuts), _ptr(first))
+    if rc != HC_OK:
+        raise HcError("hc_partition_rows failed (%d): %s" % (rc, L.hc_last_error(None).decode()))
+    return cuts, first
 
 
 def pack_only(batch: ReadBatch) -> PackedBatch:

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define HC_ABI_VERSION 1
+#define HC_ABI_VERSION 2
 
 enum {
     HC_OK = 0,
@@ -130,11 +130,17 @@ typedef struct {
     double score;                       /* prob*potence (:1139); NaN when not reached */
 } hc_pair_result;
 
+/* A pair whose score lies within ambiguity_rel_tol of the threshold. The device's log10 is not glibc's, so such a pair
+ * is re-decided on the host exactly as similarityCriterion does (src/NewEdgeCalculator.cpp:1127-1140: std::log10,
+ * reciprocal, multiply, >=) from the bit-exact (probM, prob0, cc, tc); the adjacency bit the caller receives is the
+ * host's decision. This list is the report of those pairs. */
 typedef struct {
     int32_t i, j;                       /* ap1 = read i (later arrival), ap2 = read j */
     int32_t cc, tc;
     double probM, prob0;
-    double score, cutoff;
+    double score, cutoff;               /* score as re-computed on the host with std::log10; cutoff = log10(cutoff) */
+    int32_t edge;                       /* the host's decision = the adjacency bit */
+    int32_t edge_device;                /* what the device had decided */
 } hc_ambiguous;
 
 /* Totals of one hc_score_band call. */
@@ -145,9 +151,11 @@ typedef struct {
     int64_t edges;
     int64_t sum_cc, sum_tc;             /* column steps */
     int64_t undefined;
-    int64_t ambiguous;                  /* number found (may exceed the capacity given) */
-    float kernel_ms;                    /* device time of the scoring kernel, CUDA events on its stream */
-    int32_t launches;
+    int64_t ambiguous;                  /* near-threshold pairs found and re-decided on the host (may exceed the capacity
+                                           of the caller's list; all of them are re-decided) */
+    float kernel_ms;                    /* device time from the clearing of the adjacency words to the end of the last
+                                           scoring kernel, CUDA events on the compute stream */
+    int32_t launches;                   /* scoring kernels launched (one per row window) */
 } hc_band_stats;
 
 typedef struct hc_ctx hc_ctx;
@@ -177,7 +185,9 @@ int hc_band_layout(hc_ctx* ctx, int32_t row_begin, int32_t row_end, int32_t* col
 /* Scores every ordered pair (i, j<i) of rows [row_begin,row_end) that lies in the band and writes the
  * adjacency bits (bit (j-col0[i]) of row i = edgeBetween(read i, read j)) to host memory `adj`
  * (n_words words, see hc_band_layout; may be NULL to keep the result on the device only).
- * amb/amb_cap: optional list of pairs whose score is within the tolerance of the threshold. */
+ * The rows are scored in windows (one kernel launch each); the words of a finished window travel to `adj` on a second
+ * stream while the next window is scored. Pairs within ambiguity_rel_tol of the threshold are re-decided on the host with
+ * std::log10 (see hc_ambiguous) and their bits patched, in `adj` and on the device; amb/amb_cap: optional report. */
 int hc_score_band(hc_ctx* ctx, int32_t row_begin, int32_t row_end, uint32_t* adj, int64_t n_words,
                   hc_ambiguous* amb, int32_t amb_cap, hc_band_stats* stats);
 
@@ -243,6 +253,41 @@ int hc_quasi_score_pairs(hc_ctx* ctx, const hc_quasi_params* params, const int32
  * covered intervals, for which computeOverlap returns 0: no edge as long as the cutoffs are > 0 (required here). */
 int hc_quasi_score_band(hc_ctx* ctx, const hc_quasi_params* params, int32_t row_begin, int32_t row_end, uint32_t* adj,
                         int64_t n_words, hc_band_stats* stats);
+
+/* ---- Several GPUs behind one handle ----------------------------------------------------------------
+ * The band shards by rows with no exchange step: a pair depends on its two reads only. hc_partition_rows cuts the
+ * position-sorted batch into n_parts consecutive row ranges balanced by the prefix sum of the band widths (= ordered pairs
+ * inside the band), and gives for each part the first read it has to hold: its left halo, i.e. every earlier read whose
+ * covered interval can reach one of its rows (from the running maximum of cov_last, not a constant). When everything
+ * overlaps (deep amplicons, super-read rounds) the halo reaches read 0 and the parts become equal-area row blocks of the
+ * replicated set. first[p] is a multiple of 32, so part p's local band layout is the global one shifted by first[p] and
+ * its adjacency words are the global words [word_off[cuts[p]], word_off[cuts[p+1]]) unchanged.
+ *   cov_first / cov_last: per read, as in hc_reads.   cuts: n_parts+1 entries, cuts[0] = 0, cuts[n_parts] = n_reads. */
+int hc_partition_rows(const int32_t* cov_first, const int32_t* cov_last, int32_t n_reads, int32_t n_parts,
+                      int32_t* cuts, int32_t* first);
+
+/* Reads [first, end) of a packed batch as a batch of their own (headers copied and re-based, op records shared with
+ * `p`, which must outlive the slice). Free with hc_packed_free. */
+int hc_packed_slice(const hc_packed* p, int32_t first, int32_t end, hc_packed** out);
+
+/* One host process driving n_devices GPUs (one context, two streams and one host thread per device; the same ordinal may
+ * be listed more than once). hc_multi_upload partitions the batch with hc_partition_rows and uploads each part with its
+ * halo; hc_multi_score_band scores all parts concurrently, every device copying its rows' words straight into the
+ * caller's `adj` buffer (hc_multi_band_layout's layout = hc_band_layout's of the whole batch): the final gather is the
+ * set of D2H copies, there is no collective. params->device is ignored. stats: sums over the devices, kernel_ms = the
+ * slowest device's. per_device (optional, n_devices entries): each device's own stats. */
+typedef struct hc_multi hc_multi;
+int hc_multi_create(const hc_params* params, const int32_t* devices, int32_t n_devices, hc_multi** out);
+void hc_multi_destroy(hc_multi* m);
+const char* hc_multi_last_error(const hc_multi* m);
+int hc_multi_n_devices(const hc_multi* m);
+hc_ctx* hc_multi_context(hc_multi* m, int32_t k);            /* device k's context (hc_set_kernel, hc_l2_flush, ...) */
+int hc_multi_set_params(hc_multi* m, const hc_params* params);
+int hc_multi_upload(hc_multi* m, const hc_packed* p);
+int hc_multi_partition(const hc_multi* m, int32_t* cuts, int32_t* first);     /* the partition of the resident batch */
+int hc_multi_band_layout(hc_multi* m, int32_t* col0, int64_t* word_off, int64_t* n_words);
+int hc_multi_score_band(hc_multi* m, uint32_t* adj, int64_t n_words, hc_ambiguous* amb, int32_t amb_cap,
+                        hc_band_stats* stats, hc_band_stats* per_device);
 
 /* Replaces the scalar scoring parameters (cutoffs, min overlaps, no_prob0, tolerance) of a live context;
  * the allele-frequency map and the device stay as given to hc_create. Mirrors

@@ -62,13 +62,12 @@ void GpuEdgeCalculator::flatten(const std::vector<const AlignmentRecord*>& reads
 
 void GpuEdgeCalculator::fail(const char* what, int rc) const {
     throw std::runtime_error(std::string("GpuEdgeCalculator: ") + what + " failed (" + std::to_string(rc) + "): " +
-                             hc_last_error(ctx_));
+                             hc_multi_last_error(multi_));
 }
 
-GpuEdgeCalculator::GpuEdgeCalculator(double, double edge_quasi_cutoff, double overlap, bool, std::unordered_map<int, double>& simpson_map,
-                                     double edge_quasi_cutoff_single, double overlap_single, double edge_quasi_cutoff_mixed,
-                                     unsigned int maxPosition, bool noProb0, int device)
-    : ctx_(nullptr), resident_(nullptr), resident_dirty_(false) {
+void GpuEdgeCalculator::init(double edge_quasi_cutoff, double overlap, std::unordered_map<int, double>& simpson_map,
+                             double edge_quasi_cutoff_single, double overlap_single, double edge_quasi_cutoff_mixed,
+                             unsigned int maxPosition, bool noProb0, const std::vector<int>& devices) {
     std::memset(&par_, 0, sizeof par_);
     std::memset(&stats_, 0, sizeof stats_);
     par_.edge_quasi_cutoff_cliques = edge_quasi_cutoff;
@@ -77,7 +76,8 @@ GpuEdgeCalculator::GpuEdgeCalculator(double, double edge_quasi_cutoff, double ov
     par_.min_overlap_cliques = overlap;
     par_.min_overlap_single = overlap_single;
     par_.no_prob0 = noProb0 ? 1 : 0;
-    par_.device = device;
+    devices_ = devices.empty() ? std::vector<int>(1, 0) : devices;
+    par_.device = devices_[0];
     if (!simpson_map.empty()) {                            // SIMPSON_MAP.resize(maxPosition+1) (src/NewEdgeCalculator.cpp:85-88)
         simpson_.assign((size_t)maxPosition + 1, 0.0);
         for (const auto& kv : simpson_map)
@@ -85,13 +85,31 @@ GpuEdgeCalculator::GpuEdgeCalculator(double, double edge_quasi_cutoff, double ov
         par_.simpson = simpson_.data();
         par_.simpson_len = (int32_t)simpson_.size();
     }
-    const int rc = hc_create(&par_, &ctx_);
-    if (rc != HC_OK) throw std::runtime_error(std::string("GpuEdgeCalculator: hc_create failed: ") + hc_last_error(nullptr));
+    std::vector<int32_t> dv(devices_.begin(), devices_.end());
+    const int rc = hc_multi_create(&par_, dv.data(), (int32_t)dv.size(), &multi_);
+    if (rc != HC_OK) throw std::runtime_error(std::string("GpuEdgeCalculator: hc_multi_create failed: ") + hc_last_error(nullptr));
+}
+
+GpuEdgeCalculator::GpuEdgeCalculator(double, double edge_quasi_cutoff, double overlap, bool, std::unordered_map<int, double>& simpson_map,
+                                     double edge_quasi_cutoff_single, double overlap_single, double edge_quasi_cutoff_mixed,
+                                     unsigned int maxPosition, bool noProb0, int device)
+    : multi_(nullptr), aux_(nullptr), resident_(nullptr) {
+    init(edge_quasi_cutoff, overlap, simpson_map, edge_quasi_cutoff_single, overlap_single, edge_quasi_cutoff_mixed, maxPosition,
+         noProb0, std::vector<int>(1, device));
+}
+
+GpuEdgeCalculator::GpuEdgeCalculator(double, double edge_quasi_cutoff, double overlap, bool, std::unordered_map<int, double>& simpson_map,
+                                     double edge_quasi_cutoff_single, double overlap_single, double edge_quasi_cutoff_mixed,
+                                     unsigned int maxPosition, bool noProb0, const std::vector<int>& devices)
+    : multi_(nullptr), aux_(nullptr), resident_(nullptr) {
+    init(edge_quasi_cutoff, overlap, simpson_map, edge_quasi_cutoff_single, overlap_single, edge_quasi_cutoff_mixed, maxPosition,
+         noProb0, devices);
 }
 
 GpuEdgeCalculator::~GpuEdgeCalculator() {
+    hc_multi_destroy(multi_);
+    hc_destroy(aux_);
     hc_packed_free(resident_);
-    hc_destroy(ctx_);
 }
 
 void GpuEdgeCalculator::scoreBatch(const std::deque<AlignmentRecord*>& reads) {
@@ -106,31 +124,42 @@ void GpuEdgeCalculator::scoreBatch(const std::vector<const AlignmentRecord*>& re
     Flat f;
     flatten(reads, f);
     const hc_reads view = f.view();
-    hc_packed_free(resident_);
-    resident_ = nullptr;
-    int rc = hc_pack(&view, &resident_);
+    hc_packed* packed = nullptr;
+    int rc = hc_pack(&view, &packed);
     if (rc != HC_OK) throw std::runtime_error(std::string("GpuEdgeCalculator: hc_pack failed: ") + hc_last_error(nullptr));
-    if ((rc = hc_upload(ctx_, resident_)) != HC_OK) fail("hc_upload", rc);
-    resident_dirty_ = false;
+    rc = hc_multi_upload(multi_, packed);
+    hc_packed_free(resident_);                             // the previous batch's slices are gone with the upload
+    resident_ = packed;
+    if (rc != HC_OK) fail("hc_multi_upload", rc);
     const int n = (int)reads.size();
     col0_.assign((size_t)std::max(n, 1), 0);
     word_off_.assign((size_t)n + 1, 0);
     int64_t n_words = 0;
-    if ((rc = hc_band_layout(ctx_, 0, n, col0_.data(), word_off_.data(), &n_words)) != HC_OK) fail("hc_band_layout", rc);
+    if ((rc = hc_multi_band_layout(multi_, col0_.data(), word_off_.data(), &n_words)) != HC_OK) fail("hc_multi_band_layout", rc);
     words_.assign((size_t)std::max<int64_t>(n_words, 1), 0u);
-    if ((rc = scoreResident(n, words_.data(), n_words, &stats_)) != HC_OK) fail("hc_score_band", rc);
+    near_.clear();
+    if ((rc = scoreResident(words_.data(), n_words, &stats_)) != HC_OK) fail("hc_multi_score_band", rc);
 }
 
-int GpuEdgeCalculator::scoreResident(int n, uint32_t* words, int64_t n_words, hc_band_stats* stats) {
-    return hc_score_band(ctx_, 0, n, words, n_words, nullptr, 0, stats);
+int GpuEdgeCalculator::scoreResident(uint32_t* words, int64_t n_words, hc_band_stats* stats) {
+    // near-threshold pairs come back decided by std::log10 on the host (the bits in `words` are final); keep the report
+    near_.assign(1024, hc_ambiguous());
+    const int rc = hc_multi_score_band(multi_, words, n_words, near_.data(), (int32_t)near_.size(), stats, nullptr);
+    near_.resize(rc == HC_OK ? (size_t)std::min<int64_t>(stats->ambiguous, (int64_t)near_.size()) : 0);
+    return rc;
 }
 
-int GpuEdgeCalculator::scoreResidentPair(int i, int j, bool* edge) const {
+int GpuEdgeCalculator::scorePairOn(hc_ctx* ctx, int i, int j, bool* edge) const {
     hc_pair_result res;
     const int32_t pi = i, pj = j;
-    const int rc = hc_score_pairs(ctx_, &pi, &pj, 1, &res);
+    const int rc = hc_score_pairs(ctx, &pi, &pj, 1, &res);
     if (rc == HC_OK) *edge = res.edge != 0;
     return rc;
+}
+
+int GpuEdgeCalculator::indexOf(const AlignmentRecord& ap) const {
+    const auto it = index_.find(&ap);
+    return it == index_.end() ? -1 : it->second;
 }
 
 bool GpuEdgeCalculator::edgeBetween(const AlignmentRecord& ap1, const AlignmentRecord& ap2) const {
@@ -141,7 +170,12 @@ bool GpuEdgeCalculator::edgeBetween(const AlignmentRecord& ap1, const AlignmentR
         const int rel = j - col0_[i];
         return (words_[(size_t)word_off_[i] + (rel >> 5)] >> (rel & 31)) & 1u;
     }
-    // any other two records: a two-read batch, ap2 first (the earlier arrival), scored on the device
+    // any other two records: a two-read batch, ap2 first (the earlier arrival), scored on a small second context
+    if (aux_ == nullptr) {
+        const int rc = hc_create(&par_, &aux_);
+        if (rc != HC_OK) throw std::runtime_error(std::string("GpuEdgeCalculator: hc_create failed: ") + hc_last_error(nullptr));
+    }
+    hc_set_params(aux_, &par_);
     std::vector<const AlignmentRecord*> two;
     two.push_back(&ap2);
     two.push_back(&ap1);
@@ -151,15 +185,12 @@ bool GpuEdgeCalculator::edgeBetween(const AlignmentRecord& ap1, const AlignmentR
     hc_packed* pk = nullptr;
     int rc = hc_pack(&view, &pk);
     if (rc != HC_OK) throw std::runtime_error(std::string("GpuEdgeCalculator: hc_pack failed: ") + hc_last_error(nullptr));
-    rc = hc_upload(ctx_, pk);
+    rc = hc_upload(aux_, pk);
     bool edge = false;
-    if (rc == HC_OK) rc = scoreResidentPair(1, 0, &edge);
+    if (rc == HC_OK) rc = scorePairOn(aux_, 1, 0, &edge);
     hc_packed_free(pk);
-    if (resident_ != nullptr) {                            // put the scored batch back for later pair queries
-        const int rc2 = hc_upload(ctx_, resident_);
-        if (rc2 != HC_OK) fail("hc_upload", rc2);
-    }
-    if (rc != HC_OK) fail("hc_score_pairs", rc);
+    if (rc != HC_OK)
+        throw std::runtime_error(std::string("GpuEdgeCalculator: scoring a pair failed (") + std::to_string(rc) + "): " + hc_last_error(aux_));
     return edge;
 }
 
@@ -183,8 +214,8 @@ void GpuEdgeCalculator::getPartnerLengthRange(const AlignmentRecord&, unsigned i
 
 void GpuEdgeCalculator::setOverlapCliques(double d) {      // NewEdgeCalculator::setOverlapCliques (src/NewEdgeCalculator.cpp:1382)
     par_.min_overlap_cliques = d;
-    const int rc = hc_set_params(ctx_, &par_);
-    if (rc != HC_OK) fail("hc_set_params", rc);
+    const int rc = hc_multi_set_params(multi_, &par_);
+    if (rc != HC_OK) fail("hc_multi_set_params", rc);
 }
 
 // ---- QuasispeciesEdgeCalculator behind the same binding -------------------------------------------------------------
@@ -209,14 +240,36 @@ bool GpuQuasispeciesEdgeCalculator::edgeBetween(const AlignmentRecord& ap1, cons
     return GpuEdgeCalculator::edgeBetween(ap1, ap2);
 }
 
-int GpuQuasispeciesEdgeCalculator::scoreResident(int n, uint32_t* words, int64_t n_words, hc_band_stats* stats) {
-    return hc_quasi_score_band(context(), &qpar_, 0, n, words, n_words, stats);
+int GpuQuasispeciesEdgeCalculator::scoreResident(uint32_t* words, int64_t n_words, hc_band_stats* stats) {
+    // the older scorer runs on the first device of the handle (it is dead code in the reference's CLI)
+    if (hc_multi_n_devices(handle()) != 1) throw std::runtime_error("GpuQuasispeciesEdgeCalculator: one device only");
+    return hc_quasi_score_band(hc_multi_context(handle(), 0), &qpar_, 0, batchSize(), words, n_words, stats);
 }
 
-int GpuQuasispeciesEdgeCalculator::scoreResidentPair(int i, int j, bool* edge) const {
+int GpuQuasispeciesEdgeCalculator::scorePairOn(hc_ctx* ctx, int i, int j, bool* edge) const {
     hc_quasi_result res;
     const int32_t pi = i, pj = j;
-    const int rc = hc_quasi_score_pairs(context(), &qpar_, &pi, &pj, 1, &res);
+    const int rc = hc_quasi_score_pairs(ctx, &qpar_, &pi, &pj, 1, &res);
     if (rc == HC_OK) *edge = res.edge != 0;
     return rc;
+}
+
+void GpuQuasispeciesEdgeCalculator::neighbours(const AlignmentRecord& ap, std::vector<const AlignmentRecord*>& out) const {
+    GpuEdgeCalculator::neighbours(ap, out);
+    const int i = indexOf(ap);
+    if (i <= 0) return;
+    // the same-name shortcut (:56): an earlier read of the same name is adjacent whatever its score
+    const std::string name = ap.getName();
+    std::vector<const AlignmentRecord*> merged;
+    size_t k = 0;
+    bool any = false;
+    for (int j = 0; j < i; ++j) {
+        const AlignmentRecord* r = recordAt(j);
+        const bool listed = k < out.size() && out[k] == r;
+        if (listed) k++;
+        const bool same = !listed && r->getName().compare(name) == 0;
+        any |= same;
+        if (listed || same) merged.push_back(r);
+    }
+    if (any) out.swap(merged);
 }

@@ -385,3 +385,105 @@ def test_super_read_round_with_an_allele_frequency_map():
     assert calc.last_kernel() == edge.KERNEL_STREAMED
     det, orc = _tiled_detail_vs_oracle(b, kw, "C5-simpson", edge.KERNEL_STREAMED)
     assert int((orc["tc"] > 1000).sum()) > 500
+
+
+# ---- round 2: C4-shaped input, near-threshold pairs, shared context ------------------------------------------------
+@pytest.mark.parametrize("kernel", TILED_KERNELS)
+def test_C4_shaped_amplicon_every_band_slot(kernel):
+    """BASELINE configs[3] at a size the oracle walks: 1.5 kb amplicon, 2x150 reads, nearly every pair overlaps (dense
+    tiles, loops of ~100 columns). Every band slot of every band kernel against the oracle, with and without prob0."""
+    cfg = {k: v for k, v in synth.CONFIGS["C4"].items() if k != "n_frag"}
+    b = synth.quasispecies(1500, seed=44, **cfg)
+    assert 0.2 < b.single_end.mean() < 0.8                        # merged mates and true pairs both present
+    kw = dict(noProb0=True, maxPosition=b.max_position() + 10)
+    det, orc = _tiled_detail_vs_oracle(b, kw, "C4-shape", kernel)
+    n_pairs = b.n * (b.n - 1) // 2
+    assert int((orc["status"] >= 1).sum()) > 0.9 * n_pairs        # dense: the band is the whole triangle
+    assert int(orc["edge"].sum()) > 20_000 and set(np.unique(orc["layout"])) >= {100, 200, 300, 400}
+    kw["noProb0"] = False
+    _tiled_detail_vs_oracle(b, kw, "C4-shape-prob0", kernel)
+
+
+def test_near_threshold_pairs_are_decided_by_glibc_log10():
+    """The device's log10 is not glibc's. Pairs whose score is within ambiguity_rel_tol of the threshold are listed by the
+    kernel and re-decided on the host exactly as similarityCriterion does (src/NewEdgeCalculator.cpp:1127-1140). Here the
+    cutoff is placed ON the score of known pairs (cutoff = 10**score), so those pairs sit inside the band of doubt; the
+    adjacency must be the oracle's (host libm) for every one of them, through every band kernel and the pair list."""
+    b = synth.quasispecies(500, genome_len=1200, seed=9)
+    base = dict(noProb0=True, maxPosition=b.max_position() + 10)
+    calc0 = edge.NewEdgeCalculator(**base)
+    calc0.upload(b)
+    pi, pj = common.tri_pairs(b.n)
+    ref = calc0.score_pairs(pi, pj)
+    ok = (ref["status"] == 2) & (ref["gap"] == 0) & np.isfinite(ref["score"]) & (ref["score"] < -1e-4)
+    assert ok.sum() > 1000
+    scores = np.unique(ref["score"][ok])
+    rng = np.random.default_rng(4)
+    listed = decided = 0
+    for s in rng.choice(scores, 12, replace=False):
+        kw = dict(base, edge_quasi_cutoff_single=float(10.0 ** s))
+        O = pyoracle.Oracle(b, **kw)
+        edges, e = O.all_pairs(detail=False)
+        for mode in (edge.KERNEL_TILED2, edge.KERNEL_TILED, edge.KERNEL_STREAMED, edge.KERNEL_GENERIC):
+            calc = edge.NewEdgeCalculator(**kw)
+            calc.upload(b)
+            calc.set_kernel(mode)
+            adj = calc.score_band(amb_cap=64)
+            assert adj.stats["ambiguous"] >= 1 and adj.ambiguous.shape[0] == adj.stats["ambiguous"]
+            ai, aj = adj.edges()
+            assert adj.count() == edges == adj.stats["edges"]
+            assert (ai == pi[e == 1]).all() and (aj == pj[e == 1]).all()
+            for a in adj.ambiguous:                               # the report carries the host's decision
+                k = int(a["i"]) * (int(a["i"]) - 1) // 2 + int(a["j"])
+                assert a["edge"] == e[k] and abs(a["score"] - a["cutoff"]) <= 1e-12 * abs(a["cutoff"])
+                decided += int(a["edge"] != a["edge_device"])
+            listed += adj.ambiguous.shape[0]
+        dev = calc.score_pairs(pi, pj)                            # pair list: same rule
+        assert (dev["edge"] == e).all() and int(dev["ambiguous"].sum()) >= 1
+    assert listed >= 48
+    print("near-threshold pairs listed: %d, decided differently by the host: %d" % (listed, decided))
+
+
+def test_wide_tolerance_lists_more_pairs_than_the_default_capacity():
+    """A wide tolerance (1e-2) puts thousands of pairs into the report: the device list grows and the pass is repeated;
+    every listed pair is still decided by the host rule, so the adjacency is unchanged."""
+    b = synth.quasispecies(1200, genome_len=1500, seed=10)
+    kw = dict(noProb0=True, maxPosition=b.max_position() + 10, edge_quasi_cutoff_single=0.97)
+    tight = edge.NewEdgeCalculator(**kw)
+    wide = edge.NewEdgeCalculator(ambiguity_rel_tol=0.5, **kw)
+    a0 = tight.scoreBatch(b)
+    wide.upload(b)
+    a1 = wide.score_band(amb_cap=100)
+    assert a1.stats["ambiguous"] > 4096 and a1.ambiguous.shape[0] == 100
+    assert (a1.words == a0.words).all() and a1.stats["edges"] == a0.stats["edges"]
+
+
+def test_pair_list_and_quasi_pair_list_share_one_context():
+    """hc_score_pairs and hc_quasi_score_pairs interleaved on ONE context with growing pair counts: every device buffer
+    has its own capacity (round-1 advice: the pair-list result buffer used to trust a capacity the quasi call had grown)."""
+    import ctypes as C
+    b = synth.quasispecies(700, genome_len=1500, seed=12)
+    kw = dict(noProb0=True, maxPosition=b.max_position() + 10)
+    calc = edge.NewEdgeCalculator(**kw)
+    calc.upload(b)
+    L, ctx = calc.L, calc._ctx
+    qpar = edge._QuasiParams(0.99, 0.97, 0.95, 0.9, 0.6, 0, 0, 1e-12)
+    pi, pj = common.tri_pairs(b.n)
+    O = pyoracle.Oracle(b, **kw)
+
+    def new_pairs(n):
+        out = np.zeros(n, edge.PAIR_RESULT_DTYPE)
+        assert L.hc_score_pairs(ctx, edge._ptr(pi[:n]), edge._ptr(pj[:n]), n, edge._ptr(out)) == 0
+        common.assert_pairs_equal(out, O.pairs(pi[:n], pj[:n]), "shared-ctx %d" % n)
+
+    def quasi_pairs(n):
+        out = np.zeros(n, edge.QUASI_RESULT_DTYPE)
+        assert L.hc_quasi_score_pairs(ctx, C.byref(qpar), edge._ptr(pi[:n]), edge._ptr(pj[:n]), n, edge._ptr(out)) == 0
+        return out
+
+    new_pairs(100)
+    q1 = quasi_pairs(100_000)
+    new_pairs(50_000)
+    q2 = quasi_pairs(200_000)
+    new_pairs(pi.shape[0])
+    assert (q2[:100_000]["q"].view(np.uint64) == q1["q"].view(np.uint64)).all()

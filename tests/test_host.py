@@ -22,13 +22,13 @@ def test_library_exports_every_declared_symbol():
     L = edge.load_library()
     for n in sorted(names):
         assert hasattr(L, n), "libhcgpu.so does not export " + n
-    assert L.hc_abi_version() == 1
+    assert L.hc_abi_version() == 2
 
 
 def test_struct_sizes_match_header():
     assert edge.HDR_DTYPE.itemsize == 64
     assert edge.PAIR_RESULT_DTYPE.itemsize == 48
-    assert edge.AMBIGUOUS_DTYPE.itemsize == 48
+    assert edge.AMBIGUOUS_DTYPE.itemsize == 56
 
 
 def _python_pack(b: ReadBatch, qual_chars: bytes):

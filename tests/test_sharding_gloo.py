@@ -1,7 +1,7 @@
-"""CPU, world_size 2 over gloo: the host-side sharding logic of bench.py (genome-position windows + left halo).
-Every rank builds its window of the same seeded read set; the rows it owns partition the read set and the pairs that
-pass the reference's first reject (covered intervals intersect) add up to the unsharded count -- i.e. the halo is
-wide enough and no pair is scored twice. No GPU, no scoring: only the partitioning."""
+"""CPU, world_size 2 over gloo: the host-side sharding logic (hc_partition_rows through bench.shard, no GPU, no
+scoring). Every rank takes its part of the same seeded host read set; the rows the ranks own partition the read set, and
+the pairs that pass the reference's first reject (covered intervals intersect) add up to the unsharded count -- i.e. the
+halo the library derives from the covered intervals is wide enough and no pair is scored twice."""
 import os
 import sys
 
@@ -28,7 +28,8 @@ def _worker(rank, world, port, out, workload="C3", n_frag=N_FRAG):
     import bench
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    local, row_begin, cfg = bench.make_workload(workload, n_frag, rank, world)
+    full, _ = bench.generate(workload, n_frag)
+    local, row_begin, first = bench.shard(full, rank, world)
     t = torch.tensor([local.n - row_begin, _band_pairs(local, row_begin)], dtype=torch.int64)
     dist.all_reduce(t, op=dist.ReduceOp.SUM)
     if rank == 0:
@@ -36,47 +37,89 @@ def _worker(rank, world, port, out, workload="C3", n_frag=N_FRAG):
     dist.destroy_process_group()
 
 
+def _run(world, workload, n_frag, port):
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, out, workload, n_frag)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = out.get(timeout=240)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    return got
+
+
 @pytest.mark.timeout(300)
 def test_position_windows_partition_rows_and_pairs():
     sys.path.insert(0, ROOT)
     import bench
-    full, rb, _ = bench.make_workload("C3", N_FRAG, 0, 1)
-    assert rb == 0
+    from haploclique_b200 import edge
+    full, _ = bench.generate("C3", N_FRAG)
     want = [full.n, _band_pairs(full, 0)]
-    ctx = mp.get_context("spawn")
-    out = ctx.Queue()
-    port = 29600 + os.getpid() % 300
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, out)) for r in range(2)]
-    for p in procs:
-        p.start()
-    got = out.get(timeout=240)
-    for p in procs:
-        p.join(timeout=60)
-        assert p.exitcode == 0
-    assert got == want
+    cuts, first = edge.partition_rows(full, 2)
+    assert cuts[0] == 0 and cuts[2] == full.n and first[0] == 0 and 0 < first[1] < cuts[1] and first[1] % 32 == 0
+    # the halo reaches every earlier read that can overlap a row of the part, and not much more
+    reach = min(int(np.flatnonzero(full.cov_last[:i] >= full.cov_first[i])[0]) for i in range(int(cuts[1]), min(int(cuts[1]) + 50, full.n)))
+    assert first[1] <= reach
+    assert got_close(first[1], reach, 64)
+    assert _run(2, "C3", N_FRAG, 29600 + os.getpid() % 300) == want
+
+
+def got_close(a, b, tol):
+    return abs(int(a) - int(b)) <= tol
 
 
 @pytest.mark.timeout(300)
 def test_super_read_round_row_blocks_partition_rows_and_pairs():
-    """C5 (every read overlaps most others): no position windows -- each rank holds the reads up to the end of its block
-    of rows; the blocks partition the rows, have about equal pair area, and their scored pairs add up."""
+    """C5 (every read overlaps most others): the halo reaches read 0, so each rank holds the reads up to the end of its
+    block of rows; the blocks partition the rows, have about equal pair area, and their scored pairs add up."""
     sys.path.insert(0, ROOT)
     import bench
-    full, rb, _ = bench.make_workload("C5", 600, 0, 1)
-    assert rb == 0 and full.n == 600
+    full, _ = bench.generate("C5", 600)
+    assert full.n == 600
     want = [full.n, _band_pairs(full, 0)]
-    l0, b0, _ = bench.make_workload("C5", 600, 0, 2)
-    l1, b1, _ = bench.make_workload("C5", 600, 1, 2)
-    assert b0 == 0 and l0.n == b1 and l1.n == full.n
-    assert abs(l0.n * (l0.n - 1) / 2 - full.n * (full.n - 1) / 4) < 0.02 * full.n * full.n      # equal pair area
-    ctx = mp.get_context("spawn")
-    out = ctx.Queue()
-    port = 29300 + os.getpid() % 300
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, out, "C5", 600)) for r in range(2)]
-    for p in procs:
-        p.start()
-    got = out.get(timeout=240)
-    for p in procs:
-        p.join(timeout=60)
-        assert p.exitcode == 0
-    assert got == want
+    l0, b0, f0 = bench.shard(full, 0, 2)
+    l1, b1, f1 = bench.shard(full, 1, 2)
+    assert b0 == 0 and f0 == 0 and f1 == 0 and l0.n == b1 and l1.n == full.n
+    assert abs(l0.n * (l0.n - 1) / 2 - full.n * (full.n - 1) / 4) < 0.03 * full.n * full.n      # equal pair area
+    assert _run(2, "C5", 600, 29300 + os.getpid() % 300) == want
+
+
+def test_partition_is_balanced_by_band_pairs_and_slices_rebase():
+    """hc_partition_rows / hc_packed_slice on the host: cuts at equal shares of the band-width prefix sum; a slice's
+    headers are the parent's with the op offsets re-based and its records are the parent's."""
+    import ctypes as C
+    sys.path.insert(0, ROOT)
+    import bench
+    from haploclique_b200 import edge
+    full, _ = bench.generate("C3", 6000)
+    L = edge.load_library()
+    for parts in (1, 3, 8):
+        cuts, first = edge.partition_rows(full, parts)
+        assert cuts[0] == 0 and cuts[-1] == full.n and (np.diff(cuts) >= 0).all() and (first % 32 == 0).all()
+        pmax = np.maximum.accumulate(full.cov_last)
+        col0 = np.minimum(np.searchsorted(pmax, full.cov_first, side="left"), np.arange(full.n)) & ~31
+        width = np.arange(full.n) - col0
+        share = np.array([width[cuts[p]:cuts[p + 1]].sum() for p in range(parts)], float)
+        assert share.max() - share.min() <= 2 * width.max()
+        for p in range(parts):
+            assert first[p] == (col0[cuts[p]:cuts[p + 1]].min() if cuts[p + 1] > cuts[p] else cuts[p] & ~31)
+    pk = edge.PackedBatch(full)
+    cuts, first = edge.partition_rows(full, 3)
+    h = pk.headers()
+    ops_all = np.frombuffer((C.c_uint16 * pk.n_ops_total).from_address(pk.c.ops), dtype=np.uint16)
+    for p in range(3):
+        sl = C.c_void_p()
+        assert L.hc_packed_slice(pk._h, int(first[p]), int(cuts[p + 1]), C.byref(sl)) == 0
+        c = C.cast(sl, C.POINTER(edge._Packed)).contents
+        n = int(cuts[p + 1] - first[p])
+        assert c.n_reads == n and c.n_qual_codes == pk.c.n_qual_codes
+        hs = np.frombuffer((C.c_uint8 * (64 * n)).from_address(c.hdr), dtype=edge.HDR_DTYPE)
+        base = int(h["ops_off"][first[p], 0])
+        assert (hs["ops_off"] == h["ops_off"][first[p]:cuts[p + 1]] - base).all()
+        for f in ("raw", "ext", "n_ops", "ncov_flags", "cov_first", "cov_last", "seg_flags"):
+            assert (hs[f] == h[f][first[p]:cuts[p + 1]]).all()
+        ops = np.frombuffer((C.c_uint16 * c.n_ops_total).from_address(c.ops), dtype=np.uint16)
+        assert (ops == ops_all[base:base + c.n_ops_total]).all()
+        L.hc_packed_free(sl)
