@@ -518,7 +518,9 @@ struct hc_ctx {
     struct Win { int r0, r1; size_t item0, n_items; long long word0, n_words; };
     std::vector<int4> items; std::vector<int32_t> colidx; std::vector<Win> wins;
     int plan_begin = -1, plan_end = -1, plan_ctas = 0; bool plan_windows = false;
-    cudaStream_t copy_stream = nullptr;                     // D2H of finished row windows, beside the compute stream
+    cudaStream_t copy_stream = nullptr;                     // D2H of finished row windows, beside the compute streams
+    cudaStream_t stream2 = nullptr;                         // odd row windows: their CTAs fill the SMs the previous window's tail frees
+    cudaEvent_t ev_go = nullptr, ev_join = nullptr;
     cudaEvent_t win_ev[16] = {nullptr};                     // kernel of window k done
     std::vector<uint32_t> ncov_flags;                       // host copy of the headers' flags word (host re-decision)
     std::vector<hc_ambiguous> amb_host;                     // near-threshold pairs of the last pass, re-decided
@@ -919,6 +921,9 @@ int hc_create(const hc_params* params, hc_ctx** out) {
     }
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
     if ((e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    if ((e = cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    if ((e = cudaEventCreateWithFlags(&c->ev_go, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
     for (int k = 0; k < kMaxWindows; ++k)
         if ((e = cudaEventCreateWithFlags(&c->win_ev[k], cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
@@ -950,6 +955,9 @@ void hc_destroy(hc_ctx* c) {
     cudaFree(c->d_detail); cudaFree(c->d_colidx);
     for (int k = 0; k < kMaxWindows; ++k) if (c->win_ev[k]) cudaEventDestroy(c->win_ev[k]);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->stream2) cudaStreamDestroy(c->stream2);
+    if (c->ev_go) cudaEventDestroy(c->ev_go);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -1219,21 +1227,33 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
             a.adj = c->d_adj; a.stats = c->d_stats; a.amb = c->d_amb; a.amb_cap = (int)std::min<size_t>(c->amb_cap, (size_t)INT32_MAX);
             a.detail = detail ? c->d_detail : nullptr;
             a.maxw = use_tile2 ? g2.maxw : g.maxw; a.abuf_bytes = use_tile2 ? g2.abuf_bytes : g.abuf_bytes;
+            // windows alternate between two streams: a CTA of window k+1 starts on an SM as soon as window k's CTA there
+            // has run out of work items, so the ragged end of one launch is filled by the next
+            const bool two = c->wins.size() > 1;
+            if (two) {
+                CU_TRY(c, cudaEventRecord(c->ev_go, c->stream));
+                CU_TRY(c, cudaStreamWaitEvent(c->stream2, c->ev_go, 0));
+            }
             for (size_t k = 0; k < c->wins.size(); ++k) {
                 const hc_ctx::Win& w = c->wins[k];
+                cudaStream_t ks = (k & 1) ? c->stream2 : c->stream;
                 if (w.n_items > 0) {
                     a.items = c->d_items + w.item0; a.n_items = (int)w.n_items; a.item_counter = c->d_item_counter + k;
                     const int blocks = (int)std::min<size_t>(w.n_items, (size_t)n_ctas);
-                    if (use_tile2 && split && map) tile2::score_tile2_kernel<true, true><<<blocks, threads, smem_bytes, c->stream>>>(a);
-                    else if (use_tile2 && split) tile2::score_tile2_kernel<true, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
-                    else if (use_tile2 && map) tile2::score_tile2_kernel<false, true><<<blocks, threads, smem_bytes, c->stream>>>(a);
-                    else if (use_tile2) tile2::score_tile2_kernel<false, false><<<blocks, threads, smem_bytes, c->stream>>>(a);
-                    else tile1_kernel(use_stream, map, g.nwarps == tile::kWarps)<<<blocks, threads, smem_bytes, c->stream>>>(static_cast<const tile::Args&>(a));
+                    if (use_tile2 && split && map) tile2::score_tile2_kernel<true, true><<<blocks, threads, smem_bytes, ks>>>(a);
+                    else if (use_tile2 && split) tile2::score_tile2_kernel<true, false><<<blocks, threads, smem_bytes, ks>>>(a);
+                    else if (use_tile2 && map) tile2::score_tile2_kernel<false, true><<<blocks, threads, smem_bytes, ks>>>(a);
+                    else if (use_tile2) tile2::score_tile2_kernel<false, false><<<blocks, threads, smem_bytes, ks>>>(a);
+                    else tile1_kernel(use_stream, map, g.nwarps == tile::kWarps)<<<blocks, threads, smem_bytes, ks>>>(static_cast<const tile::Args&>(a));
                     CU_TRY(c, cudaGetLastError());
                     launches++;
                     c->last_kernel = use_tile2 ? HC_KERNEL_TILED2 : (use_stream ? HC_KERNEL_STREAMED : HC_KERNEL_TILED);
                 }
-                CU_TRY(c, cudaEventRecord(c->win_ev[k], c->stream));
+                CU_TRY(c, cudaEventRecord(c->win_ev[k], ks));
+            }
+            if (two) {
+                CU_TRY(c, cudaEventRecord(c->ev_join, c->stream2));
+                CU_TRY(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
             }
             CU_TRY(c, cudaEventRecord(c->ev1, c->stream));
             // the words of a finished window go to the host while the later windows are scored

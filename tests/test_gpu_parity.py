@@ -398,7 +398,7 @@ def test_C4_shaped_amplicon_every_band_slot(kernel):
     kw = dict(noProb0=True, maxPosition=b.max_position() + 10)
     det, orc = _tiled_detail_vs_oracle(b, kw, "C4-shape", kernel)
     n_pairs = b.n * (b.n - 1) // 2
-    assert int((orc["status"] >= 1).sum()) > 0.9 * n_pairs        # dense: the band is the whole triangle
+    assert int((orc["status"] >= 1).sum()) > 0.4 * n_pairs        # dense: half of ALL pairs overlap (C2: one in eleven)
     assert int(orc["edge"].sum()) > 20_000 and set(np.unique(orc["layout"])) >= {100, 200, 300, 400}
     kw["noProb0"] = False
     _tiled_detail_vs_oracle(b, kw, "C4-shape-prob0", kernel)
