@@ -2,6 +2,7 @@
 #include "GpuEdgeCalculator.h"
 
 #include <cassert>
+#include <cstdlib>
 #include <cstring>
 #include <stdexcept>
 
@@ -77,6 +78,7 @@ void GpuEdgeCalculator::init(double edge_quasi_cutoff, double overlap, std::unor
     par_.min_overlap_single = overlap_single;
     par_.no_prob0 = noProb0 ? 1 : 0;
     devices_ = devices.empty() ? std::vector<int>(1, 0) : devices;
+    if (std::getenv("HC_GPU_NO_ROWS")) row_feeding_ = false;
     par_.device = devices_[0];
     if (!simpson_map.empty()) {                            // SIMPSON_MAP.resize(maxPosition+1) (src/NewEdgeCalculator.cpp:85-88)
         simpson_.assign((size_t)maxPosition + 1, 0.0);
@@ -93,7 +95,7 @@ void GpuEdgeCalculator::init(double edge_quasi_cutoff, double overlap, std::unor
 GpuEdgeCalculator::GpuEdgeCalculator(double, double edge_quasi_cutoff, double overlap, bool, std::unordered_map<int, double>& simpson_map,
                                      double edge_quasi_cutoff_single, double overlap_single, double edge_quasi_cutoff_mixed,
                                      unsigned int maxPosition, bool noProb0, int device)
-    : multi_(nullptr), aux_(nullptr), resident_(nullptr) {
+    : multi_(nullptr), aux_(nullptr), resident_(nullptr), row_feeding_(true) {
     init(edge_quasi_cutoff, overlap, simpson_map, edge_quasi_cutoff_single, overlap_single, edge_quasi_cutoff_mixed, maxPosition,
          noProb0, std::vector<int>(1, device));
 }
@@ -101,7 +103,7 @@ GpuEdgeCalculator::GpuEdgeCalculator(double, double edge_quasi_cutoff, double ov
 GpuEdgeCalculator::GpuEdgeCalculator(double, double edge_quasi_cutoff, double overlap, bool, std::unordered_map<int, double>& simpson_map,
                                      double edge_quasi_cutoff_single, double overlap_single, double edge_quasi_cutoff_mixed,
                                      unsigned int maxPosition, bool noProb0, const std::vector<int>& devices)
-    : multi_(nullptr), aux_(nullptr), resident_(nullptr) {
+    : multi_(nullptr), aux_(nullptr), resident_(nullptr), row_feeding_(true) {
     init(edge_quasi_cutoff, overlap, simpson_map, edge_quasi_cutoff_single, overlap_single, edge_quasi_cutoff_mixed, maxPosition,
          noProb0, devices);
 }
@@ -208,6 +210,22 @@ void GpuEdgeCalculator::neighbours(const AlignmentRecord& ap, std::vector<const 
             out.push_back(reads_[(size_t)col0_[i] + (size_t)(w - w0) * 32 + b]);
         }
     }
+}
+
+bool GpuEdgeCalculator::neighbourIndices(const AlignmentRecord& ap, int id, std::vector<int>& out) const {
+    out.clear();
+    if (id < 0 || (size_t)id >= reads_.size() || reads_[(size_t)id] != &ap) return false;
+    const int64_t w0 = word_off_[(size_t)id], w1 = word_off_[(size_t)id + 1];
+    const int c0 = col0_[(size_t)id];
+    for (int64_t w = w0; w < w1; ++w) {
+        uint32_t bits = words_[(size_t)w];
+        while (bits) {
+            const int b = __builtin_ctz(bits);
+            bits &= bits - 1;
+            out.push_back(c0 + (int)(w - w0) * 32 + b);
+        }
+    }
+    return true;
 }
 
 void GpuEdgeCalculator::getPartnerLengthRange(const AlignmentRecord&, unsigned int*, unsigned int*) const { assert(false); }

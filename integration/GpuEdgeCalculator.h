@@ -55,6 +55,16 @@ public:
      *  bits of its adjacency row: the row-consuming alternative to one edgeBetween call per active read in the finders'
      *  edge-feeding loops (src/CLEVER.cpp:218-232, src/BronKerbosch.cpp:286-292). Same answers as edgeBetween. */
     void neighbours(const AlignmentRecord& ap, std::vector<const AlignmentRecord*>& out) const;
+    /** Row feeding for the finders' edge loops (integration/CLEVER_rows.patch, BronKerbosch_rows.patch): the arrival indices
+     *  of the earlier reads adjacent to `ap`, ascending, provided `ap` is read number `id` of the scored batch (the finder's
+     *  id == position in the batch when the batch is added in order after initialize()); false otherwise and the finder
+     *  falls back to one edgeBetween call per stored alignment. No record is dereferenced: the finder may have freed
+     *  earlier ones. */
+    bool neighbourIndices(const AlignmentRecord& ap, int id, std::vector<int>& out) const;
+    bool rowFeeding() const { return row_feeding_; }
+    void setRowFeeding(bool on) { row_feeding_ = on; }
+    /** Scratch the patched CLEVER keeps with the calculator (storage slot per id), so that class keeps its layout. */
+    std::vector<size_t>& finderSlots() const { return finder_slots_; }
     /** Not implemented by NewEdgeCalculator either (src/NewEdgeCalculator.cpp:1378-1380). */
     virtual void getPartnerLengthRange(const AlignmentRecord& ap, unsigned int* min, unsigned int* max) const;
     virtual void setOverlapCliques(double d);
@@ -104,6 +114,8 @@ private:
     std::vector<uint32_t> words_;
     hc_band_stats stats_;
     hc_packed* resident_;                                  // the scored batch (the devices hold slices of it)
+    bool row_feeding_;
+    mutable std::vector<size_t> finder_slots_;
 };
 
 /** The same binding for the reference's older scorer, QuasispeciesEdgeCalculator (src/QuasispeciesEdgeCalculator.h:57,

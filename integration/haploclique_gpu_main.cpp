@@ -12,10 +12,13 @@
 #include "haploclique.cpp"
 #undef main
 
+#include <sstream>
+
 #include "GpuEdgeCalculator.h"
 
 int main(int argc, char* argv[]) {
     map<std::string, docopt::value> args = docopt::docopt(USAGE, {argv + 1, argv + argc}, true, HAPLOCLIQUE_VERSION);
+    for (auto elem : args) cout << elem.first << " " << elem.second << "\n";       // the reference echoes its arguments (:210-213)
     const string bamfile = args["<bamfile>"].asString();
     const string outfile = args["<output>"] ? args["<output>"].asString() : string("quasispecies");
     const double cutoff_cliques = stod(args["--edge_quasi_cutoff_cliques"].asString());
@@ -68,17 +71,31 @@ int main(int argc, char* argv[]) {
     } catch (const runtime_error& error) {
         cerr << error.what() << endl;
         return 1;
+    } catch (...) {
+        cerr << "Unexpected error while reading BamFile." << endl;
+        return 1;
     }
     max_position1 = std::max(max_position1, max_position2);
 
+    // HC_GPU_DEVICES=0,1,...: the rows of every iteration's batch are cut across these GPUs by the library (default: GPU 0)
+    std::vector<int> devices;
+    if (const char* e = std::getenv("HC_GPU_DEVICES")) {
+        std::string s(e), tok;
+        std::stringstream ss(s);
+        while (std::getline(ss, tok, ',')) if (!tok.empty()) devices.push_back(atoi(tok.c_str()));
+    }
+    if (devices.empty()) devices.push_back(0);
     GpuEdgeCalculator* calc;
     try {
         calc = new GpuEdgeCalculator(Q, cutoff_cliques, overlap_cliques, frameshift_merge, simpson_map, cutoff_single,
-                                     overlap_single, cutoff_mixed, max_position1, no_prob0);
+                                     overlap_single, cutoff_mixed, max_position1, no_prob0, devices);
     } catch (const runtime_error& error) {
         cerr << error.what() << endl;
         return 1;
     }
+    // HC_GPU_NO_ROWS: the finders ask edgeBetween once per stored alignment, as the unpatched reference does (for timing
+    // the row-consuming edge loops of integration/*_rows.patch against it)
+    if (std::getenv("HC_GPU_NO_ROWS")) calc->setRowFeeding(false);
     std::vector<unsigned int> read_clique_counter(original_read_names.size());
     LogWriter* lw = logfile.empty() ? nullptr : new LogWriter(logfile, read_clique_counter);
     CliqueCollector collector(lw);

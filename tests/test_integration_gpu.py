@@ -28,7 +28,7 @@ def test_clique_rounds_with_gpu_calculator_equal_the_reference(use_bk):
     # the reference's cram test input (arabis, 1104 paired records) and parameters, all rounds until convergence
     b = common.load_batch("arabis_records.npz")
     params = dict(common.WEAK, noProb0=True)
-    ref, gpu = pyref.Reference(gpu_adapter=True), pyref.Reference(gpu_adapter=True)
+    ref, gpu = pyref.Reference(), pyref.Reference(gpu_adapter=True)     # unpatched finders / row-fed finders (integration/*_rows.patch)
     for R in (ref, gpu):
         R.add_batch(b)
         R.set_params(**params)
@@ -59,36 +59,57 @@ def test_unit_expectations_through_the_adapter(golden):
         assert R.edge_gpu(case["ap1"], case["ap2"]) == case["expected"] == R.edge(case["ap1"], case["ap2"]), name
 
 
+def _run_cli(exe, d, finder, flags, bam, env=None):
+    d.mkdir()
+    cmd = [exe] + ([finder] if finder == "bronkerbosch" else []) + flags + ["--log=" + str(d / "edges.log"), bam]
+    r = subprocess.run(cmd, cwd=str(d), capture_output=True, text=True, timeout=600, env=dict(os.environ, **(env or {})))
+    assert r.returncode == 0, r.stderr[-500:]
+    return (open(d / "quasispecies.fasta", "rb").read(),
+            [ln for ln in r.stdout.splitlines() if "edges:" in ln or ln.startswith("final")],
+            open(d / "edges.log", "rb").read(), r.stdout)
+
+
+def _clis_on_bam(tmp_path, bam, flags, finder):
+    """The unmodified CLI and the GPU-backed CLI on one BAM: same per-round stdout lines (read and edge counts), byte-identical
+    FASTA and byte-identical --log dumps (every iteration's adjacency lists and cliques, src/LogWriter.h:26-70) -- with the
+    finders' edge loops fed from adjacency rows (integration/*_rows.patch, the default), with one edgeBetween call per stored
+    alignment (HC_GPU_NO_ROWS), and with the rows self-checked against the per-pair answers in every round."""
+    ref = _run_cli(pyref.CLI_REF, tmp_path / "ref", finder, flags, bam)
+    assert len(ref[0]) > 0
+    rows = _run_cli(pyref.CLI_GPU, tmp_path / "rows", finder, flags, bam)
+    pairs = _run_cli(pyref.CLI_GPU, tmp_path / "pairs", finder, flags, bam, {"HC_GPU_NO_ROWS": "1"})
+    check = _run_cli(pyref.CLI_GPU, tmp_path / "check", finder, flags, bam, {"HC_GPU_CHECK_ROWS": "1"})
+    for tag, got in (("rows", rows), ("pairs", pairs), ("check", check)):
+        assert got[0] == ref[0], tag + ": FASTA differs"
+        assert got[1] == ref[1], tag + ": per-round counts differ"
+        assert got[2] == ref[2] and len(ref[2]) > 0, tag + ": --log adjacency / cliques differ"
+    assert "rows ok" in check[3] and "MISMATCH" not in check[3]
+    return ref
+
+
 def _both_clis(tmp_path, batch, flags, finder, genome_len):
-    """Writes `batch` as a BAM with the reference's vendored BamWriter, runs the unmodified CLI and the GPU-backed CLI on
-    it: same per-round stdout lines (read and edge counts), byte-identical FASTA; then the GPU CLI once more with the
-    row-consuming hook's self-check on."""
+    """Writes `batch` as a BAM with the reference's vendored BamWriter and runs _clis_on_bam on it."""
     W = pyref.Reference()
     bam = str(tmp_path / "reads.bam")
     W.bam_writer_open(bam, "ref", genome_len)
     W.add_batch(batch)
     W.bam_writer_close()
-    outs = {}
-    for tag, exe in (("ref", pyref.CLI_REF), ("gpu", pyref.CLI_GPU)):
-        d = tmp_path / tag
-        d.mkdir()
-        cmd = [exe] + ([finder] if finder == "bronkerbosch" else []) + flags + [bam]
-        r = subprocess.run(cmd, cwd=str(d), capture_output=True, text=True, timeout=300)
-        assert r.returncode == 0, r.stderr[-500:]
-        outs[tag] = (open(d / "quasispecies.fasta", "rb").read(),
-                     [ln for ln in r.stdout.splitlines() if "edges:" in ln or ln.startswith("final")])
-    assert outs["ref"][0] == outs["gpu"][0] and len(outs["ref"][0]) > 0
-    assert outs["ref"][1] == outs["gpu"][1]
-    # the row-consuming hook (GpuEdgeCalculator::neighbours: the set bits of a read's adjacency row) gives the same
-    # neighbours, in the same order, as one edgeBetween call per earlier read -- checked by the CLI itself in every round
-    d = tmp_path / "rows"
-    d.mkdir()
-    cmd = [pyref.CLI_GPU] + ([finder] if finder == "bronkerbosch" else []) + flags + [bam]
-    r = subprocess.run(cmd, cwd=str(d), capture_output=True, text=True, timeout=300, env=dict(os.environ, HC_GPU_CHECK_ROWS="1"))
-    assert r.returncode == 0, r.stderr[-500:]
-    assert "rows ok" in r.stdout and "MISMATCH" not in r.stdout
-    assert open(d / "quasispecies.fasta", "rb").read() == outs["ref"][0]
-    return outs["ref"][1]
+    return _clis_on_bam(tmp_path, bam, flags, finder)[1]
+
+
+@pytest.mark.parametrize("finder", ["clever", "bronkerbosch"])
+def test_the_references_cram_vector_through_the_gpu_cli(tmp_path, finder):
+    """The reference's own end-to-end test (test/cram/arabis_large_500_01.t): its reads.bam, its flags, its expected
+    quasispecies.fasta.fasta -- both committed under tests/golden/ -- through haploclique_gpu (GPU edges, row-fed finders)."""
+    if not (os.path.exists(pyref.CLI_REF) and os.path.exists(pyref.CLI_GPU)):
+        pytest.skip("CLI binaries not built")
+    bam = os.path.join(common.GOLDEN, "arabis_large_500_01_reads.bam")
+    flags = ["--edge_quasi_cutoff_cliques=0.85", "--edge_quasi_cutoff_mixed=0.85", "--edge_quasi_cutoff_single=0.8",
+             "--min_overlap_cliques=0.6", "--min_overlap_single=0.5", "--no_singletons", "--significance=4", "--no_prob0"]
+    ref = _clis_on_bam(tmp_path, bam, flags, finder)
+    assert ref[0] == open(os.path.join(common.GOLDEN, "arabis_large_500_01_quasispecies.fasta"), "rb").read()
+    if finder == "clever":
+        assert "edges: 153685" in ref[1][0]
 
 
 @pytest.mark.parametrize("finder", ["clever", "bronkerbosch"])
