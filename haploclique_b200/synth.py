@@ -203,7 +203,7 @@ def super_reads(n_frag: int = 4000, clique_frac: float = 0.7, seed: int = 202611
 
 
 def zoo(n_reads: int, genome_len: int = 400, seed: int = 1, max_seg: int = 120, clique_frac: float = 0.3,
-        wide_qual=(2, 94)) -> ReadBatch:
+        wide_qual=(2, 94), indel: float = 0.02) -> ReadBatch:
     """Small adversarial batch for parity tests: single/paired mix, many start ties, leading/trailing S and
     H clips, insertions and deletions anywhere inside, N bases, wide quality range (a fifth of the segments draw
     Phred values from `wide_qual`, the rest from 20..41), 'Clique' names."""
@@ -221,9 +221,9 @@ def zoo(n_reads: int, genome_len: int = 400, seed: int = 1, max_seg: int = 120, 
         ncore = ncol - lead - trail
         for c in range(ncore):
             inner = 0 < c < ncore - 1
-            if inner and rng.random() < 0.02:
+            if inner and rng.random() < indel:
                 mid.append(b"I" * int(rng.integers(1, 3)))
-            mid.append(b"D" if inner and rng.random() < 0.02 else b"M")
+            mid.append(b"D" if inner and rng.random() < indel else b"M")
         cig = lead_op * lead + b"".join(mid) + trail_op * trail
         nq = sum(1 for ch in cig if ch in b"MIS")
         seq = _BASES[rng.choice(5, nq, p=[0.245, 0.245, 0.245, 0.245, 0.02])].tobytes()

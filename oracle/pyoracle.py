@@ -183,3 +183,26 @@ def merge_clique_se(batch, members):
                               p(oc), p(os_), p(oq), p(info))
     st, s, e, no, ns = (int(x) for x in info)
     return st, s, e, oc[:no].tobytes(), os_[:ns].tobytes(), oq[:ns].tobytes()
+
+
+def merge_clique(batch, members):
+    """AlignmentRecord(alignments, id) for any mix of single-end / paired-end members (read indices into `batch`, fold
+    order). Returns (status, single_end, seg1, seg2) with seg = (start, end, cigar_unrolled, sequence, qualities) and
+    seg2 = None for a single-end result."""
+    mem = np.ascontiguousarray(members, np.int32)
+    rows = np.stack([2 * mem, 2 * mem + 1], 1).reshape(-1)
+    cap = int(batch.cig_len[rows].sum()) + 16
+    oc, os_, oq = (np.zeros(2 * cap, np.uint8) for _ in range(3))
+    info = np.zeros(10, np.int32)
+    p = lambda a: np.ascontiguousarray(a).ctypes.data_as(C.c_void_p)
+    lib().orc_merge_clique(p(batch.single_end), p(batch.seg_start), p(batch.seg_end), p(batch.cig_off), p(batch.cig_len),
+                           p(batch.seq_off), p(batch.seq_len), p(batch.cig), p(batch.seq), p(batch.qual), p(mem),
+                           C.c_int32(mem.size), C.c_int64(cap), p(oc), p(os_), p(oq), p(info))
+    st, single = int(info[0]), bool(info[1])
+    if st:
+        return st, False, None, None
+    segs = []
+    for sg in range(1 if single else 2):
+        s, e, no, ns = (int(x) for x in info[2 + 4 * sg:6 + 4 * sg])
+        segs.append((s, e, oc[sg * cap:sg * cap + no].tobytes(), os_[sg * cap:sg * cap + ns].tobytes(), oq[sg * cap:sg * cap + ns].tobytes()))
+    return st, single, segs[0], (None if single else segs[1])

@@ -140,8 +140,10 @@ class Reference:
     def max_position(self) -> int:
         return int(self.L.hcref_max_position(self.h))
 
-    def to_batch(self):
-        """Dumps the reference's records into our ReadBatch (the packing input)."""
+    def to_batch(self, check_cov: bool = True):
+        """Dumps the reference's records into our ReadBatch (the packing input). check_cov=False: records restored from the
+        reference's unit-test fixture files carry the cov_pos rows stored in the file, which need not be what
+        coveredPositions() would build; the reference's values are then taken as they are."""
         from haploclique_b200.records import AlignmentRecord, ReadBatch
         recs = []
         info = (C.c_int * 12)()
@@ -161,7 +163,10 @@ class Reference:
         b = ReadBatch.from_records(recs)
         cov = np.array(covs, np.int32).reshape(-1, 3)
         # coveredPositions restated in records.py must agree with the reference's cov_pos
-        assert (b.ncov == cov[:, 0]).all() and (b.cov_first == cov[:, 1]).all() and (b.cov_last == cov[:, 2]).all()
+        if check_cov:
+            assert (b.ncov == cov[:, 0]).all() and (b.cov_first == cov[:, 1]).all() and (b.cov_last == cov[:, 2]).all()
+        else:
+            b.ncov[:], b.cov_first[:], b.cov_last[:] = cov[:, 0], cov[:, 1], cov[:, 2]
         return b
 
     # -- calculator ---------------------------------------------------------------------------------
@@ -197,6 +202,21 @@ class Reference:
         bufs = [C.create_string_buffer(max(k, 1)) for k in (nc1, nq1, nq1, 1, 1, 1)]
         self.L.hcref_record_data(self.h, i, *bufs)
         return bool(se), s1, e1, bufs[0].raw[:nc1], bufs[1].raw[:nq1], bufs[2].raw[:nq1]
+
+    def merge_clique_full(self, members, clique_id: int = 0):
+        """AlignmentRecord(alignments, clique_id) over records[members], any mix of single-end / paired-end members;
+        returns (single_end, seg1, seg2) with seg = (start, end, cigar, seq, qual), seg2 None for a single-end result."""
+        mem = np.ascontiguousarray(members, np.int32)
+        i = self.L.hcref_merge_clique(self.h, _p(mem), C.c_int(mem.size), C.c_uint(clique_id))
+        info = (C.c_int * 12)()
+        name = C.create_string_buffer(512)
+        self.L.hcref_record_info(self.h, i, info, name, 512)
+        se, s1, e1, s2, e2, nc1, nq1, nc2, nq2 = list(info)[:9]
+        bufs = [C.create_string_buffer(max(k, 1)) for k in (nc1, nq1, nq1, nc2, nq2, nq2)]
+        self.L.hcref_record_data(self.h, i, *bufs)
+        seg1 = (s1, e1, bufs[0].raw[:nc1], bufs[1].raw[:nq1], bufs[2].raw[:nq1])
+        seg2 = None if se else (s2, e2, bufs[3].raw[:nc2], bufs[4].raw[:nq2], bufs[5].raw[:nq2])
+        return bool(se), seg1, seg2
 
     def score_all(self):
         n = self.n

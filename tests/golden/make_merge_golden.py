@@ -26,6 +26,17 @@ def digest(rows):
     return h.hexdigest()
 
 
+def digest_general(rows):
+    h = hashlib.sha256()
+    for single, s1, s2 in rows:
+        h.update(bytes([1 if single else 0]))
+        for seg in (s1,) if single else (s1, s2):
+            start, end, cig, seq, qual = seg
+            h.update(np.array([start, end, len(cig), len(seq)], "<i4").tobytes())
+            h.update(cig); h.update(seq); h.update(qual)
+    return h.hexdigest()
+
+
 def main():
     out = {}
     R = pyref.Reference()
@@ -48,12 +59,24 @@ def main():
             rows.append((s, e, cig, seq, qual))
         out[name] = {"n_cliques": n_cl, "undefined": undefined, "sha256": digest(rows)}
         print(name, n_cl, "undefined", len(undefined))
+    # general merge (paired / mixed members): digest over (single_end, both segments) of the reference's records
+    for name, batch, seed, n_cl, span, mm in merge_cases.GENERAL_CASES():
+        R = pyref.Reference()
+        R.add_batch(batch)
+        rows, undefined = [], []
+        for t, mem in enumerate(merge_cases.windows(batch.n, n_cl, seed, span, mm)):
+            if pyoracle.merge_clique(batch, mem)[0] != 0:
+                undefined.append(t)
+                continue
+            rows.append(R.merge_clique_full(mem, t))
+        out["general_" + name] = {"n_cliques": n_cl, "undefined": undefined, "sha256": digest_general(rows)}
+        print("general", name, n_cl, "undefined", len(undefined))
     # The reference's own known-answer test for this path: test/unit/unit3.cpp:33-60 (mergeAlignmentRecordsMatch) merges
     # fixtures sample00 + sample10 and expects sample11 -- all three single-end. Their fields travel as a small npz.
     R = pyref.Reference()
-    for k in (0, 10, 11):
+    for k in (0, 10, 11, 12, 13, 14):      # unit3.cpp:65-93: sample12 + sample13 must equal sample14 (paired-end)
         R.restore_fixture(os.path.join(pyref.REFERENCE_ROOT, "test/data/simulation/unit_data/alignment_sample%02d.txt" % k))
-    R.to_batch().save(os.path.join(ROOT, "tests", "golden", "unit3_merge_fixtures.npz"))
+    R.to_batch(check_cov=False).save(os.path.join(ROOT, "tests", "golden", "unit3_merge_fixtures.npz"))
     with open(os.path.join(ROOT, "tests", "golden", "merge_golden.json"), "w") as fh:
         json.dump(out, fh, indent=1)
 

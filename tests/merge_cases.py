@@ -64,3 +64,19 @@ def CASES():
     yield "hiv50", load_batch("hiv50_records.npz"), 1, 3000, 12, 7
     yield "hiv50_large_cliques", load_batch("hiv50_records.npz"), 2, 300, 40, 30
     yield "clipped", clipped_batch(), 11, 1500, 8, 5
+
+
+def GENERAL_CASES():
+    """(label, batch, seed, n_cliques, window span, max members) for the general merge (paired and mixed members,
+    SURVEY.md 8(f) N2): the reference's paired cram input, one of its super-read rounds, synthetic single/paired mixes
+    with clips and haplotype indels, and adversarial indel-free layouts that reach every branch of
+    mergeAlignmentRecordsPaired / Mixed."""
+    from haploclique_b200 import synth
+    from tests.common import load_batch
+    yield "arabis", load_batch("arabis_records.npz"), 1, 1500, 12, 6
+    yield "arabis_wide", load_batch("arabis_records.npz"), 2, 400, 60, 8
+    yield "superreads_it1", load_batch("superreads_arabis_it1.npz"), 3, 500, 10, 5
+    yield "quasi_mix", synth.quasispecies(700, genome_len=2000, read_len=120, frag_mean=300.0, frag_sd=50.0, frag_min=165, frag_max=540,
+                                          seed=73, clip_frac=0.15, indel_err=3e-4), 3, 2500, 14, 6
+    yield "layout_zoo", synth.zoo(400, seed=80, genome_len=600, indel=0.0), 0, 3000, 16, 5
+    yield "layout_zoo_indels", synth.zoo(400, seed=84, genome_len=600, indel=0.002), 4, 3000, 16, 5

@@ -59,7 +59,7 @@ def unit3_expected():
 
 def test_merge_oracle_reproduces_the_references_unit3_vector():
     b, members, exp = unit3_expected()
-    assert b.single_end.all() and b.names[2].startswith("Clique")
+    assert b.single_end[:3].all() and b.names[2].startswith("Clique")
     st, *got = pyoracle.merge_clique_se(b, members)
     assert st == 0 and tuple(got) == exp
 
@@ -108,3 +108,88 @@ def test_merge_refuses_paired_members_and_has_no_cpu_path():
         h = load_batch("hiv50_records.npz")
         with pytest.raises(edge.HcError, match="no CPU merging path"):
             edge.merge_cliques_se(h, [[0, 1]])
+
+
+# ---- general merge: paired-end and mixed members (mergeAlignmentRecordsPaired / Mixed, src/AlignmentRecord.cpp:734-1537) ----
+def _digest_general(rows):
+    h = hashlib.sha256()
+    for single, s1, s2 in rows:
+        h.update(bytes([1 if single else 0]))
+        for seg in (s1,) if single else (s1, s2):
+            start, end, cig, seq, qual = seg
+            h.update(np.array([start, end, len(cig), len(seq)], "<i4").tobytes())
+            h.update(cig); h.update(seq); h.update(qual)
+    return h.hexdigest()
+
+
+def unit3_paired_expected():
+    """The reference's second known-answer vector, test/unit/unit3.cpp:65-93: sample12 merged with sample13 (both paired-end)
+    must equal sample14 (rows 3, 4, 5 of tests/golden/unit3_merge_fixtures.npz)."""
+    from tests.common import load_batch
+    b = load_batch("unit3_merge_fixtures.npz")
+    r = b.record(5)
+    exp = (False, (r.start1, r.end1, r.cigar1_unrolled, r.sequence1, r.qualities1),
+           (r.start2, r.end2, r.cigar2_unrolled, r.sequence2, r.qualities2))
+    return b, [3, 4], exp
+
+
+def test_general_merge_oracle_reproduces_both_unit3_vectors():
+    b, members, exp = unit3_paired_expected()
+    assert not b.single_end[3:].any() and b.names[5].startswith("Clique")
+    st, *got = pyoracle.merge_clique(b, members)
+    assert st == 0 and tuple(got) == exp
+    b, members, exp1 = unit3_expected()                       # the single-end vector through the general entry point
+    st, single, s1, s2 = pyoracle.merge_clique(b, members)
+    assert st == 0 and single and s2 is None and s1 == exp1
+
+
+@pytest.mark.parametrize("case", ["arabis", "arabis_wide", "superreads_it1", "quasi_mix", "layout_zoo", "layout_zoo_indels"])
+def test_general_merge_oracle_matches_reference_digest(case):
+    g = _golden()["general_" + case]
+    name, batch, seed, n_cl, span, mm = next(c for c in merge_cases.GENERAL_CASES() if c[0] == case)
+    rows, undefined = [], []
+    for t, mem in enumerate(merge_cases.windows(batch.n, n_cl, seed, span, mm)):
+        st, *rec = pyoracle.merge_clique(batch, mem)
+        if st:
+            undefined.append(t)
+        else:
+            rows.append(tuple(rec))
+    assert undefined == g["undefined"]
+    assert _digest_general(rows) == g["sha256"]
+
+
+def test_general_merge_agrees_with_the_single_end_restatement():
+    name, batch, seed, n_cl, span, mm = next(c for c in merge_cases.CASES() if c[0] == "clipped")
+    for mem in merge_cases.windows(batch.n, 400, seed, span, mm):
+        a = pyoracle.merge_clique_se(batch, mem)
+        st, single, s1, s2 = pyoracle.merge_clique(batch, mem)
+        assert st == a[0] and (st != 0 or (single and s1 == a[1:]))
+
+
+@pytest.mark.skipif(not pyref.available(), reason="oracle/_ref/libhcref.so not built (needs /root/reference)")
+def test_general_merge_oracle_matches_reference_directly_and_reaches_every_layout():
+    import ctypes as C
+    from haploclique_b200 import synth
+
+    def counts():
+        out = np.zeros(24, np.int64)
+        pyoracle.lib().orc_merge_layout_counts(out.ctypes.data_as(C.c_void_p))
+        return out
+
+    counts()
+    n = 0
+    for seed in (80, 81, 82, 83):
+        batch = synth.zoo(400, seed=seed, genome_len=600, indel=0.0)
+        R = pyref.Reference()
+        R.add_batch(batch)
+        for t, mem in enumerate(merge_cases.windows(batch.n, 3000, seed - 80, 16, 5)):
+            st, *rec = pyoracle.merge_clique(batch, mem)
+            if st:
+                continue
+            assert R.merge_clique_full(mem, t) == tuple(rec), "clique %d %s" % (t, mem)
+            n += 1
+    c = counts()
+    assert n > 9000
+    # every branch but the tenth paired layout (:1161, needs ar.segment2 to start left of this.segment1 with ar.segment1
+    # ending before it) is reached by this generator; 17 = no paired layout matched (`this` stays as it is)
+    assert (c[[0, 1, 2, 3, 4, 5, 6, 7, 8, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22]] > 0).all(), c.tolist()
