@@ -1,20 +1,34 @@
-// Super-read construction for single-end cliques on the device (first slice).
+// Super-read construction on the device: AlignmentRecord(alignments, clique_id)
+// (src/AlignmentRecord.cpp:211-249) for whole batches of cliques, any mix of single-end and paired-end members.
 //
-// What it replaces: AlignmentRecord(alignments, clique_id) (src/AlignmentRecord.cpp:211-249) when every member is
-// single-end -- a left fold of mergeAlignmentRecordsSingle(ar,1,1) (:581-734) over the members, each fold a lock-step
-// walk of two unrolled CIGARs (noOverlapMerge :1539-1576, overlapMerge :1578-1674) whose shared M / I columns take
-// the consensus base and the updated Phred char from computeEntry (:169-184, tables :40-90).
+// What it replaces: the left fold of the clique's members through mergeAlignmentRecordsSingle(ar,i,j) (:581-734),
+// mergeAlignmentRecordsPaired (:734-1293) and mergeAlignmentRecordsMixed (:1295-1537) -- lock-step walks of unrolled CIGARs
+// (noOverlapMerge :1539-1576, overlapMerge :1578-1674) whose shared M / I columns take the consensus base and the updated
+// Phred char from computeEntry (:169-184, tables :40-90).
 //
-// First correct CUDA path: one lane per clique, the fold ping-pongs between the caller-visible output region and a
-// scratch region of the same size in HBM, the two 94x94 quality tables sit in shared memory. Cliques are independent,
-// so a batch of a finder round's cliques fills the grid; per-column work is byte loads and one table look-up
-// (integer / byte work, HBM- and latency-bound). Paired / mixed merges are not built yet: a batch holding a
-// paired-end member is refused (HC_E_INVALID), never routed elsewhere.
+// Formulation here. A warp owns a clique. The running super-read (two segments) lives in the warp's slice of shared memory
+// across all folds (global scratch only for super-reads longer than the slice), members are read in place, and only the
+// final record is written out -- cooperatively, 32 lanes wide. A fold is a row of a layout table: a phase program
+// (tail / overlap / seat / finish steps with symbolic bounds: the reference's hand-unrolled while loops) plus a result
+// rule (which segment receives the merged string, how start / end combine, what is taken over from the member).
+//   * Plain folds -- every segment taking part is "clips, M only, clips" and the layout has no cursor quirk -- are
+//     evaluated in reference-column space by all 32 lanes: a phase covers a column interval known in O(1), a column's
+//     output slot follows from interval arithmetic (only M columns emit), so lanes work on 32 consecutive columns with
+//     no scan. This is the common case (reads without indels).
+//   * Every other fold (indels, the reference's cursor slip in the sixth paired layout, cursors that run off a CIGAR) is
+//     walked by one lane exactly as the reference walks it.
+// Results are compacted on the device; the host receives per clique the record header and the exact bytes.
+// Undefined inputs (an op pair overlapMerge does not list; a cursor past its CIGAR or its sequence: the Release build of
+// the reference never returns / throws there) end that clique with HC_MERGE_UNDEFINED / HC_MERGE_OVERRUN.
+// There is no CPU merging path: without a CUDA device every call fails with HC_E_CUDA.
 #include <cuda_runtime.h>
 
+#include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstdint>
 #include <cstdlib>
+#include <cstring>
 #include <string>
 #include <vector>
 
@@ -22,7 +36,11 @@
 
 namespace {
 
-constexpr int NQ = 94;   // quality chars 33..126
+constexpr int NQ = 94;            // quality chars 33..126
+constexpr int kWarps = 8;         // warps (= cliques in flight) per CTA
+constexpr int kSlice = 24 * 1024; // shared memory per warp: 4 segment buffers (2 segments x 2 generations) of 3 byte streams
+constexpr int kSegCap = kSlice / 12 / 16 * 16;   // ops a buffered segment may hold (2048): longer running reads use global scratch
+constexpr int kTabBytes = (2 * NQ * NQ + 255) / 256 * 256;
 
 // Phred update tables with the reference's arithmetic (src/AlignmentRecord.cpp:40-54, 68-86): error probabilities through
 // a double pow rounded to float, the posterior in float, log10 and round in float; stored as the final quality char
@@ -42,89 +60,191 @@ void build_phred_tables(uint8_t* tab) {
         }
 }
 
+// ---- layout table: bound ids ext*8 + side*4 + seg*2 + is_end; side 0 = the running record ("this"), 1 = the member ("ar")
+#define MB(ext, side, seg, is_end) ((ext) * 8 + (side) * 4 + (seg) * 2 + (is_end))
+enum : uint8_t {
+    As1 = MB(0, 0, 0, 0), Ae1 = MB(0, 0, 0, 1), As2 = MB(0, 0, 1, 0), Ae2 = MB(0, 0, 1, 1),
+    Bs1 = MB(0, 1, 0, 0), Be1 = MB(0, 1, 0, 1), Bs2 = MB(0, 1, 1, 0), Be2 = MB(0, 1, 1, 1),
+    xAs1 = MB(1, 0, 0, 0), xAe1 = MB(1, 0, 0, 1), xAs2 = MB(1, 0, 1, 0), xAe2 = MB(1, 0, 1, 1),
+    xBs1 = MB(1, 1, 0, 0), xBe1 = MB(1, 1, 0, 1), xBs2 = MB(1, 1, 1, 0), xBe2 = MB(1, 1, 1, 1)
+};
+enum : uint8_t { P_END = 0, P_START, P_START_MIN, P_TLT, P_OVL, P_OVL2, P_OVLQX, P_SEAT, P_FIN };
+struct Phase { uint8_t op, x, y, a, b; };
+// where the merged string goes (segment 0/1), start = min(v[sa], v[sb]), end = max(v[ea], v[eb]), single_end afterwards
+// (2 = leave the flag), take: 0 nothing, 1 segment 2 := ar.segment2 afterwards, 2 segment 1 := ar.segment1 beforehand
+struct Result { uint8_t seg, sa, sb, ea, eb, single, take; };
+struct Layout { Phase ph[11]; Result res; };
+#define L_START(a) {P_START, 0, 0, a, 0}
+#define L_START_MIN(a, b) {P_START_MIN, 0, 0, a, b}
+#define L_TLT(sd, sg, a) {P_TLT, sd, sg, a, 0}
+#define L_OVL(sa, sb, a) {P_OVL, sa, sb, a, 0}
+#define L_OVL2(sa, sb, a, b) {P_OVL2, sa, sb, a, b}
+#define L_OVLQX(sa, sb, a, b) {P_OVLQX, sa, sb, a, b}
+#define L_SEAT(sd, sg) {P_SEAT, sd, sg, 0, 0}
+#define L_FIN(a, b) {P_FIN, 0, 0, a, b}
+#define L_END {P_END, 0, 0, 0, 0}
+enum { LAY_PS0 = 12, LAY_SP0 = 14, LAY_SINGLE = 16, N_LAYOUTS = 20 };
+// rows 0..11: mergeAlignmentRecordsPaired's walked layouts in source order (:773 :819 :868 :907 :946 :989 :1027 :1069 :1118
+// :1161 :1204 :1249); 12, 13: this paired x ar single (:1335, :1368); 14, 15: this single x ar paired (:1461, :1496);
+// 16..19: mergeAlignmentRecordsSingle(ar, i, j) for (1,1) (1,2) (2,1) (2,2): the four overlap shapes of :637-683 are one
+// program -- the earlier extended start leads alone, both to the earlier extended end, the later end trails.
+__constant__ Layout c_layout[N_LAYOUTS] = {
+    {{L_START(xAs1), L_TLT(0, 0, xBs1), L_OVL(0, 0, Ae1), L_TLT(1, 0, As2), L_SEAT(0, 1), L_OVL(1, 0, Be1), L_TLT(0, 1, Bs2), L_SEAT(1, 1),
+      L_OVL2(1, 1, xBe2, xAe2), L_FIN(xBe2, xAe2), L_END}, {0, As1, Bs1, Be2, Ae2, 1, 0}},
+    {{L_START(xAs1), L_TLT(0, 0, xBs1), L_OVL(0, 0, Ae1), L_TLT(1, 0, As2), L_SEAT(0, 1), L_OVL2(1, 0, xBe1, xAe2), L_FIN(xBe1, xAe2), L_END},
+     {0, As1, Bs1, Be1, Ae2, 0, 1}},
+    {{L_START(xBs1), L_TLT(1, 0, xAs2), L_OVL(1, 0, Be1), L_TLT(0, 1, Bs2), L_SEAT(1, 1), L_OVL2(1, 1, xBe2, xAe2), L_FIN(xBe2, xAe2), L_END},
+     {1, As2, Bs1, Be2, Ae2, 0, 0}},
+    {{L_START(xAs2), L_TLT(0, 1, xBs1), L_OVL(1, 0, Be1), L_TLT(0, 1, Bs2), L_SEAT(1, 1), L_OVL2(1, 1, xAe2, xBe2), L_FIN(xAe2, xBe2), L_END},
+     {1, As2, Bs1, Be2, Ae2, 0, 0}},
+    {{L_START(xAs1), L_TLT(0, 0, xBs1), L_OVL(0, 0, Be1), L_TLT(0, 0, Bs2), L_SEAT(1, 1), L_OVL(0, 1, Ae1), L_TLT(1, 1, As2), L_SEAT(0, 1),
+      L_OVL2(1, 1, xBe2, xAe2), L_FIN(xBe2, xAe2), L_END}, {0, As1, Bs1, Be2, Ae2, 1, 0}},
+    {{L_START(xAs1), L_TLT(0, 0, xBs1), L_OVL(0, 0, Be1), L_TLT(0, 0, Bs2), L_SEAT(1, 1), L_OVLQX(0, 1, xAe1, xBe2), L_FIN(xAe1, xBe2), L_END},
+     {0, As1, Bs1, Be2, Ae1, 0, 0}},
+    {{L_START(xBs1), L_TLT(1, 0, xAs1), L_OVL(0, 0, Ae1), L_TLT(1, 0, As2), L_SEAT(0, 1), L_OVL(1, 0, Be1), L_TLT(0, 1, Bs2), L_SEAT(1, 1),
+      L_OVL2(1, 1, xAe2, xBe2), L_FIN(xAe2, xBe2), L_END}, {0, As1, Bs1, Be2, Ae2, 1, 0}},
+    {{L_START(xBs1), L_TLT(1, 0, xAs1), L_OVL(0, 0, Ae1), L_TLT(1, 0, As2), L_SEAT(0, 1), L_OVL2(1, 0, xBe1, xAe2), L_FIN(xBe1, xAe2), L_END},
+     {0, As1, Bs1, Be1, Ae2, 0, 1}},
+    {{L_START(xAs1), L_TLT(0, 0, xBs2), L_OVL(0, 1, Ae1), L_TLT(1, 1, As2), L_SEAT(0, 1), L_OVL2(1, 1, xAe2, xBe2), L_FIN(xAe2, xBe2), L_END},
+     {1, Bs1, Bs2, Be2, Ae2, 0, 2}},
+    {{L_START(xBs2), L_TLT(1, 1, xAs1), L_OVL(0, 1, Ae1), L_TLT(1, 1, As2), L_SEAT(0, 1), L_OVL2(1, 1, xAe2, xBe2), L_FIN(xAe2, xBe2), L_END},
+     {1, Bs1, Bs2, Be2, Ae2, 0, 2}},
+    {{L_START(xBs1), L_TLT(1, 0, xAs1), L_OVL(0, 0, Be1), L_TLT(0, 0, Bs2), L_SEAT(1, 1), L_OVL(0, 1, Ae1), L_TLT(1, 1, As2), L_SEAT(0, 1),
+      L_OVL2(1, 1, xBe2, xAe2), L_FIN(xBe2, xAe2), L_END}, {0, As1, Bs1, Be2, Ae2, 1, 0}},
+    {{L_START(xBs1), L_TLT(1, 0, xAs1), L_OVL(0, 0, Be1), L_TLT(0, 0, Bs2), L_SEAT(1, 1), L_OVL2(0, 1, xAe1, xBe2), L_FIN(xAe1, xBe2), L_END},
+     {0, As1, Bs1, Be2, Ae1, 0, 0}},
+    {{L_START(xBs1), L_TLT(1, 0, xAs1), L_OVL(0, 0, Ae1), L_TLT(1, 0, As2), L_SEAT(0, 1), L_OVL2(1, 0, xAe2, xBe1), L_FIN(xAe2, xBe1), L_END},
+     {0, As1, Bs1, Be1, Ae2, 1, 0}},
+    {{L_START(xAs1), L_TLT(0, 0, xBs1), L_OVL(0, 0, Ae1), L_TLT(1, 0, As2), L_SEAT(0, 1), L_OVL2(1, 0, xAe2, xBe1), L_FIN(xAe2, xBe1), L_END},
+     {0, As1, Bs1, Be1, Ae2, 1, 0}},
+    {{L_START(xAs1), L_TLT(0, 0, xBs1), L_OVL(0, 0, Be1), L_TLT(0, 0, Bs2), L_SEAT(1, 1), L_OVL2(0, 1, xBe2, xAe1), L_FIN(xBe2, xAe1), L_END},
+     {0, As1, Bs1, Be2, Ae1, 1, 0}},
+    {{L_START(xBs1), L_TLT(1, 0, xAs1), L_OVL(0, 0, Be1), L_TLT(0, 0, Bs2), L_SEAT(1, 1), L_OVL2(0, 1, xBe2, xAe1), L_FIN(xBe2, xAe1), L_END},
+     {0, As1, Bs1, Be2, Ae1, 1, 0}},
+    // mergeAlignmentRecordsSingle(ar, i, j). Result: (1,1) -> segment 1, single_end = true (:685-697); (1,2) -> segment 2
+    // formed from start1 / end1, flag untouched (:698-709); (2,1), (2,2) -> segment 2, single_end = false (:710-729)
+    {{L_START_MIN(xAs1, xBs1), L_TLT(0, 0, xBs1), L_TLT(1, 0, xAs1), L_OVL2(0, 0, xAe1, xBe1), L_FIN(xAe1, xBe1), L_END}, {0, As1, Bs1, Ae1, Be1, 1, 0}},
+    {{L_START_MIN(xAs1, xBs2), L_TLT(0, 0, xBs2), L_TLT(1, 1, xAs1), L_OVL2(0, 1, xAe1, xBe2), L_FIN(xAe1, xBe2), L_END}, {1, As1, Bs2, Ae1, Be2, 2, 0}},
+    {{L_START_MIN(xAs2, xBs1), L_TLT(0, 1, xBs1), L_TLT(1, 0, xAs2), L_OVL2(1, 0, xAe2, xBe1), L_FIN(xAe2, xBe1), L_END}, {1, As2, Bs1, Ae2, Be1, 0, 0}},
+    {{L_START_MIN(xAs2, xBs2), L_TLT(0, 1, xBs2), L_TLT(1, 1, xAs2), L_OVL2(1, 1, xAe2, xBe2), L_FIN(xAe2, xBe2), L_END}, {1, As2, Bs2, Ae2, Be2, 0, 0}},
+};
+
 struct Seg {
     int start, end, n_ops, n_seq;
+    int lead, trail;                  // leading / trailing clip counts (computeOffset / computeRevOffset, :126-156)
+    int lead_h;                       // H ops among the leading clips (they consume no query)
+    int plain;                        // clips, M only, clips -- and the CIGAR consumes no more query than there is
     const uint8_t *cig, *seq, *qual;
 };
 
-struct Out {
-    uint8_t *cig, *seq, *qual;
-    int n_ops, n_seq;
+struct Rec { int single; Seg s[2]; };
+
+struct OutBuf { uint8_t *cig, *seq, *qual; int n_ops, n_seq; };
+
+struct Job { int lay, after; };       // after: 1 single_end := false, 2 segment 2 := ar.segment2 + false, 3 segment 1 := ar.segment1 + false
+
+__device__ __forceinline__ bool is_clip(uint8_t c) { return c == 'S' || c == 'H'; }
+
+// Facts of a segment that the folds need: one pass over the CIGAR by one lane. (The running record's facts follow from the
+// fold that made it.)
+__device__ void seg_facts(Seg& s) {
+    int lead = 0, lead_h = 0, trail = 0;
+    while (lead < s.n_ops && is_clip(s.cig[lead])) { lead_h += s.cig[lead] == 'H'; ++lead; }
+    while (trail < s.n_ops - lead && is_clip(s.cig[s.n_ops - 1 - trail])) ++trail;
+    if (lead == s.n_ops) trail = s.n_ops;               // clips only: computeRevOffset counts them all again
+    int plain = lead + trail <= s.n_ops, cons = 0;
+    for (int k = 0; k < s.n_ops; ++k) {
+        const uint8_t c = s.cig[k];
+        cons += (c == 'M' || c == 'I' || c == 'S');
+        if (k >= lead && k < s.n_ops - trail && c != 'M') plain = 0;
+    }
+    if (cons > s.n_seq) plain = 0;
+    s.lead = lead; s.trail = trail; s.lead_h = lead_h; s.plain = plain;
+}
+
+struct Walk {
+    const Seg* seg[2][2];
+    int c[2][2], q[2][2];
+    int v[16];
+    int ref;
+    OutBuf* o;
 };
 
-__device__ __forceinline__ bool clip(uint8_t c) { return c == 'S' || c == 'H'; }
-
-__device__ __forceinline__ void emit(Out& o, uint8_t op, uint8_t base, uint8_t qual) {
+__device__ __forceinline__ void put(OutBuf& o, uint8_t op, uint8_t base, uint8_t qual) {
     o.seq[o.n_seq] = base;
     o.qual[o.n_seq++] = qual;
     o.cig[o.n_ops++] = op;
 }
 
-// One column of a stretch only one read covers (noOverlapMerge).
-__device__ __forceinline__ int lone_column(const Seg& s, Out& o, int& c, int& q, int& ref) {
+// computeEntry (:169-184) from the byte tables. A char below '!' (the reference's own agreement of Q0 with Q62+ rounds to
+// 29..32) indexes rows the reference's table builders never fill: they read as 0 there (zero-initialised storage in the g++
+// build pinned under oracle/_ref; formally indeterminate), i.e. the update is '!'.
+__device__ __forceinline__ void entry(const uint8_t* tab, uint8_t b1, uint8_t q1, uint8_t b2, uint8_t q2, uint8_t& base, uint8_t& qual) {
+    const int k1 = (int)q1 - 33, k2 = (int)q2 - 33;
+    const int i1 = max(k1, 0), i2 = max(k2, 0);
+    if (b1 == b2) { base = b1; qual = tab[i1 * NQ + i2]; }
+    else if (k1 >= k2) { base = b1; qual = tab[NQ * NQ + i1 * NQ + i2]; }
+    else { base = b2; qual = tab[NQ * NQ + i2 * NQ + i1]; }
+    if ((k1 | k2) < 0) qual = 33;
+}
+
+// noOverlapMerge (:1539-1576), one column of (side, sg)
+__device__ int tail_step(Walk& w, int side, int sg) {
+    const Seg& s = *w.seg[side][sg];
+    int& c = w.c[side][sg]; int& q = w.q[side][sg];
     if (c >= s.n_ops) return HC_MERGE_OVERRUN;
     const uint8_t op = s.cig[c];
     if (op == 'M' || op == 'I') {
-        emit(o, op, s.seq[q], s.qual[q]);
-        ++q;
-        ref += (op == 'M');
-    } else if (op == 'D') {
-        o.cig[o.n_ops++] = 'D';
-        ++ref;
-    } else if (op == 'S') {
-        ++q;
-        ++ref;
-    } else if (op == 'H') {
-        ++ref;
-    } else {
-        return HC_MERGE_UNDEFINED;
-    }
-    ++c;
+        if (q >= s.n_seq) return HC_MERGE_OVERRUN;
+        put(*w.o, op, s.seq[q], s.qual[q]);
+        ++q; ++c;
+        w.ref += (op == 'M');
+    } else if (op == 'D') { w.o->cig[w.o->n_ops++] = 'D'; ++w.ref; ++c; }
+    else if (op == 'S') { ++w.ref; ++q; ++c; }
+    else if (op == 'H') { ++w.ref; ++c; }
+    else return HC_MERGE_UNDEFINED;
     return HC_MERGE_OK;
 }
 
-// One column both reads cover (overlapMerge). Op pairs the reference does not list end the merge as UNDEFINED.
-__device__ __forceinline__ int shared_column(const Seg& a, const Seg& b, Out& o, int& c1, int& c2, int& q1, int& q2, int& ref,
-                                             const uint8_t* tab) {
+// overlapMerge (:1578-1674), one step of this.segment sa against ar.segment sb; qa = the query cursor the call was given
+__device__ int ovl_step(Walk& w, int sa, int sb, int& qa, const uint8_t* tab) {
+    const Seg& a = *w.seg[0][sa]; const Seg& b = *w.seg[1][sb];
+    int& c1 = w.c[0][sa]; int& c2 = w.c[1][sb]; int& q2 = w.q[1][sb];
+    OutBuf& o = *w.o;
     if (c1 >= a.n_ops || c2 >= b.n_ops) return HC_MERGE_OVERRUN;
     const uint8_t x = a.cig[c1], y = b.cig[c2];
-    const bool xc = clip(x), yc = clip(y);
+    const bool xc = is_clip(x), yc = is_clip(y);
     if (x == y && (x == 'M' || x == 'I')) {
-        const uint8_t b1 = a.seq[q1], b2 = b.seq[q2];
-        const int k1 = a.qual[q1] - 33, k2 = b.qual[q2] - 33;
+        if (qa >= a.n_seq || q2 >= b.n_seq) return HC_MERGE_OVERRUN;
         uint8_t base, qual;
-        const int i1 = max(k1, 0), i2 = max(k2, 0);
-        if (b1 == b2) { base = b1; qual = tab[i1 * NQ + i2]; }
-        else if (k1 >= k2) { base = b1; qual = tab[NQ * NQ + i1 * NQ + i2]; }
-        else { base = b2; qual = tab[NQ * NQ + i2 * NQ + i1]; }
-        // computeEntry itself can hand back a char below '!': agreement of Q0 with Q62, 64, 68, 70, 73 rounds to -1..-4
-        // (29..32). When such a column is merged again the reference indexes table rows 0..32, which its builders never
-        // fill (:68-86 start at 33); they sit in zero-initialised static storage, so the update reads 0 -> '!'.
-        if ((k1 | k2) < 0) qual = 33;
-        emit(o, x, base, qual);
-        ref += (x == 'M');
-        ++q1; ++q2; ++c1; ++c2;
+        entry(tab, a.seq[qa], a.qual[qa], b.seq[q2], b.qual[q2], base, qual);
+        put(o, x, base, qual);
+        w.ref += (x == 'M');
+        ++qa; ++q2; ++c1; ++c2;
     } else if ((x == 'D' || xc) && (y == 'D' || yc)) {
-        // D/D, D/clip, clip/clip: a reference column without a merged base; it stays a deletion if either read has one
+        // D/D, D/clip, clip/clip: a reference column without a merged base; it stays a deletion if either read has one;
+        // an S consumes its read's query base
         if (x == 'D' || y == 'D') o.cig[o.n_ops++] = 'D';
-        q1 += (x == 'S');
+        qa += (x == 'S');
         q2 += (y == 'S');
-        ++ref; ++c1; ++c2;
+        ++w.ref; ++c1; ++c2;
     } else if (x == 'M' && yc) {
-        emit(o, 'M', a.seq[q1], a.qual[q1]);
-        ++q1;
-        q2 += (y == 'S');
-        ++ref; ++c1; ++c2;
+        if (qa >= a.n_seq) return HC_MERGE_OVERRUN;
+        put(o, 'M', a.seq[qa], a.qual[qa]);
+        ++qa; q2 += (y == 'S');
+        ++w.ref; ++c1; ++c2;
     } else if (xc && y == 'M') {
-        emit(o, 'M', b.seq[q2], b.qual[q2]);
-        ++q2;
-        q1 += (x == 'S');
-        ++ref; ++c1; ++c2;
+        if (q2 >= b.n_seq) return HC_MERGE_OVERRUN;
+        put(o, 'M', b.seq[q2], b.qual[q2]);
+        ++q2; qa += (x == 'S');
+        ++w.ref; ++c1; ++c2;
     } else if (x == 'I' && yc) {
-        emit(o, 'I', a.seq[q1], a.qual[q1]);
-        ++c1; ++q1;
+        if (qa >= a.n_seq) return HC_MERGE_OVERRUN;
+        put(o, 'I', a.seq[qa], a.qual[qa]);
+        ++c1; ++qa;
     } else if (xc && y == 'I') {
-        emit(o, 'I', b.seq[q2], b.qual[q2]);
+        if (q2 >= b.n_seq) return HC_MERGE_OVERRUN;
+        put(o, 'I', b.seq[q2], b.qual[q2]);
         ++c2; ++q2;
     } else {
         return HC_MERGE_UNDEFINED;
@@ -132,226 +252,645 @@ __device__ __forceinline__ int shared_column(const Seg& a, const Seg& b, Out& o,
     return HC_MERGE_OK;
 }
 
-__device__ int lead_clips(const Seg& s) { int k = 0; while (k < s.n_ops && clip(s.cig[k])) ++k; return k; }
-__device__ int trail_clips(const Seg& s) { int k = 0; while (k < s.n_ops && clip(s.cig[s.n_ops - 1 - k])) ++k; return k; }
+#define M_STEP(expr) do { const int rc_ = (expr); if (rc_) return rc_; } while (0)
 
-#define HC_STEP(expr) do { const int rc_ = (expr); if (rc_) return rc_; } while (0)
+__device__ void set_bounds(Walk& w, const Rec& A, const Rec& B) {
+    const Rec* r[2] = {&A, &B};
+#pragma unroll
+    for (int side = 0; side < 2; ++side)
+#pragma unroll
+        for (int sg = 0; sg < 2; ++sg) {
+            const Seg& s = r[side]->s[sg];
+            w.seg[side][sg] = &s;
+            w.c[side][sg] = w.q[side][sg] = 0;
+            w.v[MB(0, side, sg, 0)] = s.start; w.v[MB(0, side, sg, 1)] = s.end;
+            w.v[MB(1, side, sg, 0)] = s.start - s.lead; w.v[MB(1, side, sg, 1)] = s.end + s.trail;
+        }
+}
 
-// mergeAlignmentRecordsSingle(ar,1,1): a = the running super-read, b = the next member.
-__device__ int merge_pair(const Seg& a, const Seg& b, Out& o, const uint8_t* tab) {
-    int s1 = a.start - lead_clips(a), e1 = a.end + trail_clips(a);
-    int s2 = b.start - lead_clips(b), e2 = b.end + trail_clips(b);
-    int q1 = 0, q2 = 0, c1 = 0, c2 = 0;
-    o.n_ops = o.n_seq = 0;
-    // The earlier start leads alone, then both reads up to the earlier end, then the later end trails alone. Ties go the
-    // way the reference's four cases take them (:637, :649, :661, :673): equal starts -> a leads (no columns), equal
-    // ends -> b trails (no columns).
-    const bool a_leads = s1 <= s2, b_trails = e1 <= e2;
-    const int both_from = a_leads ? s2 : s1, both_to = b_trails ? e1 : e2, all_to = b_trails ? e2 : e1;
-    int ref = a_leads ? s1 : s2;
-    if (a_leads) { while (ref < both_from) HC_STEP(lone_column(a, o, c1, q1, ref)); }
-    else { while (ref < both_from) HC_STEP(lone_column(b, o, c2, q2, ref)); }
-    while (ref <= both_to) HC_STEP(shared_column(a, b, o, c1, c2, q1, q2, ref, tab));
-    if (b_trails) { while (ref <= all_to) HC_STEP(lone_column(b, o, c2, q2, ref)); }
-    else { while (ref <= all_to) HC_STEP(lone_column(a, o, c1, q1, ref)); }
+// One lane walks a layout exactly as the reference's loops do.
+__device__ int walk_layout(Walk& w, const Layout& L, const uint8_t* tab) {
+    for (int k = 0; k < 11; ++k) {
+        const Phase ph = L.ph[k];
+        switch (ph.op) {
+            case P_END: return HC_MERGE_OK;
+            case P_START: w.ref = w.v[ph.a]; break;
+            case P_START_MIN: w.ref = min(w.v[ph.a], w.v[ph.b]); break;
+            case P_TLT: while (w.ref < w.v[ph.a]) M_STEP(tail_step(w, ph.x, ph.y)); break;
+            case P_SEAT: {                                     // computeSOffset (:136-145)
+                const Seg& s = *w.seg[ph.x][ph.y];
+                for (int t = 0; t < s.n_ops; ++t) {
+                    if (s.cig[t] == 'S') { w.c[ph.x][ph.y]++; w.q[ph.x][ph.y]++; }
+                    else if (s.cig[t] == 'H') w.c[ph.x][ph.y]++;
+                    else break;
+                }
+                break;
+            }
+            case P_OVL: while (w.ref <= w.v[ph.a]) M_STEP(ovl_step(w, ph.x, ph.y, w.q[0][ph.x], tab)); break;
+            case P_OVL2: while (w.ref <= w.v[ph.a] && w.ref <= w.v[ph.b]) M_STEP(ovl_step(w, ph.x, ph.y, w.q[0][ph.x], tab)); break;
+            case P_OVLQX: while (w.ref <= w.v[ph.a] && w.ref <= w.v[ph.b]) M_STEP(ovl_step(w, ph.x, ph.y, w.q[0][1 - ph.x], tab)); break;
+            case P_FIN: {
+                int which = -1;
+                if (w.ref - 1 == w.v[ph.a]) which = ph.b; else if (w.ref - 1 == w.v[ph.b]) which = ph.a;
+                if (which >= 0) { const int sd = (which >> 2) & 1, sg = (which >> 1) & 1; while (w.ref <= w.v[which]) M_STEP(tail_step(w, sd, sg)); }
+                break;
+            }
+        }
+    }
     return HC_MERGE_OK;
 }
 
+// ---- plain folds in reference-column space, all 32 lanes ------------------------------------------------------------
+// For a plain segment the cursors are functions of the column: op index c = p - xs (xs = extended start), the op is a
+// clip outside [start, end] and M inside, and the query index is c - lead_h. A phase of the program is a column interval
+// [lo, hi); the columns that emit are those where a participating read shows M.
+struct PlainPhase { int lo, hi; int a, b; };     // a / b: reader (side*2 + seg), -1 = none
+
+// Number of columns in [lo, x) on which segment s shows M.
+__device__ __forceinline__ int m_before(const Seg& s, int lo, int x) { return max(0, min(x, s.end + 1) - max(lo, s.start)); }
+
+// Lists the phases of a layout as column intervals when every cursor stays consistent with the columns (plain segments, no
+// quirk). Returns the number of phases, or -1 when the layout has to be walked (a cursor would run off its CIGAR, the slip
+// layout, a cursor that does not stand on the running column when its phase begins).
+__device__ int plain_phases(const Walk& w, const Layout& L, PlainPhase* out) {
+    int n = 0, ref = 0;
+    int pos[2][2] = {{INT_MIN, INT_MIN}, {INT_MIN, INT_MIN}};     // column the cursor of (side, seg) stands on; MIN = untouched
+    for (int k = 0; k < 11; ++k) {
+        const Phase ph = L.ph[k];
+        if (ph.op == P_END) break;
+        if (ph.op == P_START) { ref = w.v[ph.a]; continue; }
+        if (ph.op == P_START_MIN) { ref = min(w.v[ph.a], w.v[ph.b]); continue; }
+        if (ph.op == P_SEAT) {
+            if (pos[ph.x][ph.y] != INT_MIN) return -1;
+            pos[ph.x][ph.y] = w.seg[ph.x][ph.y]->start;                  // past the leading clips
+            continue;
+        }
+        if (ph.op == P_OVLQX) return -1;
+        int hi, sa = -1, sb = -1;
+        if (ph.op == P_TLT) { hi = w.v[ph.a]; sa = ph.x * 2 + ph.y; }
+        else if (ph.op == P_OVL) { hi = w.v[ph.a] + 1; sa = ph.x; sb = 2 + ph.y; }
+        else if (ph.op == P_OVL2) { hi = min(w.v[ph.a], w.v[ph.b]) + 1; sa = ph.x; sb = 2 + ph.y; }
+        else {                                                           // P_FIN
+            int which = -1;
+            if (ref - 1 == w.v[ph.a]) which = ph.b; else if (ref - 1 == w.v[ph.b]) which = ph.a;
+            if (which < 0) continue;
+            hi = w.v[which] + 1;
+            sa = ((which >> 2) & 1) * 2 + ((which >> 1) & 1);
+        }
+        if (hi <= ref) continue;                                         // the loop does not run
+        for (int t = 0; t < 2; ++t) {
+            const int sx = t ? sb : sa;
+            if (sx < 0) continue;
+            const int side = sx >> 1, sg = sx & 1;
+            const Seg& s = *w.seg[side][sg];
+            if (pos[side][sg] == INT_MIN) pos[side][sg] = s.start - s.lead;   // cursor 0 = the extended start
+            if (pos[side][sg] != ref) return -1;
+            if (hi - 1 > s.end + s.trail) return -1;                     // would read past the CIGAR
+            pos[side][sg] = hi;
+        }
+        out[n].lo = ref; out[n].hi = hi; out[n].a = sa; out[n].b = sb;
+        ++n;
+        ref = hi;
+    }
+    return n;
+}
+
+// All lanes: the phases' columns, 32 at a time. Output slot of a column = emitting columns before it.
+__device__ void plain_emit(const Walk& w, const PlainPhase* ph, int n_ph, OutBuf& o, const uint8_t* tab, int lane) {
+    int base_out = 0;
+    for (int k = 0; k < n_ph; ++k) {
+        const PlainPhase P = ph[k];
+        const Seg* a = P.a >= 0 ? w.seg[P.a >> 1][P.a & 1] : nullptr;
+        const Seg* b = P.b >= 0 ? w.seg[P.b >> 1][P.b & 1] : nullptr;
+        // emitting columns: M of a or M of b -- two intervals, their union counted by inclusion / exclusion
+        auto emitted_before = [&](int x) -> int {
+            int e = a ? m_before(*a, P.lo, x) : 0;
+            if (b) {
+                e += m_before(*b, P.lo, x);
+                if (a) e -= max(0, min(min(x, a->end + 1), b->end + 1) - max(max(P.lo, a->start), b->start));
+            }
+            return e;
+        };
+        for (int p = P.lo + lane; p < P.hi; p += 32) {
+            const bool ma = a && p >= a->start && p <= a->end, mb = b && p >= b->start && p <= b->end;
+            if (!ma && !mb) continue;
+            uint8_t base, qual;
+            if (ma && mb) {
+                const int qa = p - (a->start - a->lead) - a->lead_h, qb = p - (b->start - b->lead) - b->lead_h;
+                entry(tab, a->seq[qa], a->qual[qa], b->seq[qb], b->qual[qb], base, qual);
+            } else {
+                const Seg* s = ma ? a : b;
+                const int q = p - (s->start - s->lead) - s->lead_h;
+                base = s->seq[q]; qual = s->qual[q];
+            }
+            const int slot = base_out + emitted_before(p);
+            o.cig[slot] = 'M'; o.seq[slot] = base; o.qual[slot] = qual;
+        }
+        base_out += emitted_before(P.hi);
+    }
+    o.n_ops = o.n_seq = base_out;
+}
+
 struct Batch {
+    const uint8_t* single_end;
     const int32_t *seg_start, *seg_end, *cig_len, *seq_len;
     const int64_t *cig_off, *seq_off;
     const uint8_t *cig, *seq, *qual;
-    const int64_t *member_off, *out_off;
+    const int64_t* member_off;
     const int32_t* members;
-    uint8_t *out_cig, *out_seq, *out_qual;   // caller-visible result, out_off[c] .. out_off[c+1]
-    uint8_t *tmp_cig, *tmp_seq, *tmp_qual;   // the other half of the ping-pong
-    hc_merged_info* info;
+    const int64_t* res_off;        // per clique: its capacity region in the result streams, 2 segments of cap = span / 2
+    const int64_t* scratch_off;    // per clique: 4 segment buffers of cap in the scratch streams (only where cap > kSegCap)
+    uint8_t *res_cig, *res_seq, *res_qual;
+    uint8_t *scr_cig, *scr_seq, *scr_qual;
+    hc_merged_record* info;
     const uint8_t* tab;
     int32_t n_cliques;
+    unsigned long long* counters;  // [0] folds evaluated in column space, [1] folds walked
 };
 
-__device__ __forceinline__ Seg load_seg(const Batch& B, int read) {
-    const int r = 2 * read;
-    return Seg{B.seg_start[r], B.seg_end[r], B.cig_len[r], B.seq_len[r], B.cig + B.cig_off[r], B.seq + B.seq_off[r], B.qual + B.seq_off[r]};
+__device__ __forceinline__ Seg load_seg(const Batch& B, int read, int sg, bool have) {
+    const int r = 2 * read + sg;
+    Seg s;
+    s.start = have ? B.seg_start[r] : 0; s.end = have ? B.seg_end[r] : 0;
+    s.n_ops = have ? B.cig_len[r] : 0; s.n_seq = have ? B.seq_len[r] : 0;
+    s.cig = B.cig + B.cig_off[r]; s.seq = B.seq + B.seq_off[r]; s.qual = B.qual + B.seq_off[r];
+    s.lead = s.trail = s.lead_h = 0; s.plain = 0;
+    return s;
 }
 
-__global__ void __launch_bounds__(128) merge_cliques_kernel(Batch B) {
-    __shared__ uint8_t tab[2 * NQ * NQ];
+// The layout(s) of one fold: AlignmentRecord's constructor dispatch (:233-242) and the branch heads of
+// mergeAlignmentRecordsPaired / Mixed. Returns the number of jobs (0: no paired layout matches, the record stays as it is).
+__device__ int pick_jobs(const Rec& acc, const Rec& mem, const int* v, Job* jobs) {
+    if (acc.single && mem.single) { jobs[0] = Job{LAY_SINGLE, 0}; return 1; }
+    if (!acc.single && !mem.single) {
+        if (v[Ae1] < v[Bs2] && v[As2] > v[Be1]) { jobs[0] = Job{LAY_SINGLE, 0}; jobs[1] = Job{LAY_SINGLE + 3, 0}; return 2; }   // :766
+        int k = -1;
+        if      (v[xAs1] <= v[xBs1] && v[Ae1] >= v[Bs1] && v[As2] <= v[Be1] && v[Ae2] >= v[Bs2]) k = 0;
+        else if (v[xAs1] <= v[xBs1] && v[Ae1] >= v[Bs1] && v[As2] <= v[Be1] && v[Ae2] <  v[Bs2]) k = 1;
+        else if (v[xBs1] <= v[xAs2] && v[Ae1] <  v[Bs1] && v[As2] <= v[Be1] && v[Ae2] >= v[Bs2]) k = 2;
+        else if (v[xAs2] <= v[xBs1] && v[Ae1] <  v[Bs1] && v[As2] <= v[Be1] && v[Ae2] >= v[Bs2]) k = 3;
+        else if (v[xAs1] <= v[xBs1] && v[As1] <= v[Be1] && v[Ae1] >= v[Bs2] && v[As2] <= v[Be2]) k = 4;
+        else if (v[xAs1] <= v[xBs1] && v[As2] >  v[Be2] && v[Ae1] >= v[Bs2] && v[As1] <= v[Be1]) k = 5;
+        else if (v[xBs1] <= v[xAs1] && v[Ae1] >= v[Bs1] && v[As2] <= v[Be1] && v[Ae2] >= v[Bs2]) k = 6;
+        else if (v[xBs1] <= v[xAs1] && v[Ae1] >= v[Bs1] && v[As2] <= v[Be1] && v[Ae2] <  v[Bs2]) k = 7;
+        else if (v[xAs1] <= v[xBs2] && v[As1] >  v[Be1] && v[Ae1] >= v[Bs2] && v[As2] <= v[Be2]) k = 8;
+        else if (v[xBs2] <= v[xAs1] && v[Be1] <  v[As1] && v[Ae1] >= v[Bs2] && v[As2] <= v[Be2]) k = 9;
+        else if (v[xBs1] <= v[xAs1] && v[As1] <= v[Be1] && v[Ae1] >= v[Bs2] && v[As2] <= v[Be2]) k = 10;
+        else if (v[xBs1] <= v[xAs1] && v[As2] >  v[Be2] && v[As1] <= v[Be1] && v[Ae1] >= v[Bs2]) k = 11;
+        if (k < 0) return 0;
+        jobs[0] = Job{k, 0};
+        return 1;
+    }
+    if (mem.single) {                                                    // this paired, ar single (:1296-1405)
+        if (v[Be1] < v[As2]) jobs[0] = Job{LAY_SINGLE, 1};
+        else if (v[Bs1] > v[Ae1]) jobs[0] = Job{LAY_SINGLE + 2, 0};
+        else jobs[0] = Job{LAY_PS0 + (v[xBs1] <= v[xAs1] ? 0 : 1), 0};
+        return 1;
+    }
+    if (v[Ae1] < v[Bs2]) jobs[0] = Job{LAY_SINGLE, 2};                   // this single, ar paired (:1406-1536)
+    else if (v[As1] > v[Be1]) jobs[0] = Job{LAY_SINGLE + 1, 3};
+    else jobs[0] = Job{LAY_SP0 + (v[xAs1] <= v[xBs1] ? 0 : 1), 0};
+    return 1;
+}
+
+// Dynamic shared memory: the two Phred tables, then per warp 4 segment buffers (segment x generation) of 3 byte streams.
+__global__ void __launch_bounds__(kWarps * 32) merge_cliques_kernel(Batch B) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint8_t* tab = smem;
     for (int i = threadIdx.x; i < 2 * NQ * NQ; i += blockDim.x) tab[i] = B.tab[i];
     __syncthreads();
-    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < B.n_cliques; c += gridDim.x * blockDim.x) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint8_t* slice = smem + kTabBytes + (size_t)warp * kSlice;
+    __shared__ Rec s_acc[kWarps], s_mem[kWarps];
+    __shared__ PlainPhase s_ph[kWarps][12];
+    __shared__ Job s_jobs[kWarps][2];
+    __shared__ int s_ctl[kWarps][4];
+    Rec& acc = s_acc[warp];
+    Rec& mem = s_mem[warp];
+    unsigned long long n_plain = 0, n_walk = 0;
+    for (int c = blockIdx.x * kWarps + warp; c < B.n_cliques; c += gridDim.x * kWarps) {
         const int64_t m0 = B.member_off[c];
         const int m = (int)(B.member_off[c + 1] - m0);
-        const int64_t o0 = B.out_off[c];
-        Out side[2] = {{B.out_cig + o0, B.out_seq + o0, B.out_qual + o0, 0, 0}, {B.tmp_cig + o0, B.tmp_seq + o0, B.tmp_qual + o0, 0, 0}};
-        Seg acc = load_seg(B, B.members[m0]);
+        const int64_t ro = B.res_off[c], cap = (B.res_off[c + 1] - ro) / 2;      // capacity of one segment
+        const bool in_smem = cap <= kSegCap;
+        const int64_t so = B.scratch_off[c];
+        auto buffer = [&](int sg, int gen) -> OutBuf {
+            OutBuf o;
+            if (in_smem) {
+                uint8_t* p = slice + (size_t)(sg * 2 + gen) * 3 * kSegCap;
+                o.cig = p; o.seq = p + kSegCap; o.qual = p + 2 * kSegCap;
+            } else {
+                const int64_t at = so + (int64_t)(sg * 2 + gen) * cap;
+                o.cig = B.scr_cig + at; o.seq = B.scr_seq + at; o.qual = B.scr_qual + at;
+            }
+            o.n_ops = o.n_seq = 0;
+            return o;
+        };
+        int gen[2] = {0, 0};
         int status = HC_MERGE_OK;
-        // fold f = 1..m-1 writes side (m-1-f)&1, so the last fold lands in the caller-visible region
+        if (lane == 0) {
+            const int r0 = B.members[m0];
+            acc.single = B.single_end[r0] != 0;
+            acc.s[0] = load_seg(B, r0, 0, true);
+            acc.s[1] = load_seg(B, r0, 1, !acc.single);
+            seg_facts(acc.s[0]);
+            seg_facts(acc.s[1]);
+        }
+        __syncwarp();
         for (int f = 1; f < m && status == HC_MERGE_OK; ++f) {
-            const Seg b = load_seg(B, B.members[m0 + f]);
-            Out& o = side[(m - 1 - f) & 1];
-            status = merge_pair(acc, b, o, tab);
-            acc.start = min(acc.start, b.start);   // :686-687
-            acc.end = max(acc.end, b.end);
-            acc.n_ops = o.n_ops;
-            acc.n_seq = o.n_seq;
-            acc.cig = o.cig; acc.seq = o.seq; acc.qual = o.qual;
+            if (lane == 0) {
+                const int r = B.members[m0 + f];
+                mem.single = B.single_end[r] != 0;
+                mem.s[0] = load_seg(B, r, 0, true);
+                mem.s[1] = load_seg(B, r, 1, !mem.single);
+                seg_facts(mem.s[0]);
+                seg_facts(mem.s[1]);
+                Walk w0;
+                set_bounds(w0, acc, mem);
+                s_ctl[warp][3] = pick_jobs(acc, mem, w0.v, s_jobs[warp]);
+            }
+            __syncwarp();
+            const int n_jobs = s_ctl[warp][3];
+            for (int job = 0; job < n_jobs && status == HC_MERGE_OK; ++job) {
+                const int lay = s_jobs[warp][job].lay, after = s_jobs[warp][job].after;
+                const Layout& L = c_layout[lay];
+                const int tgt = L.res.seg;
+                OutBuf o = buffer(tgt, gen[tgt] ^ 1);
+                Walk w;
+                set_bounds(w, acc, mem);
+                // ---- plain folds: all lanes, column space; anything else: lane 0 walks it
+                if (lane == 0) {
+                    bool all_plain = true;
+                    for (int k = 0; k < 11 && L.ph[k].op != P_END; ++k) {
+                        const Phase ph = L.ph[k];
+                        if (ph.op == P_TLT || ph.op == P_SEAT) all_plain &= w.seg[ph.x][ph.y]->plain != 0;
+                        else if (ph.op == P_OVL || ph.op == P_OVL2 || ph.op == P_OVLQX) all_plain &= w.seg[0][ph.x]->plain != 0 && w.seg[1][ph.y]->plain != 0;
+                    }
+                    s_ctl[warp][2] = all_plain ? plain_phases(w, L, s_ph[warp]) : -1;
+                }
+                __syncwarp();
+                const int n_ph = s_ctl[warp][2];
+                int rc = HC_MERGE_OK;
+                if (n_ph >= 0) {
+                    plain_emit(w, s_ph[warp], n_ph, o, tab, lane);
+                    n_plain += lane == 0;
+                } else {
+                    __syncwarp();
+                    if (lane == 0) {
+                        w.o = &o;
+                        s_ctl[warp][2] = walk_layout(w, L, tab);
+                        s_ctl[warp][0] = o.n_ops; s_ctl[warp][1] = o.n_seq;
+                    }
+                    __syncwarp();
+                    rc = s_ctl[warp][2];
+                    o.n_ops = s_ctl[warp][0]; o.n_seq = s_ctl[warp][1];
+                    n_walk += lane == 0;
+                }
+                __syncwarp();
+                if (rc != HC_MERGE_OK) { status = rc; break; }
+                // ---- the result rule: lane 0 updates the running record
+                if (lane == 0) {
+                    const Result rs = L.res;
+                    if (rs.take == 2) acc.s[0] = mem.s[0];
+                    Seg& t = acc.s[tgt];
+                    t.start = min(w.v[rs.sa], w.v[rs.sb]); t.end = max(w.v[rs.ea], w.v[rs.eb]);
+                    t.n_ops = o.n_ops; t.n_seq = o.n_seq;
+                    t.cig = o.cig; t.seq = o.seq; t.qual = o.qual;
+                    t.lead = t.trail = t.lead_h = 0;                     // merges drop the clips
+                    int plain = 1;
+                    if (n_ph < 0) for (int k = 0; k < t.n_ops; ++k) plain &= t.cig[k] == 'M';
+                    t.plain = plain;
+                    if (rs.single != 2) acc.single = rs.single;
+                    if (rs.take == 1) acc.s[1] = mem.s[1];
+                    if (after == 1) acc.single = 0;
+                    if (after == 2) { acc.s[1] = mem.s[1]; acc.single = 0; }
+                    if (after == 3) { acc.s[0] = mem.s[0]; acc.single = 0; }
+                }
+                gen[tgt] ^= 1;
+                __syncwarp();
+            }
         }
-        if (m == 1) {   // the reference asserts size > 1 (:213); a lone member is copied through
-            for (int k = 0; k < acc.n_ops; ++k) side[0].cig[k] = acc.cig[k];
-            acc.n_seq = min(acc.n_seq, acc.n_ops);      // the slot is sized from the CIGAR length
-            for (int k = 0; k < acc.n_seq; ++k) { side[0].seq[k] = acc.seq[k]; side[0].qual[k] = acc.qual[k]; }
+        // ---- the record goes out: header by lane 0, the streams by all lanes
+        __syncwarp();
+        if (lane == 0) {
+            hc_merged_record r;
+            memset(&r, 0, sizeof r);
+            r.status = status;
+            if (status == HC_MERGE_OK) {
+                r.single_end = acc.single;
+                for (int sg = 0; sg < (acc.single ? 1 : 2); ++sg) {
+                    r.start[sg] = acc.s[sg].start; r.end[sg] = acc.s[sg].end;
+                    r.n_ops[sg] = min(acc.s[sg].n_ops, (int)cap); r.n_seq[sg] = min(acc.s[sg].n_seq, (int)cap);
+                }
+            }
+            B.info[c] = r;
         }
-        hc_merged_info r;
-        r.status = status;
-        r.start = status ? 0 : acc.start;
-        r.end = status ? 0 : acc.end;
-        r.n_ops = status ? 0 : acc.n_ops;
-        r.n_seq = status ? 0 : acc.n_seq;
-        B.info[c] = r;
+        if (status == HC_MERGE_OK) {
+            for (int sg = 0; sg < (acc.single ? 1 : 2); ++sg) {
+                const Seg& s = acc.s[sg];
+                const int no = min(s.n_ops, (int)cap), ns = min(s.n_seq, (int)cap);
+                uint8_t* dc = B.res_cig + ro + sg * cap; uint8_t* ds = B.res_seq + ro + sg * cap; uint8_t* dq = B.res_qual + ro + sg * cap;
+                for (int k = lane; k < no; k += 32) dc[k] = s.cig[k];
+                for (int k = lane; k < ns; k += 32) { ds[k] = s.seq[k]; dq[k] = s.qual[k]; }
+            }
+        }
+        __syncwarp();
     }
+    if (lane == 0 && B.counters) { atomicAdd(&B.counters[0], n_plain); atomicAdd(&B.counters[1], n_walk); }
 }
 
-struct DevBuf {
-    void* p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
-    cudaError_t put(const void* src, size_t bytes, cudaStream_t s) {
-        cudaError_t e = cudaMalloc(&p, bytes ? bytes : 1);
-        if (e != cudaSuccess) return e;
-        return bytes ? cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess;
+// Compaction: record c's bytes move from its capacity region to their final offsets (a warp per record).
+__global__ void compact_kernel(const hc_merged_record* __restrict__ info, const int64_t* __restrict__ res_off, const int64_t* __restrict__ ops_at,
+                               const int64_t* __restrict__ seq_at, const uint8_t* __restrict__ res_cig, const uint8_t* __restrict__ res_seq,
+                               const uint8_t* __restrict__ res_qual, uint8_t* __restrict__ out_cig, uint8_t* __restrict__ out_seq,
+                               uint8_t* __restrict__ out_qual, int n_cliques) {
+    const int lane = threadIdx.x & 31;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    for (int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; c < n_cliques; c += warps) {
+        const hc_merged_record r = info[c];
+        if (r.status != HC_MERGE_OK) continue;
+        const int64_t ro = res_off[c], rcap = (res_off[c + 1] - ro) / 2;
+        int64_t oa = ops_at[c], sa = seq_at[c];
+        for (int sg = 0; sg < (r.single_end ? 1 : 2); ++sg) {
+            for (int k = lane; k < r.n_ops[sg]; k += 32) out_cig[oa + k] = res_cig[ro + sg * rcap + k];
+            for (int k = lane; k < r.n_seq[sg]; k += 32) { out_seq[sa + k] = res_seq[ro + sg * rcap + k]; out_qual[sa + k] = res_qual[ro + sg * rcap + k]; }
+            oa += r.n_ops[sg]; sa += r.n_seq[sg];
+        }
     }
-    cudaError_t make(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 1); }
-};
+}
 
 int fail(int code, const std::string& msg) {
     hc::set_global_error(msg);
     return code;
 }
 
-int check_batch(const hc_reads* reads, int32_t n_cliques, const int64_t* member_off, const int32_t* members) {
-    if (!reads || n_cliques < 0 || (n_cliques > 0 && (!member_off || !members))) return fail(HC_E_INVALID, "hc_merge: null argument");
-    for (int c = 0; c < n_cliques; ++c) {
-        if (member_off[c + 1] <= member_off[c]) return fail(HC_E_INVALID, "hc_merge: empty clique");
-        for (int64_t k = member_off[c]; k < member_off[c + 1]; ++k) {
-            const int r = members[k];
-            if (r < 0 || r >= reads->n) return fail(HC_E_INVALID, "hc_merge: member index out of range");
-            if (!reads->single_end[r]) return fail(HC_E_INVALID, "hc_merge_cliques_se: paired-end member (only single-end cliques are built)");
-            const int nc = reads->cig_len[2 * r], nq = reads->seq_len[2 * r];
-            if (nc < 0 || nq < 0) return fail(HC_E_INVALID, "hc_merge: negative CIGAR / sequence length");
-            const uint8_t* cg = reads->cig + reads->cig_off[2 * r];
-            int consumed = 0;
-            for (int i = 0; i < nc; ++i) consumed += (cg[i] == 'M' || cg[i] == 'I' || cg[i] == 'S');
-            if (consumed > nq) return fail(HC_E_INVALID, "hc_merge: CIGAR consumes more query bases than the read has");
-            const uint8_t* q = reads->qual + reads->seq_off[2 * r];
-            for (int i = 0; i < nq; ++i)
-                if (q[i] < 33 || q[i] > 126) return fail(HC_E_INVALID, "hc_merge: quality char outside 33..126");
-        }
-    }
+}  // namespace
+
+struct hc_merger {
+    int device = 0, sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    // the read set (hc_merger_set_reads)
+    int n_reads = 0;
+    std::vector<uint8_t> single_end;
+    std::vector<int32_t> cig_len;
+    uint8_t* d_single = nullptr; int32_t *d_start = nullptr, *d_end = nullptr, *d_clen = nullptr, *d_slen = nullptr;
+    int64_t *d_coff = nullptr, *d_soff = nullptr;
+    uint8_t *d_cig = nullptr, *d_seq = nullptr, *d_qual = nullptr, *d_tab = nullptr;
+    size_t cap_single = 0, cap_start = 0, cap_end = 0, cap_clen = 0, cap_slen = 0, cap_coff = 0, cap_soff = 0, cap_cig = 0, cap_seq = 0, cap_qual = 0;
+    // per batch of cliques (grow-only)
+    int64_t *d_moff = nullptr, *d_resoff = nullptr, *d_scroff = nullptr, *d_opsat = nullptr, *d_seqat = nullptr; int32_t* d_members = nullptr;
+    hc_merged_record* d_info = nullptr;
+    uint8_t *d_scratch = nullptr, *d_res = nullptr, *d_out = nullptr;
+    unsigned long long* d_counters = nullptr;
+    size_t cap_moff = 0, cap_resoff = 0, cap_scroff = 0, cap_opsat = 0, cap_seqat = 0, cap_info = 0, cap_mem = 0, cap_scratch = 0, cap_res = 0, cap_out = 0;
+    int64_t out_ops = 0, out_seq = 0;
+    bool have_result = false;
+    unsigned long long folds_plain = 0, folds_walked = 0;
+    std::string err;
+};
+
+namespace {
+#define MG_TRY(m, call)                                                                        \
+    do {                                                                                       \
+        cudaError_t e__ = (call);                                                              \
+        if (e__ != cudaSuccess) {                                                              \
+            (m)->err = std::string(#call) + ": " + cudaGetErrorString(e__);                    \
+            hc::set_global_error((m)->err);                                                    \
+            return HC_E_CUDA;                                                                  \
+        }                                                                                      \
+    } while (0)
+
+template <class T>
+int mgrow(hc_merger* m, T*& p, size_t& cap, size_t need) {
+    if (need <= cap && p) return HC_OK;
+    if (p) MG_TRY(m, cudaFree(p));
+    p = nullptr; cap = 0;
+    const size_t n = std::max<size_t>(need + need / 8, 256);
+    MG_TRY(m, cudaMalloc(reinterpret_cast<void**>(&p), n * sizeof(T)));
+    cap = n;
     return HC_OK;
 }
-
+int bad_arg(hc_merger* m, const char* msg) { m->err = msg; return fail(HC_E_INVALID, msg); }
 }  // namespace
 
 extern "C" {
 
-int hc_merge_layout(const hc_reads* reads, int32_t n_cliques, const int64_t* member_off, const int32_t* members, int64_t* out_off) {
-    int rc = check_batch(reads, n_cliques, member_off, members);
-    if (rc != HC_OK) return rc;
-    if (!out_off) return fail(HC_E_INVALID, "hc_merge_layout: null out_off");
-    int64_t at = 0;
-    for (int c = 0; c < n_cliques; ++c) {
-        out_off[c] = at;
-        int64_t cap = 0;
-        for (int64_t k = member_off[c]; k < member_off[c + 1]; ++k) cap += reads->cig_len[2 * members[k]];
-        at += (cap + 15) & ~(int64_t)15;
+int hc_merger_create(int32_t device, hc_merger** out) {
+    if (!out) return fail(HC_E_INVALID, "hc_merger_create: null argument");
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(HC_E_CUDA, "hc_merger_create: no CUDA device (there is no CPU merging path)");
     }
-    out_off[n_cliques] = at;
+    if (device < 0 || device >= ndev) return fail(HC_E_INVALID, "hc_merger_create: bad device ordinal");
+    hc_merger* m = new hc_merger();
+    m->device = device;
+    auto bad = [&](cudaError_t e) { hc::set_global_error(std::string("hc_merger_create: ") + cudaGetErrorString(e)); hc_merger_destroy(m); return HC_E_CUDA; };
+    cudaError_t e;
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bad(e);
+    if ((e = cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) return bad(e);
+    if ((e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking)) != cudaSuccess) return bad(e);
+    if ((e = cudaEventCreate(&m->e0)) != cudaSuccess) return bad(e);
+    if ((e = cudaEventCreate(&m->e1)) != cudaSuccess) return bad(e);
+    std::vector<uint8_t> tab(2 * NQ * NQ);
+    build_phred_tables(tab.data());
+    if ((e = cudaMalloc((void**)&m->d_tab, tab.size())) != cudaSuccess) return bad(e);
+    if ((e = cudaMemcpy(m->d_tab, tab.data(), tab.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return bad(e);
+    if ((e = cudaMalloc((void**)&m->d_counters, 2 * sizeof(unsigned long long))) != cudaSuccess) return bad(e);
+    *out = m;
     return HC_OK;
 }
 
-int hc_merge_cliques_se(int32_t device, const hc_reads* reads, int32_t n_cliques, const int64_t* member_off, const int32_t* members,
-                        const int64_t* out_off, uint8_t* out_cig, uint8_t* out_seq, uint8_t* out_qual, hc_merged_info* info,
-                        float* kernel_ms) {
-    int rc = check_batch(reads, n_cliques, member_off, members);
-    if (rc != HC_OK) return rc;
-    if (n_cliques == 0) return HC_OK;
-    if (!out_off || !out_cig || !out_seq || !out_qual || !info) return fail(HC_E_INVALID, "hc_merge_cliques_se: null output");
-    {   // the caller's out_off must leave every clique the room hc_merge_layout gives it
-        std::vector<int64_t> want((size_t)n_cliques + 1);
-        if ((rc = hc_merge_layout(reads, n_cliques, member_off, members, want.data())) != HC_OK) return rc;
-        for (int c = 0; c < n_cliques; ++c)
-            if (out_off[c] < 0 || out_off[c + 1] - out_off[c] < want[c + 1] - want[c])
-                return fail(HC_E_INVALID, "hc_merge_cliques_se: out_off leaves a clique less room than hc_merge_layout");
-    }
-    int ndev = 0;
-    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
-        return fail(HC_E_CUDA, "hc_merge_cliques_se: no such CUDA device (there is no CPU merging path)");
-#define MG_TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { if (stream) cudaStreamDestroy(stream); \
-        return fail(HC_E_CUDA, std::string("hc_merge_cliques_se: ") + cudaGetErrorString(e_)); } } while (0)
-    cudaStream_t stream = nullptr;
-    MG_TRY(cudaSetDevice(device));
-    MG_TRY(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-    const int n = reads->n;
-    // bytes of the three char streams actually referenced
+void hc_merger_destroy(hc_merger* m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    cudaFree(m->d_single); cudaFree(m->d_start); cudaFree(m->d_end); cudaFree(m->d_clen); cudaFree(m->d_slen); cudaFree(m->d_coff); cudaFree(m->d_soff);
+    cudaFree(m->d_cig); cudaFree(m->d_seq); cudaFree(m->d_qual); cudaFree(m->d_tab); cudaFree(m->d_moff); cudaFree(m->d_resoff); cudaFree(m->d_scroff);
+    cudaFree(m->d_opsat); cudaFree(m->d_seqat); cudaFree(m->d_members); cudaFree(m->d_info); cudaFree(m->d_scratch); cudaFree(m->d_res); cudaFree(m->d_out);
+    cudaFree(m->d_counters);
+    if (m->e0) cudaEventDestroy(m->e0);
+    if (m->e1) cudaEventDestroy(m->e1);
+    if (m->stream) cudaStreamDestroy(m->stream);
+    delete m;
+}
+
+const char* hc_merger_last_error(const hc_merger* m) { return m ? m->err.c_str() : hc::global_error(); }
+
+int hc_merger_set_reads(hc_merger* m, const hc_reads* rd) {
+    if (!m) return fail(HC_E_INVALID, "hc_merger_set_reads: null merger");
+    if (!rd || rd->n < 0) return bad_arg(m, "hc_merger_set_reads: bad argument");
+    const int n = rd->n;
     int64_t cig_bytes = 0, seq_bytes = 0;
-    for (int r = 0; r < 2 * n; ++r) {
-        cig_bytes = std::max<int64_t>(cig_bytes, reads->cig_off[r] + reads->cig_len[r]);
-        seq_bytes = std::max<int64_t>(seq_bytes, reads->seq_off[r] + reads->seq_len[r]);
+    for (int r = 0; r < n; ++r)
+        for (int s = 0; s < (rd->single_end[r] ? 1 : 2); ++s) {
+            const int k = 2 * r + s;
+            const int nc = rd->cig_len[k], nq = rd->seq_len[k];
+            if (nc < 0 || nq < 0 || rd->cig_off[k] < 0 || rd->seq_off[k] < 0) return bad_arg(m, "hc_merger_set_reads: negative length or offset");
+            cig_bytes = std::max<int64_t>(cig_bytes, rd->cig_off[k] + nc);
+            seq_bytes = std::max<int64_t>(seq_bytes, rd->seq_off[k] + nq);
+        }
+    // quality chars: the update tables cover 33..126. Chars below '!' are what computeEntry itself can emit (super-reads of
+    // an earlier round) and are accepted; above 126 is refused. CIGAR ops outside MIDSH are refused.
+    int bad = 0;
+    hc::parallel_ranges(n, 4096, [&](int r0, int r1) {
+        int mine = 0;
+        for (int r = r0; r < r1 && !mine; ++r)
+            for (int s = 0; s < (rd->single_end[r] ? 1 : 2); ++s) {
+                const int k = 2 * r + s;
+                const uint8_t* q = rd->qual + rd->seq_off[k];
+                for (int i = 0; i < rd->seq_len[k]; ++i) if (q[i] > 126) mine = 1;
+                const uint8_t* cg = rd->cig + rd->cig_off[k];
+                for (int i = 0; i < rd->cig_len[k]; ++i)
+                    if (cg[i] != 'M' && cg[i] != 'I' && cg[i] != 'D' && cg[i] != 'S' && cg[i] != 'H') mine = 2;
+            }
+        if (mine) bad = mine;
+    });
+    if (bad == 1) return bad_arg(m, "hc_merger_set_reads: quality char above 126");
+    if (bad == 2) return bad_arg(m, "hc_merger_set_reads: CIGAR op outside MIDSH");
+    MG_TRY(m, cudaSetDevice(m->device));
+    MG_TRY(m, cudaStreamSynchronize(m->stream));
+    m->have_result = false;
+    int rc;
+    const size_t n2 = (size_t)std::max(2 * n, 2);
+    if ((rc = mgrow(m, m->d_single, m->cap_single, n2)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_start, m->cap_start, n2)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_end, m->cap_end, n2)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_clen, m->cap_clen, n2)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_slen, m->cap_slen, n2)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_coff, m->cap_coff, n2)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_soff, m->cap_soff, n2)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_cig, m->cap_cig, (size_t)cig_bytes + 16)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_seq, m->cap_seq, (size_t)seq_bytes + 16)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_qual, m->cap_qual, (size_t)seq_bytes + 16)) != HC_OK) return rc;
+    MG_TRY(m, cudaMemcpyAsync(m->d_single, rd->single_end, (size_t)n, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_start, rd->seg_start, sizeof(int32_t) * 2 * n, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_end, rd->seg_end, sizeof(int32_t) * 2 * n, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_clen, rd->cig_len, sizeof(int32_t) * 2 * n, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_slen, rd->seq_len, sizeof(int32_t) * 2 * n, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_coff, rd->cig_off, sizeof(int64_t) * 2 * n, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_soff, rd->seq_off, sizeof(int64_t) * 2 * n, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_cig, rd->cig, (size_t)cig_bytes, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_seq, rd->seq, (size_t)seq_bytes, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_qual, rd->qual, (size_t)seq_bytes, cudaMemcpyHostToDevice, m->stream));
+    m->n_reads = n;
+    m->single_end.assign(rd->single_end, rd->single_end + n);
+    m->cig_len.assign(rd->cig_len, rd->cig_len + 2 * (size_t)n);
+    MG_TRY(m, cudaStreamSynchronize(m->stream));
+    return HC_OK;
+}
+
+int hc_merge_run(hc_merger* m, int32_t n_cliques, const int64_t* member_off, const int32_t* members, hc_merged_record* info,
+                 int64_t* total_ops, int64_t* total_seq, float* kernel_ms) {
+    if (!m) return fail(HC_E_INVALID, "hc_merge_run: null merger");
+    if (n_cliques < 0 || (n_cliques > 0 && (!member_off || !members || !info))) return bad_arg(m, "hc_merge_run: null argument");
+    if (!m->d_cig) { m->err = "hc_merge_run: no read set (hc_merger_set_reads)"; return fail(HC_E_STATE, m->err); }
+    m->have_result = false;
+    if (total_ops) *total_ops = 0;
+    if (total_seq) *total_seq = 0;
+    if (kernel_ms) *kernel_ms = 0.f;
+    if (n_cliques == 0) { m->out_ops = m->out_seq = 0; m->have_result = true; return HC_OK; }
+    // capacity of one segment of clique c: the members' CIGAR lengths summed (a merged segment cannot be longer)
+    std::vector<int64_t> resoff((size_t)n_cliques + 1), scroff((size_t)n_cliques + 1);
+    int64_t rat = 0, sat = 0;
+    for (int c = 0; c < n_cliques; ++c) {
+        if (member_off[c + 1] <= member_off[c]) return bad_arg(m, "hc_merge_run: empty clique");
+        int64_t cap = 0;
+        for (int64_t k = member_off[c]; k < member_off[c + 1]; ++k) {
+            const int r = members[k];
+            if (r < 0 || r >= m->n_reads) return bad_arg(m, "hc_merge_run: member index out of range");
+            cap += m->cig_len[2 * (size_t)r] + (m->single_end[r] ? 0 : m->cig_len[2 * (size_t)r + 1]);
+        }
+        cap = std::max<int64_t>(16, (cap + 15) & ~(int64_t)15);
+        resoff[c] = rat; scroff[c] = sat;
+        rat += 2 * cap;
+        sat += cap > kSegCap ? 4 * cap : 0;                // global scratch only where shared memory cannot hold the running record
     }
-    const int64_t n_members = member_off[n_cliques], out_bytes = out_off[n_cliques];
-    std::vector<uint8_t> tab(2 * NQ * NQ);
-    build_phred_tables(tab.data());
-    DevBuf d_start, d_end, d_clen, d_slen, d_coff, d_soff, d_cig, d_seq, d_qual, d_moff, d_mem, d_ooff, d_tab, d_oc, d_os, d_oq, d_tc, d_ts, d_tq, d_info;
-    MG_TRY(d_start.put(reads->seg_start, sizeof(int32_t) * 2 * n, stream));
-    MG_TRY(d_end.put(reads->seg_end, sizeof(int32_t) * 2 * n, stream));
-    MG_TRY(d_clen.put(reads->cig_len, sizeof(int32_t) * 2 * n, stream));
-    MG_TRY(d_slen.put(reads->seq_len, sizeof(int32_t) * 2 * n, stream));
-    MG_TRY(d_coff.put(reads->cig_off, sizeof(int64_t) * 2 * n, stream));
-    MG_TRY(d_soff.put(reads->seq_off, sizeof(int64_t) * 2 * n, stream));
-    MG_TRY(d_cig.put(reads->cig, (size_t)cig_bytes, stream));
-    MG_TRY(d_seq.put(reads->seq, (size_t)seq_bytes, stream));
-    MG_TRY(d_qual.put(reads->qual, (size_t)seq_bytes, stream));
-    MG_TRY(d_moff.put(member_off, sizeof(int64_t) * ((size_t)n_cliques + 1), stream));
-    MG_TRY(d_mem.put(members, sizeof(int32_t) * (size_t)n_members, stream));
-    MG_TRY(d_ooff.put(out_off, sizeof(int64_t) * ((size_t)n_cliques + 1), stream));
-    MG_TRY(d_tab.put(tab.data(), tab.size(), stream));
-    MG_TRY(d_oc.make((size_t)out_bytes)); MG_TRY(d_os.make((size_t)out_bytes)); MG_TRY(d_oq.make((size_t)out_bytes));
-    MG_TRY(d_tc.make((size_t)out_bytes)); MG_TRY(d_ts.make((size_t)out_bytes)); MG_TRY(d_tq.make((size_t)out_bytes));
-    MG_TRY(d_info.make(sizeof(hc_merged_info) * (size_t)n_cliques));
+    resoff[n_cliques] = rat; scroff[n_cliques] = sat;
+    MG_TRY(m, cudaSetDevice(m->device));
+    int rc;
+    const int64_t n_members = member_off[n_cliques];
+    const size_t nc1 = (size_t)n_cliques + 1;
+    if ((rc = mgrow(m, m->d_moff, m->cap_moff, nc1)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_resoff, m->cap_resoff, nc1)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_scroff, m->cap_scroff, nc1)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_opsat, m->cap_opsat, nc1)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_seqat, m->cap_seqat, nc1)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_info, m->cap_info, nc1)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_members, m->cap_mem, (size_t)n_members)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_scratch, m->cap_scratch, (size_t)sat * 3 + 64)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_res, m->cap_res, (size_t)rat * 3 + 64)) != HC_OK) return rc;
+    MG_TRY(m, cudaMemcpyAsync(m->d_moff, member_off, sizeof(int64_t) * nc1, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_members, members, sizeof(int32_t) * (size_t)n_members, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_resoff, resoff.data(), sizeof(int64_t) * nc1, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_scroff, scroff.data(), sizeof(int64_t) * nc1, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemsetAsync(m->d_counters, 0, 2 * sizeof(unsigned long long), m->stream));
     Batch B{};
-    B.seg_start = (const int32_t*)d_start.p; B.seg_end = (const int32_t*)d_end.p;
-    B.cig_len = (const int32_t*)d_clen.p; B.seq_len = (const int32_t*)d_slen.p;
-    B.cig_off = (const int64_t*)d_coff.p; B.seq_off = (const int64_t*)d_soff.p;
-    B.cig = (const uint8_t*)d_cig.p; B.seq = (const uint8_t*)d_seq.p; B.qual = (const uint8_t*)d_qual.p;
-    B.member_off = (const int64_t*)d_moff.p; B.out_off = (const int64_t*)d_ooff.p; B.members = (const int32_t*)d_mem.p;
-    B.out_cig = (uint8_t*)d_oc.p; B.out_seq = (uint8_t*)d_os.p; B.out_qual = (uint8_t*)d_oq.p;
-    B.tmp_cig = (uint8_t*)d_tc.p; B.tmp_seq = (uint8_t*)d_ts.p; B.tmp_qual = (uint8_t*)d_tq.p;
-    B.info = (hc_merged_info*)d_info.p; B.tab = (const uint8_t*)d_tab.p; B.n_cliques = n_cliques;
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    MG_TRY(cudaEventCreate(&e0));
-    MG_TRY(cudaEventCreate(&e1));
-    // Resident CTAs per SM bound the number of cliques in flight, hence the ping-pong working set that has to live in L2
-    // (HC_MERGE_BLOCKS_PER_SM overrides, 1..16; measurements in DESIGN.md 4.5).
-    int sm_count = 148, per_sm = 8;
-    MG_TRY(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
-    if (const char* e = std::getenv("HC_MERGE_BLOCKS_PER_SM")) per_sm = std::max(1, std::min(16, std::atoi(e)));
-    const int blocks = std::max(1, std::min((n_cliques + 127) / 128, sm_count * per_sm));
-    MG_TRY(cudaEventRecord(e0, stream));
-    merge_cliques_kernel<<<blocks, 128, 0, stream>>>(B);
-    MG_TRY(cudaGetLastError());
-    MG_TRY(cudaEventRecord(e1, stream));
-    MG_TRY(cudaMemcpyAsync(out_cig, d_oc.p, (size_t)out_bytes, cudaMemcpyDeviceToHost, stream));
-    MG_TRY(cudaMemcpyAsync(out_seq, d_os.p, (size_t)out_bytes, cudaMemcpyDeviceToHost, stream));
-    MG_TRY(cudaMemcpyAsync(out_qual, d_oq.p, (size_t)out_bytes, cudaMemcpyDeviceToHost, stream));
-    MG_TRY(cudaMemcpyAsync(info, d_info.p, sizeof(hc_merged_info) * (size_t)n_cliques, cudaMemcpyDeviceToHost, stream));
-    MG_TRY(cudaStreamSynchronize(stream));
+    B.single_end = m->d_single; B.seg_start = m->d_start; B.seg_end = m->d_end; B.cig_len = m->d_clen; B.seq_len = m->d_slen;
+    B.cig_off = m->d_coff; B.seq_off = m->d_soff; B.cig = m->d_cig; B.seq = m->d_seq; B.qual = m->d_qual;
+    B.member_off = m->d_moff; B.members = m->d_members; B.res_off = m->d_resoff; B.scratch_off = m->d_scroff;
+    B.res_cig = m->d_res; B.res_seq = m->d_res + rat; B.res_qual = m->d_res + 2 * rat;
+    B.scr_cig = m->d_scratch; B.scr_seq = m->d_scratch + sat; B.scr_qual = m->d_scratch + 2 * sat;
+    B.info = m->d_info; B.tab = m->d_tab; B.n_cliques = n_cliques; B.counters = m->d_counters;
+    const size_t smem = (size_t)kTabBytes + (size_t)kWarps * kSlice;
+    MG_TRY(m, cudaFuncSetAttribute(merge_cliques_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    MG_TRY(m, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, merge_cliques_kernel, kWarps * 32, smem));
+    const int blocks = std::max(1, std::min((n_cliques + kWarps - 1) / kWarps, m->sm_count * std::max(per_sm, 1)));
+    MG_TRY(m, cudaEventRecord(m->e0, m->stream));
+    merge_cliques_kernel<<<blocks, kWarps * 32, smem, m->stream>>>(B);
+    MG_TRY(m, cudaGetLastError());
+    MG_TRY(m, cudaEventRecord(m->e1, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(info, m->d_info, sizeof(hc_merged_record) * (size_t)n_cliques, cudaMemcpyDeviceToHost, m->stream));
+    unsigned long long cnt[2] = {0, 0};
+    MG_TRY(m, cudaMemcpyAsync(cnt, m->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost, m->stream));
+    MG_TRY(m, cudaStreamSynchronize(m->stream));
+    m->folds_plain = cnt[0]; m->folds_walked = cnt[1];
+    // final offsets: clique-major, segment 1 then segment 2
+    std::vector<int64_t> ops_at(nc1), seq_at(nc1);
+    int64_t oa = 0, sa = 0;
+    for (int c = 0; c < n_cliques; ++c) {
+        ops_at[c] = oa; seq_at[c] = sa;
+        if (info[c].status == HC_MERGE_OK)
+            for (int sg = 0; sg < (info[c].single_end ? 1 : 2); ++sg) { oa += info[c].n_ops[sg]; sa += info[c].n_seq[sg]; }
+    }
+    ops_at[n_cliques] = oa; seq_at[n_cliques] = sa;
+    m->out_ops = oa; m->out_seq = sa;
+    if ((rc = mgrow(m, m->d_out, m->cap_out, (size_t)oa + 2 * (size_t)sa + 64)) != HC_OK) return rc;
+    MG_TRY(m, cudaMemcpyAsync(m->d_opsat, ops_at.data(), sizeof(int64_t) * nc1, cudaMemcpyHostToDevice, m->stream));
+    MG_TRY(m, cudaMemcpyAsync(m->d_seqat, seq_at.data(), sizeof(int64_t) * nc1, cudaMemcpyHostToDevice, m->stream));
+    compact_kernel<<<std::max(1, std::min((n_cliques + 7) / 8, m->sm_count * 8)), 256, 0, m->stream>>>(
+        m->d_info, m->d_resoff, m->d_opsat, m->d_seqat, m->d_res, m->d_res + rat, m->d_res + 2 * rat, m->d_out, m->d_out + oa, m->d_out + oa + sa, n_cliques);
+    MG_TRY(m, cudaGetLastError());
+    MG_TRY(m, cudaStreamSynchronize(m->stream));
     float ms = 0.f;
-    MG_TRY(cudaEventElapsedTime(&ms, e0, e1));
+    MG_TRY(m, cudaEventElapsedTime(&ms, m->e0, m->e1));
     if (kernel_ms) *kernel_ms = ms;
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
-    cudaStreamDestroy(stream);
-#undef MG_TRY
+    if (total_ops) *total_ops = oa;
+    if (total_seq) *total_seq = sa;
+    m->have_result = true;
+    return HC_OK;
+}
+
+int hc_merge_fetch(hc_merger* m, uint8_t* cig, uint8_t* seq, uint8_t* qual) {
+    if (!m) return fail(HC_E_INVALID, "hc_merge_fetch: null merger");
+    if (!m->have_result) { m->err = "hc_merge_fetch: no result (hc_merge_run)"; return fail(HC_E_STATE, m->err); }
+    if ((m->out_ops > 0 && !cig) || (m->out_seq > 0 && (!seq || !qual))) return bad_arg(m, "hc_merge_fetch: null buffer");
+    MG_TRY(m, cudaSetDevice(m->device));
+    if (m->out_ops > 0) MG_TRY(m, cudaMemcpyAsync(cig, m->d_out, (size_t)m->out_ops, cudaMemcpyDeviceToHost, m->stream));
+    if (m->out_seq > 0) {
+        MG_TRY(m, cudaMemcpyAsync(seq, m->d_out + m->out_ops, (size_t)m->out_seq, cudaMemcpyDeviceToHost, m->stream));
+        MG_TRY(m, cudaMemcpyAsync(qual, m->d_out + m->out_ops + m->out_seq, (size_t)m->out_seq, cudaMemcpyDeviceToHost, m->stream));
+    }
+    MG_TRY(m, cudaStreamSynchronize(m->stream));
+    return HC_OK;
+}
+
+int hc_merge_fold_counts(const hc_merger* m, int64_t* column_space, int64_t* walked) {
+    if (!m) return HC_E_INVALID;
+    if (column_space) *column_space = (int64_t)m->folds_plain;
+    if (walked) *walked = (int64_t)m->folds_walked;
     return HC_OK;
 }
 

@@ -110,8 +110,6 @@ def load_library():
         L.hc_multi_partition.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.hc_multi_band_layout.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.hc_multi_score_band.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
-        L.hc_merge_layout.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
-        L.hc_merge_cliques_se.argtypes = [C.c_int32, C.c_void_p, C.c_int32] + [C.c_void_p] * 8
         assert C.sizeof(_BandStats) == 72 and HDR_DTYPE.itemsize == 64 and AMBIGUOUS_DTYPE.itemsize == 56
         _lib = L
     return _lib
@@ -574,54 +572,117 @@ def device_count() -> int:
     return int(load_library().hc_device_count())
 
 
-# ---- super-read construction, single-end cliques (include/hc_edge.h hc_merge_*) --------------
-MERGED_INFO_DTYPE = np.dtype([("status", np.int32), ("start", np.int32), ("end", np.int32), ("n_ops", np.int32),
-                              ("n_seq", np.int32)])
+# ---- super-read construction (include/hc_edge.h hc_merger_* / hc_merge_*) ------------------------------
+MERGED_RECORD_DTYPE = np.dtype([("status", np.int32), ("single_end", np.int32), ("start", np.int32, 2), ("end", np.int32, 2),
+                                ("n_ops", np.int32, 2), ("n_seq", np.int32, 2)])
 HC_MERGE_OK, HC_MERGE_UNDEFINED, HC_MERGE_OVERRUN = 0, 1, 2
 
 
 class MergedCliques:
-    """Result of merge_cliques_se: per clique the super-read's start1/end1, unrolled CIGAR, bases and quality chars."""
+    """Result of Merger.merge: per clique the super-read's header (`info`) and its unrolled CIGAR(s), bases and quality
+    chars, compacted back to back (clique-major, segment 1 then segment 2)."""
 
-    def __init__(self, info, out_off, cig, seq, qual, kernel_ms):
-        self.info, self.out_off, self.cig, self.seq, self.qual, self.kernel_ms = info, out_off, cig, seq, qual, kernel_ms
+    def __init__(self, info, cig, seq, qual, kernel_ms, folds):
+        self.info, self.cig, self.seq, self.qual, self.kernel_ms, self.folds = info, cig, seq, qual, kernel_ms, folds
+        ok = info["status"] == HC_MERGE_OK
+        nseg = np.where(info["single_end"] != 0, 1, 2)
+        no = np.where(ok, info["n_ops"][:, 0] + np.where(nseg == 2, info["n_ops"][:, 1], 0), 0).astype(np.int64)
+        ns = np.where(ok, info["n_seq"][:, 0] + np.where(nseg == 2, info["n_seq"][:, 1], 0), 0).astype(np.int64)
+        self.ops_at = np.concatenate([[0], np.cumsum(no)])
+        self.seq_at = np.concatenate([[0], np.cumsum(ns)])
 
     def __len__(self):
         return self.info.shape[0]
 
-    def record(self, c: int, clique_id: Optional[int] = None) -> Optional[AlignmentRecord]:
-        """The super-read as an AlignmentRecord named like the reference names it (src/AlignmentRecord.cpp:246);
+    def segments(self, c: int):
+        """(single_end, seg1, seg2) with seg = (start, end, cigar, sequence, qualities), seg2 None for a single-end result;
         None where the reference's merge is undefined (info['status'] != 0)."""
         r = self.info[c]
         if r["status"] != HC_MERGE_OK:
             return None
-        o = int(self.out_off[c])
-        return AlignmentRecord("Clique_%d" % (c if clique_id is None else clique_id), True, int(r["start"]), int(r["end"]),
-                               self.cig[o:o + r["n_ops"]].tobytes(), self.seq[o:o + r["n_seq"]].tobytes(),
-                               self.qual[o:o + r["n_seq"]].tobytes())
+        oa, sa = int(self.ops_at[c]), int(self.seq_at[c])
+        out = []
+        for sg in range(1 if r["single_end"] else 2):
+            no, ns = int(r["n_ops"][sg]), int(r["n_seq"][sg])
+            out.append((int(r["start"][sg]), int(r["end"][sg]), self.cig[oa:oa + no].tobytes(), self.seq[sa:sa + ns].tobytes(),
+                        self.qual[sa:sa + ns].tobytes()))
+            oa += no
+            sa += ns
+        return bool(r["single_end"]), out[0], (None if r["single_end"] else out[1])
+
+    def record(self, c: int, clique_id: Optional[int] = None) -> Optional[AlignmentRecord]:
+        """The super-read as an AlignmentRecord named like the reference names it (src/AlignmentRecord.cpp:246)."""
+        s = self.segments(c)
+        if s is None:
+            return None
+        single, a, b = s
+        rec = AlignmentRecord("Clique_%d" % (c if clique_id is None else clique_id), single, a[0], a[1], a[2], a[3], a[4])
+        if not single:
+            rec.start2, rec.end2, rec.cigar2_unrolled, rec.sequence2, rec.qualities2 = b
+        return rec
 
 
-def merge_cliques_se(reads: ReadBatch, cliques: Sequence[Sequence[int]], device: int = 0) -> MergedCliques:
-    """AlignmentRecord(alignments, clique_id) (src/AlignmentRecord.cpp:211-249) for a batch of single-end cliques, on the
-    GPU: `cliques[c]` lists read indices into `reads` in the order of the reference's `alignments` vector."""
-    L = load_library()
-    member_off = np.zeros(len(cliques) + 1, np.int64)
-    member_off[1:] = np.cumsum([len(c) for c in cliques])
-    members = np.ascontiguousarray(np.concatenate([np.asarray(c, np.int32) for c in cliques]) if len(cliques) else np.zeros(0, np.int32))
-    keep = [np.ascontiguousarray(getattr(reads, k)) for k in (
-        "single_end", "is_clique", "ncov", "cov_first", "cov_last", "seg_start", "seg_end", "cig_off", "cig_len",
-        "seq_off", "seq_len", "cig", "seq", "qual")]
-    rd = _Reads(reads.n, *[_ptr(a) for a in keep])
-    out_off = np.zeros(len(cliques) + 1, np.int64)
-    rc = L.hc_merge_layout(C.byref(rd), C.c_int32(len(cliques)), _ptr(member_off), _ptr(members), _ptr(out_off))
-    if rc != HC_OK:
-        raise HcError("hc_merge_layout failed (%d): %s" % (rc, L.hc_last_error(None).decode()))
-    total = max(int(out_off[-1]), 1)
-    cig, seq, qual = (np.zeros(total, np.uint8) for _ in range(3))
-    info = np.zeros(len(cliques), MERGED_INFO_DTYPE)
-    ms = C.c_float(0.0)
-    rc = L.hc_merge_cliques_se(C.c_int32(device), C.byref(rd), C.c_int32(len(cliques)), _ptr(member_off), _ptr(members),
-                               _ptr(out_off), _ptr(cig), _ptr(seq), _ptr(qual), _ptr(info), C.byref(ms))
-    if rc != HC_OK:
-        raise HcError("hc_merge_cliques_se failed (%d): %s" % (rc, L.hc_last_error(None).decode()))
-    return MergedCliques(info, out_off, cig, seq, qual, float(ms.value))
+class Merger:
+    """hc_merger: grow-only device buffers, one stream; set_reads once per finder round, merge per batch of cliques."""
+
+    def __init__(self, device: int = 0):
+        self.L = load_library()
+        self.L.hc_merger_create.argtypes = [C.c_int32, C.c_void_p]
+        self.L.hc_merger_destroy.argtypes = [C.c_void_p]
+        self.L.hc_merger_last_error.restype = C.c_char_p
+        self.L.hc_merger_last_error.argtypes = [C.c_void_p]
+        self.L.hc_merger_set_reads.argtypes = [C.c_void_p, C.c_void_p]
+        self.L.hc_merge_run.argtypes = [C.c_void_p, C.c_int32] + [C.c_void_p] * 6
+        self.L.hc_merge_fetch.argtypes = [C.c_void_p] * 4
+        self.L.hc_merge_fold_counts.argtypes = [C.c_void_p] * 3
+        self._h = C.c_void_p()
+        rc = self.L.hc_merger_create(C.c_int32(device), C.byref(self._h))
+        if rc != HC_OK:
+            self._h = None
+            raise HcError("hc_merger_create failed (%d): %s" % (rc, self.L.hc_last_error(None).decode()))
+        self._keep = None
+
+    def __del__(self):
+        try:
+            if self._h:
+                self.L.hc_merger_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != HC_OK:
+            raise HcError("%s failed (%d): %s" % (what, rc, self.L.hc_merger_last_error(self._h).decode()))
+
+    def set_reads(self, reads: ReadBatch):
+        self._keep = [np.ascontiguousarray(getattr(reads, k)) for k in (
+            "single_end", "is_clique", "ncov", "cov_first", "cov_last", "seg_start", "seg_end", "cig_off", "cig_len",
+            "seq_off", "seq_len", "cig", "seq", "qual")]
+        rd = _Reads(reads.n, *[_ptr(a) for a in self._keep])
+        self._check(self.L.hc_merger_set_reads(self._h, C.byref(rd)), "hc_merger_set_reads")
+
+    def merge(self, cliques: Sequence[Sequence[int]]) -> MergedCliques:
+        n = len(cliques)
+        member_off = np.zeros(n + 1, np.int64)
+        member_off[1:] = np.cumsum([len(c) for c in cliques])
+        members = np.ascontiguousarray(np.concatenate([np.asarray(c, np.int32) for c in cliques]) if n else np.zeros(0, np.int32))
+        info = np.zeros(max(n, 1), MERGED_RECORD_DTYPE)
+        to, ts, ms = C.c_int64(0), C.c_int64(0), C.c_float(0.0)
+        self._check(self.L.hc_merge_run(self._h, C.c_int32(n), _ptr(member_off), _ptr(members), _ptr(info), C.byref(to), C.byref(ts),
+                                        C.byref(ms)), "hc_merge_run")
+        cig = np.zeros(max(int(to.value), 1), np.uint8)
+        seq = np.zeros(max(int(ts.value), 1), np.uint8)
+        qual = np.zeros(max(int(ts.value), 1), np.uint8)
+        self._check(self.L.hc_merge_fetch(self._h, _ptr(cig), _ptr(seq), _ptr(qual)), "hc_merge_fetch")
+        a, b = C.c_int64(0), C.c_int64(0)
+        self.L.hc_merge_fold_counts(self._h, C.byref(a), C.byref(b))
+        return MergedCliques(info[:n], cig[:int(to.value)], seq[:int(ts.value)], qual[:int(ts.value)], float(ms.value),
+                             {"column_space": int(a.value), "walked": int(b.value)})
+
+
+def merge_cliques(reads: ReadBatch, cliques: Sequence[Sequence[int]], device: int = 0) -> MergedCliques:
+    """AlignmentRecord(alignments, clique_id) (src/AlignmentRecord.cpp:211-249) for a batch of cliques on the GPU:
+    `cliques[c]` lists read indices into `reads` in the order of the reference's `alignments` vector."""
+    m = Merger(device)
+    m.set_reads(reads)
+    return m.merge(cliques)

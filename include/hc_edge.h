@@ -16,6 +16,7 @@
  *                                            CLEVER::addAlignment (src/CLEVER.cpp:218-232) and
  *                                            BronKerbosch::addAlignment (src/BronKerbosch.cpp:286)
  *     hc_packed_free(packed); hc_destroy(ctx)
+ * Several GPUs behind one handle: hc_multi_*. Super-read construction for a round's cliques: hc_merger_* / hc_merge_*.
  */
 #ifndef HC_EDGE_H_
 #define HC_EDGE_H_
@@ -309,38 +310,48 @@ int hc_measure_peaks(int32_t device, double* lds_gbs, double* dmul_per_s);
 /* The two 127x127 match-probability tables the context uploaded (row-major [q1][q2], doubles). */
 int hc_get_tables(const hc_ctx* ctx, double* eq127x127, double* uneq127x127);
 
-/* ---- Super-read construction, single-end cliques (first slice) --------------------------------
+/* ---- Super-read construction -----------------------------------------------------------------------
  * Replaces AlignmentRecord::AlignmentRecord(unique_ptr<vector<const AlignmentRecord*>>& alignments, unsigned clique_id)
- * (src/AlignmentRecord.cpp:211-249; call site Clique -> super-read in src/CliqueCollector.h) for cliques whose members
- * are all single-end: the fold of mergeAlignmentRecordsSingle(ar,1,1) (:581-734) over the members in the given order.
+ * (src/AlignmentRecord.cpp:211-249; call site: a clique becomes a super-read in src/CliqueCollector.h:59) for whole batches
+ * of cliques and any mix of single-end and paired-end members: the fold of mergeAlignmentRecordsSingle (:581-734),
+ * mergeAlignmentRecordsPaired (:734-1293) and mergeAlignmentRecordsMixed (:1295-1537) over the members in the given order.
  * The caller keeps name ("Clique_<id>"), readNames and cov_pos, which are set unions / derived fields (:243-248).
- * Paired-end members are refused with HC_E_INVALID (mergeAlignmentRecordsPaired / Mixed are not built yet).
- * There is no CPU merging path: without a CUDA device the call fails with HC_E_CUDA. */
+ * There is no CPU merging path: without a CUDA device the calls fail with HC_E_CUDA.
+ *     hc_merger_create(device, &m)                      once
+ *     hc_merger_set_reads(m, &reads)                    per finder round: the reads the cliques refer to (same hc_reads as hc_pack)
+ *     hc_merge_run(m, n, member_off, members, info, &total_ops, &total_seq, &ms)
+ *     hc_merge_fetch(m, cig, seq, qual)                 the records' bytes, compacted on the device
+ *     hc_merger_destroy(m) */
 #define HC_MERGE_OK 0
 #define HC_MERGE_UNDEFINED 1            /* an op pair overlapMerge does not list (:1671 assert(false): the Release build of
                                            the reference never leaves that loop) */
-#define HC_MERGE_OVERRUN 2              /* a cursor ran past its CIGAR (start/end disagree with the CIGAR: the reference
-                                           reads past the vector there) */
+#define HC_MERGE_OVERRUN 2              /* a cursor ran past its CIGAR or its sequence (the layout's loops ask for columns
+                                           the read does not have: the reference reads past the vector / throws from .at()) */
 typedef struct {
     int32_t status;                     /* HC_MERGE_* */
-    int32_t start;                      /* start1 of the super-read (:686) */
-    int32_t end;                        /* end1 (:687) */
-    int32_t n_ops;                      /* length of cigar1_unrolled: M / I / D only, clips are dropped by the merge */
-    int32_t n_seq;                      /* length of sequence1 and of its quality string */
-} hc_merged_info;
+    int32_t single_end;                 /* AlignmentRecord::single_end of the super-read */
+    int32_t start[2], end[2];           /* start1/end1, start2/end2 */
+    int32_t n_ops[2];                   /* lengths of cigar1_unrolled / cigar2_unrolled (M / I / D only: merges drop clips) */
+    int32_t n_seq[2];                   /* lengths of sequence1 / sequence2 and their quality strings */
+} hc_merged_record;
 
-/* Clique c holds reads members[member_off[c] .. member_off[c+1]) in fold order (the order of the reference's
- * `alignments` vector). Fills out_off[n_cliques+1]: clique c's result occupies [out_off[c], out_off[c+1]) of each of the
- * three output streams (an upper bound: the members' CIGAR lengths summed, rounded up to 16). */
-int hc_merge_layout(const hc_reads* reads, int32_t n_cliques, const int64_t* member_off, const int32_t* members,
-                    int64_t* out_off);
+typedef struct hc_merger hc_merger;
+int hc_merger_create(int32_t device, hc_merger** out);
+void hc_merger_destroy(hc_merger* m);
+const char* hc_merger_last_error(const hc_merger* m);
+int hc_merger_set_reads(hc_merger* m, const hc_reads* reads);
 
-/* Merges every clique on `device`. out_cig / out_seq / out_qual: host buffers of out_off[n_cliques] bytes each; the
- * first info[c].n_ops / n_seq bytes at out_off[c] are the super-read's unrolled CIGAR, bases and quality chars.
- * kernel_ms (optional): device time of the merge kernel alone. */
-int hc_merge_cliques_se(int32_t device, const hc_reads* reads, int32_t n_cliques, const int64_t* member_off,
-                        const int32_t* members, const int64_t* out_off, uint8_t* out_cig, uint8_t* out_seq,
-                        uint8_t* out_qual, hc_merged_info* info, float* kernel_ms);
+/* Clique c holds reads members[member_off[c] .. member_off[c+1]) in fold order (the order of the reference's `alignments`
+ * vector). info[c]: the super-read's header. The records' bytes stay on the device until hc_merge_fetch: unrolled CIGARs
+ * back to back (clique-major, segment 1 then segment 2 of a paired result; total_ops bytes), and likewise bases and quality
+ * chars (total_seq bytes each); a clique whose status is not HC_MERGE_OK contributes nothing. kernel_ms (optional): device
+ * time of the merge kernel. */
+int hc_merge_run(hc_merger* m, int32_t n_cliques, const int64_t* member_off, const int32_t* members, hc_merged_record* info,
+                 int64_t* total_ops, int64_t* total_seq, float* kernel_ms);
+int hc_merge_fetch(hc_merger* m, uint8_t* cig, uint8_t* seq, uint8_t* qual);
+/* How the folds of the last hc_merge_run were evaluated: in reference-column space by a whole warp (segments that are
+ * clips / M only / clips), or walked op by op by one lane (indels, cursor quirks). */
+int hc_merge_fold_counts(const hc_merger* m, int64_t* column_space, int64_t* walked);
 
 #ifdef __cplusplus
 }

@@ -95,7 +95,7 @@ void GpuEdgeCalculator::init(double edge_quasi_cutoff, double overlap, std::unor
 GpuEdgeCalculator::GpuEdgeCalculator(double, double edge_quasi_cutoff, double overlap, bool, std::unordered_map<int, double>& simpson_map,
                                      double edge_quasi_cutoff_single, double overlap_single, double edge_quasi_cutoff_mixed,
                                      unsigned int maxPosition, bool noProb0, int device)
-    : multi_(nullptr), aux_(nullptr), resident_(nullptr), row_feeding_(true) {
+    : multi_(nullptr), aux_(nullptr), resident_(nullptr), flat_(new Flat()), row_feeding_(true) {
     init(edge_quasi_cutoff, overlap, simpson_map, edge_quasi_cutoff_single, overlap_single, edge_quasi_cutoff_mixed, maxPosition,
          noProb0, std::vector<int>(1, device));
 }
@@ -103,7 +103,7 @@ GpuEdgeCalculator::GpuEdgeCalculator(double, double edge_quasi_cutoff, double ov
 GpuEdgeCalculator::GpuEdgeCalculator(double, double edge_quasi_cutoff, double overlap, bool, std::unordered_map<int, double>& simpson_map,
                                      double edge_quasi_cutoff_single, double overlap_single, double edge_quasi_cutoff_mixed,
                                      unsigned int maxPosition, bool noProb0, const std::vector<int>& devices)
-    : multi_(nullptr), aux_(nullptr), resident_(nullptr), row_feeding_(true) {
+    : multi_(nullptr), aux_(nullptr), resident_(nullptr), flat_(new Flat()), row_feeding_(true) {
     init(edge_quasi_cutoff, overlap, simpson_map, edge_quasi_cutoff_single, overlap_single, edge_quasi_cutoff_mixed, maxPosition,
          noProb0, devices);
 }
@@ -112,6 +112,7 @@ GpuEdgeCalculator::~GpuEdgeCalculator() {
     hc_multi_destroy(multi_);
     hc_destroy(aux_);
     hc_packed_free(resident_);
+    delete flat_;
 }
 
 void GpuEdgeCalculator::scoreBatch(const std::deque<AlignmentRecord*>& reads) {
@@ -123,9 +124,8 @@ void GpuEdgeCalculator::scoreBatch(const std::vector<const AlignmentRecord*>& re
     index_.clear();
     reads_ = reads;
     for (size_t k = 0; k < reads.size(); ++k) index_[reads[k]] = (int)k;
-    Flat f;
-    flatten(reads, f);
-    const hc_reads view = f.view();
+    flatten(reads, *flat_);
+    const hc_reads view = flat_->view();
     hc_packed* packed = nullptr;
     int rc = hc_pack(&view, &packed);
     if (rc != HC_OK) throw std::runtime_error(std::string("GpuEdgeCalculator: hc_pack failed: ") + hc_last_error(nullptr));
@@ -158,6 +158,8 @@ int GpuEdgeCalculator::scorePairOn(hc_ctx* ctx, int i, int j, bool* edge) const 
     if (rc == HC_OK) *edge = res.edge != 0;
     return rc;
 }
+
+hc_reads GpuEdgeCalculator::batchView() const { return flat_->view(); }
 
 int GpuEdgeCalculator::indexOf(const AlignmentRecord& ap) const {
     const auto it = index_.find(&ap);

@@ -65,6 +65,9 @@ public:
     void setRowFeeding(bool on) { row_feeding_ = on; }
     /** Scratch the patched CLEVER keeps with the calculator (storage slot per id), so that class keeps its layout. */
     std::vector<size_t>& finderSlots() const { return finder_slots_; }
+    /** The scored batch as the flat arrays hc_pack was given (valid until the next scoreBatch): the read set of this round
+     *  for the GPU super-read merge (GpuSuperReadBuilder). */
+    hc_reads batchView() const;
     /** Not implemented by NewEdgeCalculator either (src/NewEdgeCalculator.cpp:1378-1380). */
     virtual void getPartnerLengthRange(const AlignmentRecord& ap, unsigned int* min, unsigned int* max) const;
     virtual void setOverlapCliques(double d);
@@ -114,6 +117,7 @@ private:
     std::vector<uint32_t> words_;
     hc_band_stats stats_;
     hc_packed* resident_;                                  // the scored batch (the devices hold slices of it)
+    Flat* flat_;                                           // its flat arrays
     bool row_feeding_;
     mutable std::vector<size_t> finder_slots_;
 };

@@ -15,6 +15,7 @@
 #include <sstream>
 
 #include "GpuEdgeCalculator.h"
+#include "GpuSuperReadBuilder.h"
 
 int main(int argc, char* argv[]) {
     map<std::string, docopt::value> args = docopt::docopt(USAGE, {argv + 1, argv + argc}, true, HAPLOCLIQUE_VERSION);
@@ -99,6 +100,18 @@ int main(int argc, char* argv[]) {
     std::vector<unsigned int> read_clique_counter(original_read_names.size());
     LogWriter* lw = logfile.empty() ? nullptr : new LogWriter(logfile, read_clique_counter);
     CliqueCollector collector(lw);
+    // the cliques of a round become super-reads in one GPU batch when the collector finishes (integration/
+    // CliqueCollector_batch.patch); HC_GPU_NO_MERGE keeps the reference's one-by-one host fold (for timing against it)
+    GpuSuperReadBuilder* builder = nullptr;
+    if (!std::getenv("HC_GPU_NO_MERGE")) {
+        try {
+            builder = new GpuSuperReadBuilder(*calc, devices[0]);
+        } catch (const runtime_error& error) {
+            cerr << error.what() << endl;
+            return 1;
+        }
+        collector.setSuperReadBuilder(builder);
+    }
     CliqueFinder* finder;
     if (args["bronkerbosch"].asBool()) finder = new BronKerbosch(*calc, collector, lw);
     else finder = new CLEVER(*calc, collector, lw, max_cliques, limit_clique_size, original_read_names.size(), filter_singletons);
@@ -144,7 +157,12 @@ int main(int argc, char* argv[]) {
         cout << "\tedges: " << edgecounter << endl;
         delete reads;
         finder->finish();
-        reads = collector.finish();
+        try {
+            reads = collector.finish();
+        } catch (const runtime_error& error) {
+            cerr << error.what() << endl;
+            return 1;
+        }
         if (lw) lw->finish();
         stdev = setProbabilities(*reads);
         if (finder->hasConverged()) break;
@@ -168,8 +186,12 @@ int main(int argc, char* argv[]) {
     delete reads;
     delete finder;
     delete lw;
-    delete calc;
     cout.precision(3);
-    cout << std::fixed << "time: " << (double)(clock() - clock_start) / CLOCKS_PER_SEC << " (gpu kernels " << gpu_ms << " ms)" << endl;
+    cout << std::fixed << "time: " << (double)(clock() - clock_start) / CLOCKS_PER_SEC << " (gpu scoring kernels " << gpu_ms << " ms";
+    if (builder) cout << ", gpu merge kernels " << builder->kernelMilliseconds() << " ms for " << builder->cliquesMerged() << " cliques, folds in column space "
+                      << builder->foldsInColumnSpace() << ", walked " << builder->foldsWalked();
+    cout << ")" << endl;
+    delete builder;
+    delete calc;
     return 0;
 }

@@ -26,6 +26,7 @@
 #undef main
 
 #ifdef HC_WITH_GPU_ADAPTER
+#include "GpuSuperReadBuilder.h"
 #include "GpuEdgeCalculator.h"          // integration/: the product's reference-side binding, tested through the reference's finders
 #endif
 
@@ -401,6 +402,15 @@ static int iterate_impl(RefCtx* c, EdgeCalculator& calc, int use_bk, int filter_
     std::vector<unsigned int> read_clique_counter(c->names.size());
     LogWriter* lw = (logfile && logfile[0]) ? new LogWriter(logfile, read_clique_counter) : nullptr;
     CliqueCollector collector(lw);
+#ifdef HC_WITH_GPU_ADAPTER
+    // with the GPU adapter the round's cliques are merged in one GPU batch (integration/CliqueCollector_batch.patch) unless
+    // HC_GPU_NO_MERGE asks for the reference's own host fold
+    std::unique_ptr<GpuSuperReadBuilder> builder;
+    if (gpu && !std::getenv("HC_GPU_NO_MERGE")) {
+        builder.reset(new GpuSuperReadBuilder(*static_cast<GpuEdgeCalculator*>(gpu)));
+        collector.setSuperReadBuilder(builder.get());
+    }
+#endif
     CliqueFinder* finder;
     if (use_bk) finder = new BronKerbosch(calc, collector, lw);
     else finder = new CLEVER(calc, collector, lw, 0, 0, c->names.size(), filter_singletons != 0);

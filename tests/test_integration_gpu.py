@@ -2,6 +2,7 @@
 oracle/_ref/libhcref_gpu.so and oracle/_ref/haploclique_gpu) driving the reference's own clique finders: whole-program
 parity -- same edges, same cliques, same super-reads, same FASTA as the unmodified reference on the same input."""
 import os
+import re
 import subprocess
 
 import numpy as np
@@ -79,9 +80,14 @@ def _clis_on_bam(tmp_path, bam, flags, finder):
     rows = _run_cli(pyref.CLI_GPU, tmp_path / "rows", finder, flags, bam)
     pairs = _run_cli(pyref.CLI_GPU, tmp_path / "pairs", finder, flags, bam, {"HC_GPU_NO_ROWS": "1"})
     check = _run_cli(pyref.CLI_GPU, tmp_path / "check", finder, flags, bam, {"HC_GPU_CHECK_ROWS": "1"})
-    for tag, got in (("rows", rows), ("pairs", pairs), ("check", check)):
+    # `rows` also builds every round's super-reads in one GPU batch (integration/CliqueCollector_batch.patch); `hostfold` keeps
+    # the reference's one-by-one constructor: same output either way
+    hostfold = _run_cli(pyref.CLI_GPU, tmp_path / "hostfold", finder, flags, bam, {"HC_GPU_NO_MERGE": "1"})
+    assert "gpu merge kernels" in rows[3] and "gpu merge kernels" not in hostfold[3]
+    for tag, got in (("rows", rows), ("pairs", pairs), ("check", check), ("hostfold", hostfold)):
         assert got[0] == ref[0], tag + ": FASTA differs"
-        assert got[1] == ref[1], tag + ": per-round counts differ"
+        lines = [re.sub(r"\trows ok: \d+ neighbours", "", ln) for ln in got[1]]      # the self-check's own note
+        assert lines == ref[1], tag + ": per-round counts differ"
         assert got[2] == ref[2] and len(ref[2]) > 0, tag + ": --log adjacency / cliques differ"
     assert "rows ok" in check[3] and "MISMATCH" not in check[3]
     return ref

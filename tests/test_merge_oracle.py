@@ -95,19 +95,13 @@ def test_merge_oracle_matches_reference_directly():
     assert n > 400
 
 
-def test_merge_refuses_paired_members_and_has_no_cpu_path():
-    """Host-side argument checks of hc_merge_* need no GPU; the merge itself fails with HC_E_CUDA without one."""
+def test_merge_has_no_cpu_path():
+    """Without a CUDA device the merger cannot be created (HC_E_CUDA): there is no CPU merging path in the product."""
     import torch
     from haploclique_b200 import edge
-    from tests.common import load_batch
-    b = load_batch("arabis_records.npz")
-    paired = int(np.flatnonzero(b.single_end == 0)[0])
-    with pytest.raises(edge.HcError, match="paired-end"):
-        edge.merge_cliques_se(b, [[paired, paired + 1]])
     if not torch.cuda.is_available():
-        h = load_batch("hiv50_records.npz")
         with pytest.raises(edge.HcError, match="no CPU merging path"):
-            edge.merge_cliques_se(h, [[0, 1]])
+            edge.Merger()
 
 
 # ---- general merge: paired-end and mixed members (mergeAlignmentRecordsPaired / Mixed, src/AlignmentRecord.cpp:734-1537) ----
