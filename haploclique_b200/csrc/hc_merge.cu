@@ -37,9 +37,9 @@
 namespace {
 
 constexpr int NQ = 94;            // quality chars 33..126
-constexpr int kWarps = 8;         // warps (= cliques in flight) per CTA
-constexpr int kSlice = 24 * 1024; // shared memory per warp: 4 segment buffers (2 segments x 2 generations) of 3 byte streams
-constexpr int kSegCap = kSlice / 12 / 16 * 16;   // ops a buffered segment may hold (2048): longer running reads use global scratch
+constexpr int kWarps = 16;        // warps (= cliques in flight) per CTA
+constexpr int kSlice = 12 * 1024; // shared memory per warp: 4 segment buffers (2 segments x 2 generations) of 3 byte streams
+constexpr int kSegCap = kSlice / 12 / 16 * 16;   // ops a buffered segment may hold (1024): longer running reads use global scratch
 constexpr int kTabBytes = (2 * NQ * NQ + 255) / 256 * 256;
 
 // Phred update tables with the reference's arithmetic (src/AlignmentRecord.cpp:40-54, 68-86): error probabilities through
@@ -144,23 +144,6 @@ struct OutBuf { uint8_t *cig, *seq, *qual; int n_ops, n_seq; };
 struct Job { int lay, after; };       // after: 1 single_end := false, 2 segment 2 := ar.segment2 + false, 3 segment 1 := ar.segment1 + false
 
 __device__ __forceinline__ bool is_clip(uint8_t c) { return c == 'S' || c == 'H'; }
-
-// Facts of a segment that the folds need: one pass over the CIGAR by one lane. (The running record's facts follow from the
-// fold that made it.)
-__device__ void seg_facts(Seg& s) {
-    int lead = 0, lead_h = 0, trail = 0;
-    while (lead < s.n_ops && is_clip(s.cig[lead])) { lead_h += s.cig[lead] == 'H'; ++lead; }
-    while (trail < s.n_ops - lead && is_clip(s.cig[s.n_ops - 1 - trail])) ++trail;
-    if (lead == s.n_ops) trail = s.n_ops;               // clips only: computeRevOffset counts them all again
-    int plain = lead + trail <= s.n_ops, cons = 0;
-    for (int k = 0; k < s.n_ops; ++k) {
-        const uint8_t c = s.cig[k];
-        cons += (c == 'M' || c == 'I' || c == 'S');
-        if (k >= lead && k < s.n_ops - trail && c != 'M') plain = 0;
-    }
-    if (cons > s.n_seq) plain = 0;
-    s.lead = lead; s.trail = trail; s.lead_h = lead_h; s.plain = plain;
-}
 
 struct Walk {
     const Seg* seg[2][2];
@@ -396,6 +379,7 @@ struct Batch {
     const int32_t *seg_start, *seg_end, *cig_len, *seq_len;
     const int64_t *cig_off, *seq_off;
     const uint8_t *cig, *seq, *qual;
+    const int4* facts;             // per segment row: lead, trail, lead_h, plain (host-built in hc_merger_set_reads)
     const int64_t* member_off;
     const int32_t* members;
     const int64_t* res_off;        // per clique: its capacity region in the result streams, 2 segments of cap = span / 2
@@ -414,7 +398,8 @@ __device__ __forceinline__ Seg load_seg(const Batch& B, int read, int sg, bool h
     s.start = have ? B.seg_start[r] : 0; s.end = have ? B.seg_end[r] : 0;
     s.n_ops = have ? B.cig_len[r] : 0; s.n_seq = have ? B.seq_len[r] : 0;
     s.cig = B.cig + B.cig_off[r]; s.seq = B.seq + B.seq_off[r]; s.qual = B.qual + B.seq_off[r];
-    s.lead = s.trail = s.lead_h = 0; s.plain = 0;
+    const int4 f = have ? B.facts[r] : make_int4(0, 0, 0, 0);
+    s.lead = f.x; s.trail = f.y; s.lead_h = f.z; s.plain = f.w;
     return s;
 }
 
@@ -493,8 +478,6 @@ __global__ void __launch_bounds__(kWarps * 32) merge_cliques_kernel(Batch B) {
             acc.single = B.single_end[r0] != 0;
             acc.s[0] = load_seg(B, r0, 0, true);
             acc.s[1] = load_seg(B, r0, 1, !acc.single);
-            seg_facts(acc.s[0]);
-            seg_facts(acc.s[1]);
         }
         __syncwarp();
         for (int f = 1; f < m && status == HC_MERGE_OK; ++f) {
@@ -503,8 +486,6 @@ __global__ void __launch_bounds__(kWarps * 32) merge_cliques_kernel(Batch B) {
                 mem.single = B.single_end[r] != 0;
                 mem.s[0] = load_seg(B, r, 0, true);
                 mem.s[1] = load_seg(B, r, 1, !mem.single);
-                seg_facts(mem.s[0]);
-                seg_facts(mem.s[1]);
                 Walk w0;
                 set_bounds(w0, acc, mem);
                 s_ctl[warp][3] = pick_jobs(acc, mem, w0.v, s_jobs[warp]);
@@ -557,7 +538,10 @@ __global__ void __launch_bounds__(kWarps * 32) merge_cliques_kernel(Batch B) {
                     t.n_ops = o.n_ops; t.n_seq = o.n_seq;
                     t.cig = o.cig; t.seq = o.seq; t.qual = o.qual;
                     t.lead = t.trail = t.lead_h = 0;                     // merges drop the clips
-                    int plain = 1;
+                    // A merged record takes min / max of the starts / ends but drops clip columns: where a clip column of one
+                    // read met no M of the other, its CIGAR is shorter than end - start + 1 (the reference walks such a record
+                    // by cursor and runs off it); only a record whose CIGAR is exactly its columns may be folded in column space
+                    int plain = t.n_ops == t.end - t.start + 1;
                     if (n_ph < 0) for (int k = 0; k < t.n_ops; ++k) plain &= t.cig[k] == 'M';
                     t.plain = plain;
                     if (rs.single != 2) acc.single = rs.single;
@@ -637,6 +621,7 @@ struct hc_merger {
     uint8_t* d_single = nullptr; int32_t *d_start = nullptr, *d_end = nullptr, *d_clen = nullptr, *d_slen = nullptr;
     int64_t *d_coff = nullptr, *d_soff = nullptr;
     uint8_t *d_cig = nullptr, *d_seq = nullptr, *d_qual = nullptr, *d_tab = nullptr;
+    int4* d_facts = nullptr; size_t cap_facts = 0;
     size_t cap_single = 0, cap_start = 0, cap_end = 0, cap_clen = 0, cap_slen = 0, cap_coff = 0, cap_soff = 0, cap_cig = 0, cap_seq = 0, cap_qual = 0;
     // per batch of cliques (grow-only)
     int64_t *d_moff = nullptr, *d_resoff = nullptr, *d_scroff = nullptr, *d_opsat = nullptr, *d_seqat = nullptr; int32_t* d_members = nullptr;
@@ -707,7 +692,7 @@ void hc_merger_destroy(hc_merger* m) {
     if (!m) return;
     cudaSetDevice(m->device);
     cudaFree(m->d_single); cudaFree(m->d_start); cudaFree(m->d_end); cudaFree(m->d_clen); cudaFree(m->d_slen); cudaFree(m->d_coff); cudaFree(m->d_soff);
-    cudaFree(m->d_cig); cudaFree(m->d_seq); cudaFree(m->d_qual); cudaFree(m->d_tab); cudaFree(m->d_moff); cudaFree(m->d_resoff); cudaFree(m->d_scroff);
+    cudaFree(m->d_facts); cudaFree(m->d_cig); cudaFree(m->d_seq); cudaFree(m->d_qual); cudaFree(m->d_tab); cudaFree(m->d_moff); cudaFree(m->d_resoff); cudaFree(m->d_scroff);
     cudaFree(m->d_opsat); cudaFree(m->d_seqat); cudaFree(m->d_members); cudaFree(m->d_info); cudaFree(m->d_scratch); cudaFree(m->d_res); cudaFree(m->d_out);
     cudaFree(m->d_counters);
     if (m->e0) cudaEventDestroy(m->e0);
@@ -733,7 +718,11 @@ int hc_merger_set_reads(hc_merger* m, const hc_reads* rd) {
         }
     // quality chars: the update tables cover 33..126. Chars below '!' are what computeEntry itself can emit (super-reads of
     // an earlier round) and are accepted; above 126 is refused. CIGAR ops outside MIDSH are refused.
+    // In the same pass: the facts of every segment the folds need -- leading / trailing clip counts (computeOffset /
+    // computeRevOffset, :126-156), H ops among the leading clips (they consume no query), and whether the segment is "plain":
+    // clips, M only, clips, with a CIGAR that consumes no more query than there is and is exactly the segment's columns.
     int bad = 0;
+    std::vector<int4> facts((size_t)std::max(2 * n, 2), make_int4(0, 0, 0, 0));
     hc::parallel_ranges(n, 4096, [&](int r0, int r1) {
         int mine = 0;
         for (int r = r0; r < r1 && !mine; ++r)
@@ -742,8 +731,21 @@ int hc_merger_set_reads(hc_merger* m, const hc_reads* rd) {
                 const uint8_t* q = rd->qual + rd->seq_off[k];
                 for (int i = 0; i < rd->seq_len[k]; ++i) if (q[i] > 126) mine = 1;
                 const uint8_t* cg = rd->cig + rd->cig_off[k];
-                for (int i = 0; i < rd->cig_len[k]; ++i)
-                    if (cg[i] != 'M' && cg[i] != 'I' && cg[i] != 'D' && cg[i] != 'S' && cg[i] != 'H') mine = 2;
+                const int nc = rd->cig_len[k];
+                int lead = 0, lead_h = 0, trail = 0, cons = 0;
+                while (lead < nc && (cg[lead] == 'S' || cg[lead] == 'H')) { lead_h += cg[lead] == 'H'; ++lead; }
+                while (trail < nc - lead && (cg[nc - 1 - trail] == 'S' || cg[nc - 1 - trail] == 'H')) ++trail;
+                if (lead == nc) trail = nc;                      // clips only: computeRevOffset counts them all again
+                int plain = lead + trail <= nc;
+                for (int i = 0; i < nc; ++i) {
+                    const uint8_t c = cg[i];
+                    if (c != 'M' && c != 'I' && c != 'D' && c != 'S' && c != 'H') mine = 2;
+                    cons += (c == 'M' || c == 'I' || c == 'S');
+                    if (i >= lead && i < nc - trail && c != 'M') plain = 0;
+                }
+                if (cons > rd->seq_len[k]) plain = 0;
+                if (nc != lead + trail + (rd->seg_end[k] - rd->seg_start[k] + 1)) plain = 0;
+                facts[(size_t)k] = make_int4(lead, trail, lead_h, plain);
             }
         if (mine) bad = mine;
     });
@@ -761,6 +763,8 @@ int hc_merger_set_reads(hc_merger* m, const hc_reads* rd) {
     if ((rc = mgrow(m, m->d_slen, m->cap_slen, n2)) != HC_OK) return rc;
     if ((rc = mgrow(m, m->d_coff, m->cap_coff, n2)) != HC_OK) return rc;
     if ((rc = mgrow(m, m->d_soff, m->cap_soff, n2)) != HC_OK) return rc;
+    if ((rc = mgrow(m, m->d_facts, m->cap_facts, n2)) != HC_OK) return rc;
+    MG_TRY(m, cudaMemcpyAsync(m->d_facts, facts.data(), sizeof(int4) * (size_t)(2 * n), cudaMemcpyHostToDevice, m->stream));
     if ((rc = mgrow(m, m->d_cig, m->cap_cig, (size_t)cig_bytes + 16)) != HC_OK) return rc;
     if ((rc = mgrow(m, m->d_seq, m->cap_seq, (size_t)seq_bytes + 16)) != HC_OK) return rc;
     if ((rc = mgrow(m, m->d_qual, m->cap_qual, (size_t)seq_bytes + 16)) != HC_OK) return rc;
@@ -828,7 +832,7 @@ int hc_merge_run(hc_merger* m, int32_t n_cliques, const int64_t* member_off, con
     MG_TRY(m, cudaMemsetAsync(m->d_counters, 0, 2 * sizeof(unsigned long long), m->stream));
     Batch B{};
     B.single_end = m->d_single; B.seg_start = m->d_start; B.seg_end = m->d_end; B.cig_len = m->d_clen; B.seq_len = m->d_slen;
-    B.cig_off = m->d_coff; B.seq_off = m->d_soff; B.cig = m->d_cig; B.seq = m->d_seq; B.qual = m->d_qual;
+    B.cig_off = m->d_coff; B.seq_off = m->d_soff; B.cig = m->d_cig; B.seq = m->d_seq; B.qual = m->d_qual; B.facts = m->d_facts;
     B.member_off = m->d_moff; B.members = m->d_members; B.res_off = m->d_resoff; B.scratch_off = m->d_scroff;
     B.res_cig = m->d_res; B.res_seq = m->d_res + rat; B.res_qual = m->d_res + 2 * rat;
     B.scr_cig = m->d_scratch; B.scr_seq = m->d_scratch + sat; B.scr_qual = m->d_scratch + 2 * sat;
