@@ -109,6 +109,22 @@ void build_match_tables(double* eq, double* uneq) {
     }
 }
 
+void build_phred_tables(uint8_t* tab) {
+    constexpr int NQ = 94;
+    float p[NQ];
+    for (int q = 0; q < NQ; ++q) p[q] = (float)std::pow(10.0, (double)((float)(-q) / 10));
+    for (int i = 0; i < NQ; ++i)
+        for (int j = 0; j < NQ; ++j) {
+            const float p1 = p[i], p2 = p[j];
+            float agree = (p1 * p2 / 3) / (1 - p1 - p2 + 4 * p1 * p2 / 3);
+            float dis = (p1 * (1 - p2 / 3)) / (p1 + p2 - 4 * p1 * p2 / 3);
+            const int va = (int)std::round(-10 * std::log10(agree));
+            const int vd = (int)std::round(-10 * std::log10(dis));
+            tab[i * NQ + j] = (uint8_t)(char)std::min(va + 33, 126);
+            tab[NQ * NQ + i * NQ + j] = (uint8_t)(char)std::min(vd + 33, 126);
+        }
+}
+
 void build_prob0_ladder(std::vector<double>& F, int n_max) {
     F.assign(static_cast<size_t>(n_max) + 1, 0.0);
     const double step = std::log10(0.25);

@@ -22,6 +22,12 @@ void build_match_tables(double* eq, double* uneq);
 // reference's running sum. Filled for 0..n_max.
 void build_prob0_ladder(std::vector<double>& F, int n_max);
 
+// Phred update tables of the merges with the reference's arithmetic (src/AlignmentRecord.cpp:40-54, 68-86): error
+// probabilities through a double pow rounded to float, the posterior in float, log10 and round in float; stored as the final
+// quality char min(v + 33, 126) (:173, :177, :180). tab[0..94*94) = bases agree, tab[94*94..) = bases differ (first index: the
+// larger quality). Indices are quality char - 33.
+void build_phred_tables(uint8_t* tab2x94x94);
+
 // Host buffer that is page-locked when a CUDA device is available (hc_upload then runs at full PCIe rate)
 // and plain malloc otherwise (packing itself never needs a GPU).
 struct HostBuf {

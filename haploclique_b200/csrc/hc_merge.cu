@@ -42,24 +42,6 @@ constexpr int kSlice = 12 * 1024; // shared memory per warp: 4 segment buffers (
 constexpr int kSegCap = kSlice / 12 / 16 * 16;   // ops a buffered segment may hold (1024): longer running reads use global scratch
 constexpr int kTabBytes = (2 * NQ * NQ + 255) / 256 * 256;
 
-// Phred update tables with the reference's arithmetic (src/AlignmentRecord.cpp:40-54, 68-86): error probabilities through
-// a double pow rounded to float, the posterior in float, log10 and round in float; stored as the final quality char
-// min(v + 33, 126) (:173, :177, :180). tab[0] = bases agree, tab[1] = bases differ (first index: the larger quality).
-void build_phred_tables(uint8_t* tab) {
-    float p[NQ];
-    for (int q = 0; q < NQ; ++q) p[q] = (float)std::pow(10.0, (double)((float)(-q) / 10));
-    for (int i = 0; i < NQ; ++i)
-        for (int j = 0; j < NQ; ++j) {
-            const float p1 = p[i], p2 = p[j];
-            float agree = (p1 * p2 / 3) / (1 - p1 - p2 + 4 * p1 * p2 / 3);
-            float dis = (p1 * (1 - p2 / 3)) / (p1 + p2 - 4 * p1 * p2 / 3);
-            const int va = (int)std::round(-10 * std::log10(agree));
-            const int vd = (int)std::round(-10 * std::log10(dis));
-            tab[i * NQ + j] = (uint8_t)(char)std::min(va + 33, 126);
-            tab[NQ * NQ + i * NQ + j] = (uint8_t)(char)std::min(vd + 33, 126);
-        }
-}
-
 // ---- layout table: bound ids ext*8 + side*4 + seg*2 + is_end; side 0 = the running record ("this"), 1 = the member ("ar")
 #define MB(ext, side, seg, is_end) ((ext) * 8 + (side) * 4 + (seg) * 2 + (is_end))
 enum : uint8_t {
@@ -680,7 +662,7 @@ int hc_merger_create(int32_t device, hc_merger** out) {
     if ((e = cudaEventCreate(&m->e0)) != cudaSuccess) return bad(e);
     if ((e = cudaEventCreate(&m->e1)) != cudaSuccess) return bad(e);
     std::vector<uint8_t> tab(2 * NQ * NQ);
-    build_phred_tables(tab.data());
+    hc::build_phred_tables(tab.data());
     if ((e = cudaMalloc((void**)&m->d_tab, tab.size())) != cudaSuccess) return bad(e);
     if ((e = cudaMemcpy(m->d_tab, tab.data(), tab.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return bad(e);
     if ((e = cudaMalloc((void**)&m->d_counters, 2 * sizeof(unsigned long long))) != cudaSuccess) return bad(e);

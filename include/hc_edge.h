@@ -353,6 +353,32 @@ int hc_merge_fetch(hc_merger* m, uint8_t* cig, uint8_t* seq, uint8_t* qual);
  * clips / M only / clips), or walked op by op by one lane (indels, cursor quirks). */
 int hc_merge_fold_counts(const hc_merger* m, int64_t* column_space, int64_t* walked);
 
+/* ---- Alignments in BAM order -> the position-sorted batch -----------------------------------------------
+ * Replaces readBamFile (src/haploclique.cpp:143-201) and the record building it drives: AlignmentRecord(BamAlignment)
+ * (src/AlignmentRecord.cpp:186-209), pairWith (:251-312) and getMergedDnaSequence for overlapping mates (:380-580), up to the
+ * hc_reads arrays hc_pack / hc_merger_set_reads take -- without AlignmentRecord objects and without cov_pos (32 bytes per
+ * covered column in the reference; only its size and its first / last position are needed and they are counted off the
+ * CIGAR). The BAM decoder stays with the caller (integration/GpuBamLoader feeds the reference's vendored BamTools reader).
+ * Host code only, no GPU needed.
+ *     hc_loader_create(&l);  for every alignment in file order: hc_loader_add(l, ...);  hc_loader_finish(l, &reads, &max_position)
+ * hc_loader_add: name, 0-based position, CIGAR as op chars + lengths (BamTools' CigarOp), query bases and qualities as
+ * stored. Alignments without an M op of positive length are skipped as the reference skips them (:160-165). HC_E_INVALID
+ * where the reference's mate merge is undefined for two overlapping mates (its loop would not return).
+ * hc_loader_finish: the batch in the reference's arrival order (pairs in file order, leftovers in the reference's hash
+ * order, std::sort by start); the arrays belong to the loader and live until hc_loader_destroy. max_position as :195-198.
+ * hc_loader_record_name(read) indexes hc_loader_name(k), the reference's readNames vector. */
+typedef struct hc_loader hc_loader;
+int hc_loader_create(hc_loader** out);
+void hc_loader_destroy(hc_loader* l);
+const char* hc_loader_last_error(const hc_loader* l);
+int hc_loader_add(hc_loader* l, const char* name, int32_t position0, const char* cigar_ops, const uint32_t* cigar_lens, int32_t n_cigar,
+                  const char* bases, const char* quals, int32_t n_bases);
+int hc_loader_finish(hc_loader* l, hc_reads* out, uint32_t* max_position);
+int32_t hc_loader_n_names(const hc_loader* l);
+const char* hc_loader_name(const hc_loader* l, int32_t k);
+int32_t hc_loader_record_name(const hc_loader* l, int32_t read);
+int hc_loader_counts(const hc_loader* l, int64_t* alignments, int64_t* skipped, int64_t* merged_mates);
+
 #ifdef __cplusplus
 }
 #endif

@@ -25,11 +25,11 @@ jobs=()
 for n in AlignmentRecord ShortDnaSequence NewEdgeCalculator QuasispeciesEdgeCalculator CLEVER BronKerbosch Clique GaussianEdgeCalculator; do
     jobs+=("$T/$n.cpp $OBJ/$n.o")
 done
-jobs+=("../integration/GpuEdgeCalculator.cpp $OBJ/GpuEdgeCalculator.o" "../integration/GpuSuperReadBuilder.cpp $OBJ/GpuSuperReadBuilder.o"
+jobs+=("../integration/GpuEdgeCalculator.cpp $OBJ/GpuEdgeCalculator.o" "../integration/GpuSuperReadBuilder.cpp $OBJ/GpuSuperReadBuilder.o" "../integration/GpuBamLoader.cpp $OBJ/GpuBamLoader.o"
        "ref_api.cpp $OBJ/ref_api_gpu.o" "../integration/haploclique_gpu_main.cpp $OBJ/gpu_main.o")
 printf '%s\n' "${jobs[@]}" | xargs -P 8 -L 1 bash -c 'compile "$0" "$1"'
 REF_OBJS=""
-for n in AlignmentRecord ShortDnaSequence NewEdgeCalculator QuasispeciesEdgeCalculator CLEVER BronKerbosch Clique GaussianEdgeCalculator GpuEdgeCalculator GpuSuperReadBuilder; do REF_OBJS="$REF_OBJS $OBJ/$n.o"; done
+for n in AlignmentRecord ShortDnaSequence NewEdgeCalculator QuasispeciesEdgeCalculator CLEVER BronKerbosch Clique GaussianEdgeCalculator GpuEdgeCalculator GpuSuperReadBuilder GpuBamLoader; do REF_OBJS="$REF_OBJS $OBJ/$n.o"; done
 LINK="-L../haploclique_b200 -lhcgpu -Wl,-rpath,\$ORIGIN/../../haploclique_b200 -lz -lpthread"
 g++ -shared -o "$OUT/libhcref_gpu.so" "$OBJ/ref_api_gpu.o" $REF_OBJS $DOCOPT_O $BAM_OBJS $LINK
 g++ -o "$OUT/haploclique_gpu" "$OBJ/gpu_main.o" $REF_OBJS $DOCOPT_O $BAM_OBJS $LINK

@@ -25,7 +25,9 @@
 #include "haploclique.cpp"
 #undef main
 
+#include <chrono>
 #ifdef HC_WITH_GPU_ADAPTER
+#include "GpuBamLoader.h"
 #include "GpuSuperReadBuilder.h"
 #include "GpuEdgeCalculator.h"          // integration/: the product's reference-side binding, tested through the reference's finders
 #endif
@@ -528,6 +530,72 @@ long hcref_quasi_gpu_pairs(void* p, const int* pi, const int* pj, long npairs, d
     (void)simpson_val; (void)n_simpson; (void)cut_single; (void)ov_single; (void)cut_mixed; (void)edge_out;
     return -1;
 #endif
+}
+
+
+// ---- the product's direct BAM -> SoA loader (integration/GpuBamLoader + hc_loader_*) for the N3 parity tests --------------
+// Returns a handle (free with hcref_direct_free) or null; *n / *max_position / counts[3] = alignments, skipped, merged mates.
+void* hcref_direct_load(const char* path, int* n, unsigned* max_position, long long* counts, double* seconds) {
+#ifdef HC_WITH_GPU_ADAPTER
+    try {
+        const auto t0 = std::chrono::steady_clock::now();
+        GpuBamLoader* L = new GpuBamLoader();
+        L->load(path);
+        if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (n) *n = L->reads().n;
+        if (max_position) *max_position = L->maxPosition();
+        if (counts) { int64_t a = 0, b = 0, c = 0; hc_loader_counts(L->handle(), &a, &b, &c); counts[0] = a; counts[1] = b; counts[2] = c; }
+        return L;
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "hcref_direct_load: %s\n", e.what());
+        return nullptr;
+    }
+#else
+    (void)path; (void)n; (void)max_position; (void)counts; (void)seconds;
+    return nullptr;
+#endif
+}
+// the hc_reads arrays of a loaded file (pointers into the handle) and the name of arrival r
+const void* hcref_direct_reads(void* h) {
+#ifdef HC_WITH_GPU_ADAPTER
+    return &static_cast<GpuBamLoader*>(h)->reads();
+#else
+    (void)h; return nullptr;
+#endif
+}
+int hcref_direct_name(void* h, int read, char* out, int cap) {
+#ifdef HC_WITH_GPU_ADAPTER
+    std::snprintf(out, cap, "%s", static_cast<GpuBamLoader*>(h)->recordName(read).c_str());
+    return 0;
+#else
+    (void)h; (void)read; (void)out; (void)cap; return -1;
+#endif
+}
+void hcref_direct_free(void* h) {
+#ifdef HC_WITH_GPU_ADAPTER
+    delete static_cast<GpuBamLoader*>(h);
+#else
+    (void)h;
+#endif
+}
+// seconds the reference's own readBamFile needs for the same file (records freed afterwards)
+double hcref_time_read_bam(const char* path, int* n) {
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::string> names;
+    unsigned int mp = 0;
+    BamTools::SamHeader header;
+    BamTools::RefVector refs;
+    std::deque<AlignmentRecord*>* reads = nullptr;
+    {
+        std::streambuf* old = std::cout.rdbuf(nullptr);        // "Read BamFile: done"
+        try { reads = readBamFile(path, names, mp, header, refs); } catch (...) { std::cout.rdbuf(old); return -1.0; }
+        std::cout.rdbuf(old);
+    }
+    const double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (n) *n = (int)reads->size();
+    for (auto* r : *reads) delete r;
+    delete reads;
+    return s;
 }
 
 }  // extern "C"
