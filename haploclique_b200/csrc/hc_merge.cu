@@ -356,12 +356,17 @@ __device__ void plain_emit(const Walk& w, const PlainPhase* ph, int n_ph, OutBuf
     o.n_ops = o.n_seq = base_out;
 }
 
+// Per segment row (2*read + segment), host-built in hc_merger_set_reads: three 16-byte loads bring a segment in.
+struct SegHdr {
+    int32_t start, end, n_ops, n_seq;
+    int32_t lead, trail, lead_h, plain;      // clip counts (computeOffset / computeRevOffset, :126-156), H among the leading clips, plain flag
+    int64_t cig_off, seq_off;
+};
+
 struct Batch {
     const uint8_t* single_end;
-    const int32_t *seg_start, *seg_end, *cig_len, *seq_len;
-    const int64_t *cig_off, *seq_off;
+    const SegHdr* seg;
     const uint8_t *cig, *seq, *qual;
-    const int4* facts;             // per segment row: lead, trail, lead_h, plain (host-built in hc_merger_set_reads)
     const int64_t* member_off;
     const int32_t* members;
     const int64_t* res_off;        // per clique: its capacity region in the result streams, 2 segments of cap = span / 2
@@ -374,15 +379,21 @@ struct Batch {
     unsigned long long* counters;  // [0] folds evaluated in column space, [1] folds walked
 };
 
-__device__ __forceinline__ Seg load_seg(const Batch& B, int read, int sg, bool have) {
-    const int r = 2 * read + sg;
-    Seg s;
-    s.start = have ? B.seg_start[r] : 0; s.end = have ? B.seg_end[r] : 0;
-    s.n_ops = have ? B.cig_len[r] : 0; s.n_seq = have ? B.seq_len[r] : 0;
-    s.cig = B.cig + B.cig_off[r]; s.seq = B.seq + B.seq_off[r]; s.qual = B.qual + B.seq_off[r];
-    const int4 f = have ? B.facts[r] : make_int4(0, 0, 0, 0);
-    s.lead = f.x; s.trail = f.y; s.lead_h = f.z; s.plain = f.w;
-    return s;
+// Lanes 0 and 1 bring the two segments of a read into a record in shared memory (lane = segment).
+__device__ __forceinline__ void load_rec(const Batch& B, int read, Rec& rec, int lane) {
+    if (lane < 2) {
+        const bool single = B.single_end[read] != 0;
+        const int4* p = reinterpret_cast<const int4*>(B.seg + 2 * (size_t)read + lane);
+        const int4 a = __ldg(p), f = __ldg(p + 1), o = __ldg(p + 2);
+        const bool have = lane == 0 || !single;
+        const long long cig_off = ((long long)(unsigned)o.y << 32) | (unsigned)o.x, seq_off = ((long long)(unsigned)o.w << 32) | (unsigned)o.z;
+        Seg s;
+        s.start = have ? a.x : 0; s.end = have ? a.y : 0; s.n_ops = have ? a.z : 0; s.n_seq = have ? a.w : 0;
+        s.lead = have ? f.x : 0; s.trail = have ? f.y : 0; s.lead_h = have ? f.z : 0; s.plain = have ? f.w : 0;
+        s.cig = B.cig + cig_off; s.seq = B.seq + seq_off; s.qual = B.qual + seq_off;
+        rec.s[lane] = s;
+        if (lane == 0) rec.single = single;
+    }
 }
 
 // The layout(s) of one fold: AlignmentRecord's constructor dispatch (:233-242) and the branch heads of
@@ -455,19 +466,12 @@ __global__ void __launch_bounds__(kWarps * 32) merge_cliques_kernel(Batch B) {
         };
         int gen[2] = {0, 0};
         int status = HC_MERGE_OK;
-        if (lane == 0) {
-            const int r0 = B.members[m0];
-            acc.single = B.single_end[r0] != 0;
-            acc.s[0] = load_seg(B, r0, 0, true);
-            acc.s[1] = load_seg(B, r0, 1, !acc.single);
-        }
+        load_rec(B, B.members[m0], acc, lane);
         __syncwarp();
         for (int f = 1; f < m && status == HC_MERGE_OK; ++f) {
+            load_rec(B, B.members[m0 + f], mem, lane);
+            __syncwarp();
             if (lane == 0) {
-                const int r = B.members[m0 + f];
-                mem.single = B.single_end[r] != 0;
-                mem.s[0] = load_seg(B, r, 0, true);
-                mem.s[1] = load_seg(B, r, 1, !mem.single);
                 Walk w0;
                 set_bounds(w0, acc, mem);
                 s_ctl[warp][3] = pick_jobs(acc, mem, w0.v, s_jobs[warp]);
@@ -482,7 +486,17 @@ __global__ void __launch_bounds__(kWarps * 32) merge_cliques_kernel(Batch B) {
                 Walk w;
                 set_bounds(w, acc, mem);
                 // ---- plain folds: all lanes, column space; anything else: lane 0 walks it
-                if (lane == 0) {
+                if (lane == 0 && lay >= LAY_SINGLE) {
+                    // mergeAlignmentRecordsSingle on two plain segments that overlap or abut: the leader's tail, the overlap and
+                    // the trailer's tail are one run of columns [min start, max end]; a column emits where either read shows M
+                    const int i = (lay - LAY_SINGLE) >> 1, j = (lay - LAY_SINGLE) & 1;
+                    const Seg& sa = acc.s[i]; const Seg& sb = mem.s[j];
+                    const int xas = sa.start - sa.lead, xae = sa.end + sa.trail, xbs = sb.start - sb.lead, xbe = sb.end + sb.trail;
+                    if (sa.plain && sb.plain && max(xas, xbs) <= min(xae, xbe) + 1) {
+                        s_ph[warp][0] = PlainPhase{min(xas, xbs), max(xae, xbe) + 1, i, 2 + j};
+                        s_ctl[warp][2] = 1;
+                    } else s_ctl[warp][2] = -1;
+                } else if (lane == 0) {
                     bool all_plain = true;
                     for (int k = 0; k < 11 && L.ph[k].op != P_END; ++k) {
                         const Phase ph = L.ph[k];
@@ -600,11 +614,10 @@ struct hc_merger {
     int n_reads = 0;
     std::vector<uint8_t> single_end;
     std::vector<int32_t> cig_len;
-    uint8_t* d_single = nullptr; int32_t *d_start = nullptr, *d_end = nullptr, *d_clen = nullptr, *d_slen = nullptr;
-    int64_t *d_coff = nullptr, *d_soff = nullptr;
+    uint8_t* d_single = nullptr;
     uint8_t *d_cig = nullptr, *d_seq = nullptr, *d_qual = nullptr, *d_tab = nullptr;
-    int4* d_facts = nullptr; size_t cap_facts = 0;
-    size_t cap_single = 0, cap_start = 0, cap_end = 0, cap_clen = 0, cap_slen = 0, cap_coff = 0, cap_soff = 0, cap_cig = 0, cap_seq = 0, cap_qual = 0;
+    SegHdr* d_seg = nullptr; size_t cap_seghdr = 0;
+    size_t cap_single = 0, cap_cig = 0, cap_seq = 0, cap_qual = 0;
     // per batch of cliques (grow-only)
     int64_t *d_moff = nullptr, *d_resoff = nullptr, *d_scroff = nullptr, *d_opsat = nullptr, *d_seqat = nullptr; int32_t* d_members = nullptr;
     hc_merged_record* d_info = nullptr;
@@ -673,8 +686,7 @@ int hc_merger_create(int32_t device, hc_merger** out) {
 void hc_merger_destroy(hc_merger* m) {
     if (!m) return;
     cudaSetDevice(m->device);
-    cudaFree(m->d_single); cudaFree(m->d_start); cudaFree(m->d_end); cudaFree(m->d_clen); cudaFree(m->d_slen); cudaFree(m->d_coff); cudaFree(m->d_soff);
-    cudaFree(m->d_facts); cudaFree(m->d_cig); cudaFree(m->d_seq); cudaFree(m->d_qual); cudaFree(m->d_tab); cudaFree(m->d_moff); cudaFree(m->d_resoff); cudaFree(m->d_scroff);
+    cudaFree(m->d_single); cudaFree(m->d_seg); cudaFree(m->d_cig); cudaFree(m->d_seq); cudaFree(m->d_qual); cudaFree(m->d_tab); cudaFree(m->d_moff); cudaFree(m->d_resoff); cudaFree(m->d_scroff);
     cudaFree(m->d_opsat); cudaFree(m->d_seqat); cudaFree(m->d_members); cudaFree(m->d_info); cudaFree(m->d_scratch); cudaFree(m->d_res); cudaFree(m->d_out);
     cudaFree(m->d_counters);
     if (m->e0) cudaEventDestroy(m->e0);
@@ -704,7 +716,8 @@ int hc_merger_set_reads(hc_merger* m, const hc_reads* rd) {
     // computeRevOffset, :126-156), H ops among the leading clips (they consume no query), and whether the segment is "plain":
     // clips, M only, clips, with a CIGAR that consumes no more query than there is and is exactly the segment's columns.
     int bad = 0;
-    std::vector<int4> facts((size_t)std::max(2 * n, 2), make_int4(0, 0, 0, 0));
+    std::vector<SegHdr> hdr((size_t)std::max(2 * n, 2));
+    std::memset(hdr.data(), 0, hdr.size() * sizeof(SegHdr));
     hc::parallel_ranges(n, 4096, [&](int r0, int r1) {
         int mine = 0;
         for (int r = r0; r < r1 && !mine; ++r)
@@ -727,7 +740,10 @@ int hc_merger_set_reads(hc_merger* m, const hc_reads* rd) {
                 }
                 if (cons > rd->seq_len[k]) plain = 0;
                 if (nc != lead + trail + (rd->seg_end[k] - rd->seg_start[k] + 1)) plain = 0;
-                facts[(size_t)k] = make_int4(lead, trail, lead_h, plain);
+                SegHdr& h = hdr[(size_t)k];
+                h.start = rd->seg_start[k]; h.end = rd->seg_end[k]; h.n_ops = nc; h.n_seq = rd->seq_len[k];
+                h.lead = lead; h.trail = trail; h.lead_h = lead_h; h.plain = plain;
+                h.cig_off = rd->cig_off[k]; h.seq_off = rd->seq_off[k];
             }
         if (mine) bad = mine;
     });
@@ -739,24 +755,12 @@ int hc_merger_set_reads(hc_merger* m, const hc_reads* rd) {
     int rc;
     const size_t n2 = (size_t)std::max(2 * n, 2);
     if ((rc = mgrow(m, m->d_single, m->cap_single, n2)) != HC_OK) return rc;
-    if ((rc = mgrow(m, m->d_start, m->cap_start, n2)) != HC_OK) return rc;
-    if ((rc = mgrow(m, m->d_end, m->cap_end, n2)) != HC_OK) return rc;
-    if ((rc = mgrow(m, m->d_clen, m->cap_clen, n2)) != HC_OK) return rc;
-    if ((rc = mgrow(m, m->d_slen, m->cap_slen, n2)) != HC_OK) return rc;
-    if ((rc = mgrow(m, m->d_coff, m->cap_coff, n2)) != HC_OK) return rc;
-    if ((rc = mgrow(m, m->d_soff, m->cap_soff, n2)) != HC_OK) return rc;
-    if ((rc = mgrow(m, m->d_facts, m->cap_facts, n2)) != HC_OK) return rc;
-    MG_TRY(m, cudaMemcpyAsync(m->d_facts, facts.data(), sizeof(int4) * (size_t)(2 * n), cudaMemcpyHostToDevice, m->stream));
+    if ((rc = mgrow(m, m->d_seg, m->cap_seghdr, n2)) != HC_OK) return rc;
+    MG_TRY(m, cudaMemcpyAsync(m->d_seg, hdr.data(), sizeof(SegHdr) * (size_t)(2 * n), cudaMemcpyHostToDevice, m->stream));
     if ((rc = mgrow(m, m->d_cig, m->cap_cig, (size_t)cig_bytes + 16)) != HC_OK) return rc;
     if ((rc = mgrow(m, m->d_seq, m->cap_seq, (size_t)seq_bytes + 16)) != HC_OK) return rc;
     if ((rc = mgrow(m, m->d_qual, m->cap_qual, (size_t)seq_bytes + 16)) != HC_OK) return rc;
     MG_TRY(m, cudaMemcpyAsync(m->d_single, rd->single_end, (size_t)n, cudaMemcpyHostToDevice, m->stream));
-    MG_TRY(m, cudaMemcpyAsync(m->d_start, rd->seg_start, sizeof(int32_t) * 2 * n, cudaMemcpyHostToDevice, m->stream));
-    MG_TRY(m, cudaMemcpyAsync(m->d_end, rd->seg_end, sizeof(int32_t) * 2 * n, cudaMemcpyHostToDevice, m->stream));
-    MG_TRY(m, cudaMemcpyAsync(m->d_clen, rd->cig_len, sizeof(int32_t) * 2 * n, cudaMemcpyHostToDevice, m->stream));
-    MG_TRY(m, cudaMemcpyAsync(m->d_slen, rd->seq_len, sizeof(int32_t) * 2 * n, cudaMemcpyHostToDevice, m->stream));
-    MG_TRY(m, cudaMemcpyAsync(m->d_coff, rd->cig_off, sizeof(int64_t) * 2 * n, cudaMemcpyHostToDevice, m->stream));
-    MG_TRY(m, cudaMemcpyAsync(m->d_soff, rd->seq_off, sizeof(int64_t) * 2 * n, cudaMemcpyHostToDevice, m->stream));
     MG_TRY(m, cudaMemcpyAsync(m->d_cig, rd->cig, (size_t)cig_bytes, cudaMemcpyHostToDevice, m->stream));
     MG_TRY(m, cudaMemcpyAsync(m->d_seq, rd->seq, (size_t)seq_bytes, cudaMemcpyHostToDevice, m->stream));
     MG_TRY(m, cudaMemcpyAsync(m->d_qual, rd->qual, (size_t)seq_bytes, cudaMemcpyHostToDevice, m->stream));
@@ -813,8 +817,7 @@ int hc_merge_run(hc_merger* m, int32_t n_cliques, const int64_t* member_off, con
     MG_TRY(m, cudaMemcpyAsync(m->d_scroff, scroff.data(), sizeof(int64_t) * nc1, cudaMemcpyHostToDevice, m->stream));
     MG_TRY(m, cudaMemsetAsync(m->d_counters, 0, 2 * sizeof(unsigned long long), m->stream));
     Batch B{};
-    B.single_end = m->d_single; B.seg_start = m->d_start; B.seg_end = m->d_end; B.cig_len = m->d_clen; B.seq_len = m->d_slen;
-    B.cig_off = m->d_coff; B.seq_off = m->d_soff; B.cig = m->d_cig; B.seq = m->d_seq; B.qual = m->d_qual; B.facts = m->d_facts;
+    B.single_end = m->d_single; B.seg = m->d_seg; B.cig = m->d_cig; B.seq = m->d_seq; B.qual = m->d_qual;
     B.member_off = m->d_moff; B.members = m->d_members; B.res_off = m->d_resoff; B.scratch_off = m->d_scroff;
     B.res_cig = m->d_res; B.res_seq = m->d_res + rat; B.res_qual = m->d_res + 2 * rat;
     B.scr_cig = m->d_scratch; B.scr_seq = m->d_scratch + sat; B.scr_qual = m->d_scratch + 2 * sat;
