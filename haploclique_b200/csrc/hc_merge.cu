@@ -37,9 +37,9 @@
 namespace {
 
 constexpr int NQ = 94;            // quality chars 33..126
-constexpr int kWarps = 16;        // warps (= cliques in flight) per CTA
-constexpr int kSlice = 12 * 1024; // shared memory per warp: 4 segment buffers (2 segments x 2 generations) of 3 byte streams
-constexpr int kSegCap = kSlice / 12 / 16 * 16;   // ops a buffered segment may hold (1024): longer running reads use global scratch
+constexpr int kWarps = 24;        // warps (= cliques in flight) per CTA
+constexpr int kSlice = 6 * 1024;  // shared memory per warp: 4 segment buffers (2 segments x 2 generations) of 3 byte streams
+constexpr int kSegCap = kSlice / 12 / 16 * 16;   // ops a buffered segment may hold (512): longer running reads use global scratch
 constexpr int kTabBytes = (2 * NQ * NQ + 255) / 256 * 256;
 
 // ---- layout table: bound ids ext*8 + side*4 + seg*2 + is_end; side 0 = the running record ("this"), 1 = the member ("ar")
@@ -121,7 +121,7 @@ struct Seg {
 
 struct Rec { int single; Seg s[2]; };
 
-struct OutBuf { uint8_t *cig, *seq, *qual; int n_ops, n_seq; };
+struct OutBuf { uint8_t *cig, *seq, *qual; int n_ops, n_seq, cap; };
 
 struct Job { int lay, after; };       // after: 1 single_end := false, 2 segment 2 := ar.segment2 + false, 3 segment 1 := ar.segment1 + false
 
@@ -135,10 +135,19 @@ struct Walk {
     OutBuf* o;
 };
 
-__device__ __forceinline__ void put(OutBuf& o, uint8_t op, uint8_t base, uint8_t qual) {
+// The walker's emits are bounded by the clique's capacity (columns spanned + insertions); an undefined walk that would emit
+// more stops as an overrun.
+__device__ __forceinline__ bool put(OutBuf& o, uint8_t op, uint8_t base, uint8_t qual) {
+    if (o.n_ops >= o.cap) return false;
     o.seq[o.n_seq] = base;
     o.qual[o.n_seq++] = qual;
     o.cig[o.n_ops++] = op;
+    return true;
+}
+__device__ __forceinline__ bool put_d(OutBuf& o) {
+    if (o.n_ops >= o.cap) return false;
+    o.cig[o.n_ops++] = 'D';
+    return true;
 }
 
 // computeEntry (:169-184) from the byte tables. A char below '!' (the reference's own agreement of Q0 with Q62+ rounds to
@@ -161,10 +170,10 @@ __device__ int tail_step(Walk& w, int side, int sg) {
     const uint8_t op = s.cig[c];
     if (op == 'M' || op == 'I') {
         if (q >= s.n_seq) return HC_MERGE_OVERRUN;
-        put(*w.o, op, s.seq[q], s.qual[q]);
+        if (!put(*w.o, op, s.seq[q], s.qual[q])) return HC_MERGE_OVERRUN;
         ++q; ++c;
         w.ref += (op == 'M');
-    } else if (op == 'D') { w.o->cig[w.o->n_ops++] = 'D'; ++w.ref; ++c; }
+    } else if (op == 'D') { if (!put_d(*w.o)) return HC_MERGE_OVERRUN; ++w.ref; ++c; }
     else if (op == 'S') { ++w.ref; ++q; ++c; }
     else if (op == 'H') { ++w.ref; ++c; }
     else return HC_MERGE_UNDEFINED;
@@ -183,33 +192,33 @@ __device__ int ovl_step(Walk& w, int sa, int sb, int& qa, const uint8_t* tab) {
         if (qa >= a.n_seq || q2 >= b.n_seq) return HC_MERGE_OVERRUN;
         uint8_t base, qual;
         entry(tab, a.seq[qa], a.qual[qa], b.seq[q2], b.qual[q2], base, qual);
-        put(o, x, base, qual);
+        if (!put(o, x, base, qual)) return HC_MERGE_OVERRUN;
         w.ref += (x == 'M');
         ++qa; ++q2; ++c1; ++c2;
     } else if ((x == 'D' || xc) && (y == 'D' || yc)) {
         // D/D, D/clip, clip/clip: a reference column without a merged base; it stays a deletion if either read has one;
         // an S consumes its read's query base
-        if (x == 'D' || y == 'D') o.cig[o.n_ops++] = 'D';
+        if ((x == 'D' || y == 'D') && !put_d(o)) return HC_MERGE_OVERRUN;
         qa += (x == 'S');
         q2 += (y == 'S');
         ++w.ref; ++c1; ++c2;
     } else if (x == 'M' && yc) {
         if (qa >= a.n_seq) return HC_MERGE_OVERRUN;
-        put(o, 'M', a.seq[qa], a.qual[qa]);
+        if (!put(o, 'M', a.seq[qa], a.qual[qa])) return HC_MERGE_OVERRUN;
         ++qa; q2 += (y == 'S');
         ++w.ref; ++c1; ++c2;
     } else if (xc && y == 'M') {
         if (q2 >= b.n_seq) return HC_MERGE_OVERRUN;
-        put(o, 'M', b.seq[q2], b.qual[q2]);
+        if (!put(o, 'M', b.seq[q2], b.qual[q2])) return HC_MERGE_OVERRUN;
         ++q2; qa += (x == 'S');
         ++w.ref; ++c1; ++c2;
     } else if (x == 'I' && yc) {
         if (qa >= a.n_seq) return HC_MERGE_OVERRUN;
-        put(o, 'I', a.seq[qa], a.qual[qa]);
+        if (!put(o, 'I', a.seq[qa], a.qual[qa])) return HC_MERGE_OVERRUN;
         ++c1; ++qa;
     } else if (xc && y == 'I') {
         if (q2 >= b.n_seq) return HC_MERGE_OVERRUN;
-        put(o, 'I', b.seq[q2], b.qual[q2]);
+        if (!put(o, 'I', b.seq[q2], b.qual[q2])) return HC_MERGE_OVERRUN;
         ++c2; ++q2;
     } else {
         return HC_MERGE_UNDEFINED;
@@ -363,6 +372,44 @@ struct SegHdr {
     int64_t cig_off, seq_off;
 };
 
+// mergeAlignmentRecordsSingle(ar, i, j) on two plain segments that overlap or abut, all 32 lanes: the leader's tail, the
+// overlap and the trailer's tail are one run of columns [min extended start, max extended end]; a column emits where either
+// read shows M, and its slot is the number of emitting columns before it (interval arithmetic, no scan).
+__device__ __forceinline__ void single_plain_fold(const Seg& a, const Seg& b, OutBuf& o, const uint8_t* tab, int lane) {
+    const int as = a.start, ae = a.end, bs = b.start, be = b.end;               // the M ranges
+    const int hi = max(ae + a.trail, be + b.trail) + 1;
+    const int alen = ae - as + 1, blen = be - bs + 1;
+    const int cs = max(as, bs), clen = max(0, min(ae, be) - cs + 1);            // both show M
+    const uint8_t* aseq = a.seq + (a.lead - a.lead_h) - as; const uint8_t* aql = a.qual + (a.lead - a.lead_h) - as;   // index by column
+    const uint8_t* bseq = b.seq + (b.lead - b.lead_h) - bs; const uint8_t* bql = b.qual + (b.lead - b.lead_h) - bs;
+    // 128 columns per pass: every lane first issues the loads of its 4 columns (one memory latency per pass: the member's bytes
+    // come from L2), then merges and stores them
+    constexpr int U = 4;
+    for (int p0 = min(as, bs) + lane; p0 < hi; p0 += 32 * U) {                  // columns left of the first M emit nothing
+        uint8_t xa[U], qa[U], xb[U], qb[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int p = p0 + 32 * u;
+            const bool ma = p >= as && p <= ae, mb = p >= bs && p <= be;
+            xa[u] = ma ? aseq[p] : 0; qa[u] = ma ? aql[p] : 0;
+            xb[u] = mb ? bseq[p] : 0; qb[u] = mb ? bql[p] : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int p = p0 + 32 * u;
+            const bool ma = p >= as && p <= ae, mb = p >= bs && p <= be;
+            if (!ma && !mb) continue;
+            uint8_t base, qual;
+            if (ma && mb) entry(tab, xa[u], qa[u], xb[u], qb[u], base, qual);
+            else if (ma) { base = xa[u]; qual = qa[u]; }
+            else { base = xb[u]; qual = qb[u]; }
+            const int slot = min(max(p - as, 0), alen) + min(max(p - bs, 0), blen) - min(max(p - cs, 0), clen);
+            o.cig[slot] = 'M'; o.seq[slot] = base; o.qual[slot] = qual;
+        }
+    }
+    o.n_ops = o.n_seq = alen + blen - clen;
+}
+
 struct Batch {
     const uint8_t* single_end;
     const SegHdr* seg;
@@ -379,12 +426,24 @@ struct Batch {
     unsigned long long* counters;  // [0] folds evaluated in column space, [1] folds walked
 };
 
-// Lanes 0 and 1 bring the two segments of a read into a record in shared memory (lane = segment).
-__device__ __forceinline__ void load_rec(const Batch& B, int read, Rec& rec, int lane) {
-    if (lane < 2) {
-        const bool single = B.single_end[read] != 0;
+// Lanes 0 and 1 bring the two segments of a read into a record in shared memory (lane = segment): the loads are issued by
+// fetch_rec (one fold ahead, so that their latency hides behind the current fold), commit_rec writes the record.
+struct RecRegs { int4 a, f, o; int single; };
+__device__ __forceinline__ RecRegs fetch_rec(const Batch& B, int read, int lane) {
+    RecRegs r;
+    r.a = r.f = r.o = make_int4(0, 0, 0, 0);
+    r.single = 1;
+    if (lane < 2 && read >= 0) {
+        r.single = B.single_end[read] != 0;
         const int4* p = reinterpret_cast<const int4*>(B.seg + 2 * (size_t)read + lane);
-        const int4 a = __ldg(p), f = __ldg(p + 1), o = __ldg(p + 2);
+        r.a = __ldg(p); r.f = __ldg(p + 1); r.o = __ldg(p + 2);
+    }
+    return r;
+}
+__device__ __forceinline__ void commit_rec(const Batch& B, const RecRegs& r, Rec& rec, int lane) {
+    if (lane < 2) {
+        const bool single = r.single != 0;
+        const int4 a = r.a, f = r.f, o = r.o;
         const bool have = lane == 0 || !single;
         const long long cig_off = ((long long)(unsigned)o.y << 32) | (unsigned)o.x, seq_off = ((long long)(unsigned)o.w << 32) | (unsigned)o.z;
         Seg s;
@@ -431,8 +490,75 @@ __device__ int pick_jobs(const Rec& acc, const Rec& mem, const int* v, Job* jobs
     return 1;
 }
 
+// The merged string becomes a segment of the running record.
+__device__ void set_merged(Seg& t, const OutBuf& o, int start, int end, bool known_plain_ops) {
+    t.start = start; t.end = end;
+    t.n_ops = o.n_ops; t.n_seq = o.n_seq;
+    t.cig = o.cig; t.seq = o.seq; t.qual = o.qual;
+    t.lead = t.trail = t.lead_h = 0;                     // merges drop the clips
+    // A merged record takes min / max of the starts / ends but drops clip columns: where a clip column of one read met no M of
+    // the other, its CIGAR is shorter than end - start + 1 (the reference walks such a record by cursor and runs off it); only
+    // a record whose CIGAR is exactly its columns may be folded in column space
+    int plain = t.n_ops == t.end - t.start + 1;
+    if (!known_plain_ops) for (int k = 0; k < t.n_ops; ++k) plain &= t.cig[k] == 'M';
+    t.plain = plain;
+}
+
+// Result rule of a paired / mixed layout (lane 0).
+__device__ void apply_result(Rec& acc, const Rec& mem, const Result rs, const OutBuf& o, bool known_plain_ops) {
+    int v[16];
+    const Rec* r[2] = {&acc, &mem};
+    for (int side = 0; side < 2; ++side)
+        for (int sg = 0; sg < 2; ++sg) { v[MB(0, side, sg, 0)] = r[side]->s[sg].start; v[MB(0, side, sg, 1)] = r[side]->s[sg].end; }
+    if (rs.take == 2) acc.s[0] = mem.s[0];
+    set_merged(acc.s[rs.seg], o, min(v[rs.sa], v[rs.sb]), max(v[rs.ea], v[rs.eb]), known_plain_ops);
+    if (rs.single != 2) acc.single = rs.single;
+    if (rs.take == 1) acc.s[1] = mem.s[1];
+}
+
+// One job through the layout table: all lanes evaluate it in column space when every segment taking part is plain and the
+// cursors stay on the columns; otherwise lane 0 walks it as the reference does. ctl[2] >= 0 afterwards: it ran in column space.
+__device__ __noinline__ int generic_job(const Rec& acc, const Rec& mem, int lay, OutBuf& o, const uint8_t* tab, int lane, PlainPhase* ph_sm, int* ctl,
+                                        unsigned long long& n_plain, unsigned long long& n_walk) {
+    const Layout& L = c_layout[lay];
+    Walk w;
+    set_bounds(w, acc, mem);
+    if (lane == 0) {
+        bool all_plain = true;
+        for (int k = 0; k < 11 && L.ph[k].op != P_END; ++k) {
+            const Phase ph = L.ph[k];
+            if (ph.op == P_TLT || ph.op == P_SEAT) all_plain &= w.seg[ph.x][ph.y]->plain != 0;
+            else if (ph.op == P_OVL || ph.op == P_OVL2 || ph.op == P_OVLQX) all_plain &= w.seg[0][ph.x]->plain != 0 && w.seg[1][ph.y]->plain != 0;
+        }
+        ctl[2] = all_plain ? plain_phases(w, L, ph_sm) : -1;
+    }
+    __syncwarp();
+    const int n_ph = ctl[2];
+    if (n_ph >= 0) {
+        plain_emit(w, ph_sm, n_ph, o, tab, lane);
+        n_plain += lane == 0;
+        return HC_MERGE_OK;
+    }
+    __syncwarp();
+    if (lane == 0) {
+        w.o = &o;
+        ctl[3] = walk_layout(w, L, tab);
+        ctl[0] = o.n_ops; ctl[1] = o.n_seq;
+    }
+    __syncwarp();
+    o.n_ops = ctl[0]; o.n_seq = ctl[1];
+    n_walk += lane == 0;
+    return ctl[3];
+}
+
+__device__ __noinline__ int pick_jobs_general(const Rec& acc, const Rec& mem, Job* jobs) {
+    Walk w0;
+    set_bounds(w0, acc, mem);
+    return pick_jobs(acc, mem, w0.v, jobs);
+}
+
 // Dynamic shared memory: the two Phred tables, then per warp 4 segment buffers (segment x generation) of 3 byte streams.
-__global__ void __launch_bounds__(kWarps * 32) merge_cliques_kernel(Batch B) {
+__global__ void __launch_bounds__(kWarps * 32, 1) merge_cliques_kernel(Batch B) {
     extern __shared__ __align__(16) uint8_t smem[];
     uint8_t* tab = smem;
     for (int i = threadIdx.x; i < 2 * NQ * NQ; i += blockDim.x) tab[i] = B.tab[i];
@@ -440,9 +566,9 @@ __global__ void __launch_bounds__(kWarps * 32) merge_cliques_kernel(Batch B) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint8_t* slice = smem + kTabBytes + (size_t)warp * kSlice;
     __shared__ Rec s_acc[kWarps], s_mem[kWarps];
-    __shared__ PlainPhase s_ph[kWarps][12];
+    __shared__ PlainPhase s_ph[kWarps][11];
     __shared__ Job s_jobs[kWarps][2];
-    __shared__ int s_ctl[kWarps][4];
+    __shared__ int s_ctl[kWarps][5];
     Rec& acc = s_acc[warp];
     Rec& mem = s_mem[warp];
     unsigned long long n_plain = 0, n_walk = 0;
@@ -462,91 +588,71 @@ __global__ void __launch_bounds__(kWarps * 32) merge_cliques_kernel(Batch B) {
                 o.cig = B.scr_cig + at; o.seq = B.scr_seq + at; o.qual = B.scr_qual + at;
             }
             o.n_ops = o.n_seq = 0;
+            o.cap = (int)cap;
             return o;
         };
         int gen[2] = {0, 0};
         int status = HC_MERGE_OK;
-        load_rec(B, B.members[m0], acc, lane);
+        // the member indices of the clique, one per lane (cliques of more than 32 reads fetch the rest as they go)
+        const int my_member = lane < m ? __ldg(B.members + m0 + lane) : -1;
+        commit_rec(B, fetch_rec(B, __shfl_sync(0xffffffffu, my_member, 0), lane), acc, lane);
+        RecRegs next = fetch_rec(B, m > 1 ? __shfl_sync(0xffffffffu, my_member, 1) : -1, lane);
         __syncwarp();
         for (int f = 1; f < m && status == HC_MERGE_OK; ++f) {
-            load_rec(B, B.members[m0 + f], mem, lane);
-            __syncwarp();
-            if (lane == 0) {
-                Walk w0;
-                set_bounds(w0, acc, mem);
-                s_ctl[warp][3] = pick_jobs(acc, mem, w0.v, s_jobs[warp]);
+            commit_rec(B, next, mem, lane);
+            {
+                int nr = -1;
+                if (f + 1 < m) nr = f + 1 < 32 ? __shfl_sync(0xffffffffu, my_member, (f + 1) & 31) : __ldg(B.members + m0 + f + 1);   // f, m: warp-uniform
+                next = fetch_rec(B, nr, lane);
             }
             __syncwarp();
-            const int n_jobs = s_ctl[warp][3];
+            if (lane == 0) {
+                if (acc.single && mem.single) { s_jobs[warp][0] = Job{LAY_SINGLE, 0}; s_ctl[warp][4] = 1; }
+                else s_ctl[warp][4] = pick_jobs_general(acc, mem, s_jobs[warp]);
+            }
+            __syncwarp();
+            const int n_jobs = s_ctl[warp][4];
             for (int job = 0; job < n_jobs && status == HC_MERGE_OK; ++job) {
                 const int lay = s_jobs[warp][job].lay, after = s_jobs[warp][job].after;
-                const Layout& L = c_layout[lay];
-                const int tgt = L.res.seg;
-                OutBuf o = buffer(tgt, gen[tgt] ^ 1);
-                Walk w;
-                set_bounds(w, acc, mem);
-                // ---- plain folds: all lanes, column space; anything else: lane 0 walks it
-                if (lane == 0 && lay >= LAY_SINGLE) {
-                    // mergeAlignmentRecordsSingle on two plain segments that overlap or abut: the leader's tail, the overlap and
-                    // the trailer's tail are one run of columns [min start, max end]; a column emits where either read shows M
+                int rc;
+                if (lay >= LAY_SINGLE) {
+                    // ---- mergeAlignmentRecordsSingle(ar, i, j): the bulk of all folds
                     const int i = (lay - LAY_SINGLE) >> 1, j = (lay - LAY_SINGLE) & 1;
-                    const Seg& sa = acc.s[i]; const Seg& sb = mem.s[j];
-                    const int xas = sa.start - sa.lead, xae = sa.end + sa.trail, xbs = sb.start - sb.lead, xbe = sb.end + sb.trail;
-                    if (sa.plain && sb.plain && max(xas, xbs) <= min(xae, xbe) + 1) {
-                        s_ph[warp][0] = PlainPhase{min(xas, xbs), max(xae, xbe) + 1, i, 2 + j};
-                        s_ctl[warp][2] = 1;
-                    } else s_ctl[warp][2] = -1;
-                } else if (lane == 0) {
-                    bool all_plain = true;
-                    for (int k = 0; k < 11 && L.ph[k].op != P_END; ++k) {
-                        const Phase ph = L.ph[k];
-                        if (ph.op == P_TLT || ph.op == P_SEAT) all_plain &= w.seg[ph.x][ph.y]->plain != 0;
-                        else if (ph.op == P_OVL || ph.op == P_OVL2 || ph.op == P_OVLQX) all_plain &= w.seg[0][ph.x]->plain != 0 && w.seg[1][ph.y]->plain != 0;
+                    const int tgt = (i | j) ? 1 : 0;
+                    OutBuf o = buffer(tgt, gen[tgt] ^ 1);
+                    const Seg sa = acc.s[i], sb = mem.s[j];
+                    const bool fast = sa.plain && sb.plain && max(sa.start - sa.lead, sb.start - sb.lead) <= min(sa.end + sa.trail, sb.end + sb.trail) + 1;
+                    if (fast) {
+                        single_plain_fold(sa, sb, o, tab, lane);
+                        rc = HC_MERGE_OK;
+                        n_plain += lane == 0;
+                    } else {
+                        rc = generic_job(acc, mem, lay, o, tab, lane, s_ph[warp], s_ctl[warp], n_plain, n_walk);
                     }
-                    s_ctl[warp][2] = all_plain ? plain_phases(w, L, s_ph[warp]) : -1;
-                }
-                __syncwarp();
-                const int n_ph = s_ctl[warp][2];
-                int rc = HC_MERGE_OK;
-                if (n_ph >= 0) {
-                    plain_emit(w, s_ph[warp], n_ph, o, tab, lane);
-                    n_plain += lane == 0;
-                } else {
                     __syncwarp();
+                    if (rc != HC_MERGE_OK) { status = rc; break; }
                     if (lane == 0) {
-                        w.o = &o;
-                        s_ctl[warp][2] = walk_layout(w, L, tab);
-                        s_ctl[warp][0] = o.n_ops; s_ctl[warp][1] = o.n_seq;
+                        // result rules of :685-729: (1,1) -> segment 1, single_end; (1,2) -> segment 2 formed from start1 / end1,
+                        // flag untouched; (2,1), (2,2) -> segment 2, paired
+                        Seg& t = acc.s[tgt];
+                        const int st = min(sa.start, sb.start), en = max(sa.end, sb.end);
+                        set_merged(t, o, st, en, fast);
+                        if ((i | j) == 0) acc.single = 1; else if (i == 1) acc.single = 0;
+                        if (after == 1) acc.single = 0;
+                        if (after == 2) { acc.s[1] = mem.s[1]; acc.single = 0; }
+                        if (after == 3) { acc.s[0] = mem.s[0]; acc.single = 0; }
                     }
+                    gen[tgt] ^= 1;
+                } else {
+                    // ---- a paired / mixed layout: its program, walked or (plain segments) evaluated in column space
+                    const int tgt = c_layout[lay].res.seg;
+                    OutBuf o = buffer(tgt, gen[tgt] ^ 1);
+                    rc = generic_job(acc, mem, lay, o, tab, lane, s_ph[warp], s_ctl[warp], n_plain, n_walk);
                     __syncwarp();
-                    rc = s_ctl[warp][2];
-                    o.n_ops = s_ctl[warp][0]; o.n_seq = s_ctl[warp][1];
-                    n_walk += lane == 0;
+                    if (rc != HC_MERGE_OK) { status = rc; break; }
+                    if (lane == 0) apply_result(acc, mem, c_layout[lay].res, o, s_ctl[warp][2] >= 0);
+                    gen[tgt] ^= 1;
                 }
-                __syncwarp();
-                if (rc != HC_MERGE_OK) { status = rc; break; }
-                // ---- the result rule: lane 0 updates the running record
-                if (lane == 0) {
-                    const Result rs = L.res;
-                    if (rs.take == 2) acc.s[0] = mem.s[0];
-                    Seg& t = acc.s[tgt];
-                    t.start = min(w.v[rs.sa], w.v[rs.sb]); t.end = max(w.v[rs.ea], w.v[rs.eb]);
-                    t.n_ops = o.n_ops; t.n_seq = o.n_seq;
-                    t.cig = o.cig; t.seq = o.seq; t.qual = o.qual;
-                    t.lead = t.trail = t.lead_h = 0;                     // merges drop the clips
-                    // A merged record takes min / max of the starts / ends but drops clip columns: where a clip column of one
-                    // read met no M of the other, its CIGAR is shorter than end - start + 1 (the reference walks such a record
-                    // by cursor and runs off it); only a record whose CIGAR is exactly its columns may be folded in column space
-                    int plain = t.n_ops == t.end - t.start + 1;
-                    if (n_ph < 0) for (int k = 0; k < t.n_ops; ++k) plain &= t.cig[k] == 'M';
-                    t.plain = plain;
-                    if (rs.single != 2) acc.single = rs.single;
-                    if (rs.take == 1) acc.s[1] = mem.s[1];
-                    if (after == 1) acc.single = 0;
-                    if (after == 2) { acc.s[1] = mem.s[1]; acc.single = 0; }
-                    if (after == 3) { acc.s[0] = mem.s[0]; acc.single = 0; }
-                }
-                gen[tgt] ^= 1;
                 __syncwarp();
             }
         }
@@ -613,7 +719,7 @@ struct hc_merger {
     // the read set (hc_merger_set_reads)
     int n_reads = 0;
     std::vector<uint8_t> single_end;
-    std::vector<int32_t> cig_len;
+    std::vector<int32_t> cig_len, seg_xs, seg_xe, seg_ins;      // per segment row: CIGAR length, extended start / end, I ops
     uint8_t* d_single = nullptr;
     uint8_t *d_cig = nullptr, *d_seq = nullptr, *d_qual = nullptr, *d_tab = nullptr;
     SegHdr* d_seg = nullptr; size_t cap_seghdr = 0;
@@ -716,6 +822,7 @@ int hc_merger_set_reads(hc_merger* m, const hc_reads* rd) {
     // computeRevOffset, :126-156), H ops among the leading clips (they consume no query), and whether the segment is "plain":
     // clips, M only, clips, with a CIGAR that consumes no more query than there is and is exactly the segment's columns.
     int bad = 0;
+    std::vector<int32_t> xs((size_t)std::max(2 * n, 2), 0), xe((size_t)std::max(2 * n, 2), 0), ins((size_t)std::max(2 * n, 2), 0);
     std::vector<SegHdr> hdr((size_t)std::max(2 * n, 2));
     std::memset(hdr.data(), 0, hdr.size() * sizeof(SegHdr));
     hc::parallel_ranges(n, 4096, [&](int r0, int r1) {
@@ -740,6 +847,9 @@ int hc_merger_set_reads(hc_merger* m, const hc_reads* rd) {
                 }
                 if (cons > rd->seq_len[k]) plain = 0;
                 if (nc != lead + trail + (rd->seg_end[k] - rd->seg_start[k] + 1)) plain = 0;
+                int n_ins = 0;
+                for (int i = 0; i < nc; ++i) n_ins += cg[i] == 'I';
+                xs[(size_t)k] = rd->seg_start[k] - lead; xe[(size_t)k] = rd->seg_end[k] + trail; ins[(size_t)k] = n_ins;
                 SegHdr& h = hdr[(size_t)k];
                 h.start = rd->seg_start[k]; h.end = rd->seg_end[k]; h.n_ops = nc; h.n_seq = rd->seq_len[k];
                 h.lead = lead; h.trail = trail; h.lead_h = lead_h; h.plain = plain;
@@ -767,6 +877,7 @@ int hc_merger_set_reads(hc_merger* m, const hc_reads* rd) {
     m->n_reads = n;
     m->single_end.assign(rd->single_end, rd->single_end + n);
     m->cig_len.assign(rd->cig_len, rd->cig_len + 2 * (size_t)n);
+    m->seg_xs.swap(xs); m->seg_xe.swap(xe); m->seg_ins.swap(ins);
     MG_TRY(m, cudaStreamSynchronize(m->stream));
     return HC_OK;
 }
@@ -781,17 +892,25 @@ int hc_merge_run(hc_merger* m, int32_t n_cliques, const int64_t* member_off, con
     if (total_seq) *total_seq = 0;
     if (kernel_ms) *kernel_ms = 0.f;
     if (n_cliques == 0) { m->out_ops = m->out_seq = 0; m->have_result = true; return HC_OK; }
-    // capacity of one segment of clique c: the members' CIGAR lengths summed (a merged segment cannot be longer)
+    // capacity of one segment of clique c: a fold emits one op per reference column it passes (M / D) or per insertion it
+    // takes over, so a merged segment holds at most (columns the members span, clips included) + (their I ops) ops -- and never
+    // more than the members' CIGAR lengths summed
     std::vector<int64_t> resoff((size_t)n_cliques + 1), scroff((size_t)n_cliques + 1);
     int64_t rat = 0, sat = 0;
     for (int c = 0; c < n_cliques; ++c) {
         if (member_off[c + 1] <= member_off[c]) return bad_arg(m, "hc_merge_run: empty clique");
-        int64_t cap = 0;
+        int64_t cap = 0, n_ins = 0;
+        int32_t lo = INT_MAX, hi = INT_MIN;
         for (int64_t k = member_off[c]; k < member_off[c + 1]; ++k) {
             const int r = members[k];
             if (r < 0 || r >= m->n_reads) return bad_arg(m, "hc_merge_run: member index out of range");
-            cap += m->cig_len[2 * (size_t)r] + (m->single_end[r] ? 0 : m->cig_len[2 * (size_t)r + 1]);
+            for (int sg = 0; sg < (m->single_end[r] ? 1 : 2); ++sg) {
+                const size_t row = 2 * (size_t)r + sg;
+                cap += m->cig_len[row]; n_ins += m->seg_ins[row];
+                lo = std::min(lo, m->seg_xs[row]); hi = std::max(hi, m->seg_xe[row]);
+            }
         }
+        if (hi >= lo) cap = std::min<int64_t>(cap, (int64_t)hi - lo + 1 + n_ins);
         cap = std::max<int64_t>(16, (cap + 15) & ~(int64_t)15);
         resoff[c] = rat; scroff[c] = sat;
         rat += 2 * cap;
