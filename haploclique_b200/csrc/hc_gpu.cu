@@ -812,9 +812,16 @@ void build_items_range(hc_ctx* c, int w0, int w1, int n_ctas, std::vector<int4>&
     }
     long long chunk = (total + (long long)n_ctas * 16 - 1) / ((long long)n_ctas * 16);
     chunk = std::max<long long>(32, std::min<long long>(chunk, 4096));
+    const size_t item0 = items.size();
     for (size_t b = 0; b < blks.size(); ++b)
         for (long long r = first[b]; r <= last[b]; r += chunk)
             items.push_back(make_int4((int)(base_blk + b), (int)r, (int)std::min<long long>(r + chunk, (long long)last[b] + 1), 0));
+    // Order of the items = order in which the persistent CTAs take them. Row-major (HC_ITEM_ORDER=rows): the CTAs running at
+    // the same time work on the same few thousand rows against different column blocks, so a row's stream comes from HBM
+    // once and from L2 afterwards; block-major (the default until measured otherwise): they share a column block instead.
+    static const bool by_rows = [] { const char* e = std::getenv("HC_ITEM_ORDER"); return e && e[0] == 'r'; }();
+    if (by_rows)
+        std::stable_sort(items.begin() + item0, items.end(), [chunk](const int4& a, const int4& b) { return a.y / chunk < b.y / chunk; });
 }
 
 // Adjacency words per row window (HC_WINDOW_WORDS overrides): the rows of a band are scored in windows so that the words

@@ -364,7 +364,8 @@ void hc_packed_free(hc_packed* p) {
     delete p;
 }
 
-// Rows -> parts for several GPUs: cuts at equal shares of the prefix sum of the band widths; a part's
+// Rows -> parts for several GPUs: cuts at equal shares of the scoring work (scored pairs, weighted by the
+// columns they share); a part's
 // halo starts at the smallest band start (col0) of its rows. col0 exactly as compute_layout() in hc_gpu.cu defines it.
 int hc_partition_rows(const int32_t* cov_first, const int32_t* cov_last, int32_t n, int32_t n_parts, int32_t* cuts, int32_t* first) {
     if (!cov_first || !cov_last || !cuts || !first || n < 0 || n_parts < 1) {
@@ -379,7 +380,38 @@ int hc_partition_rows(const int32_t* cov_first, const int32_t* cov_last, int32_t
         for (int i = k0; i < k1; ++i)
             col0[i] = (int32_t)(std::lower_bound(pmax.begin(), pmax.begin() + i, cov_first[i]) - pmax.begin()) & ~31;
     });
-    for (int i = 0; i < n; ++i) acc[i + 1] = acc[i] + (i - col0[i]);
+    // Weight of row i = what it costs to score: a per-pair part and a per-column part. Pairs: the earlier reads whose covered
+    // interval reaches cov_first[i] (the band width i - col0[i] overstates them: one long earlier read widens the band of every
+    // later row). Columns: the length of the intersection of the covered spans, min(last_i, last_j) - first_i + 1, summed over
+    // those reads. Both come from two Fenwick trees (count, sum of cov_last) over the ranks of cov_last. The ratio -- one pair
+    // costs as much as kColumnsPerPair shared columns -- is measured (C3 on B200: 5.3e-8 ms per pair, 2.5e-10 ms per column).
+    {
+        constexpr int64_t kColumnsPerPair = 215;
+        std::vector<int32_t> lasts(cov_last, cov_last + n);
+        std::sort(lasts.begin(), lasts.end());
+        lasts.erase(std::unique(lasts.begin(), lasts.end()), lasts.end());
+        const int m = (int)lasts.size();
+        std::vector<int32_t> cnt((size_t)m + 1, 0);
+        std::vector<int64_t> sum((size_t)m + 1, 0);
+        auto prefix = [&](int r, int64_t& c, int64_t& sm) {          // over ranks 1..r
+            c = 0; sm = 0;
+            for (int k = r; k > 0; k -= k & -k) { c += cnt[k]; sm += sum[k]; }
+        };
+        for (int i = 0; i < n; ++i) {
+            const int rf = (int)(std::lower_bound(lasts.begin(), lasts.end(), cov_first[i]) - lasts.begin());   // lasts[0..rf) < first_i
+            const int rl = (int)(std::lower_bound(lasts.begin(), lasts.end(), cov_last[i]) - lasts.begin());    // lasts[0..rl) < last_i
+            int64_t c_f, s_f, c_l, s_l;
+            prefix(rf, c_f, s_f);
+            prefix(std::max(rl, rf), c_l, s_l);
+            const int64_t scored = i - c_f;                           // cov_last[j] >= first_i
+            const int64_t inside = c_l - c_f, inside_sum = s_l - s_f; // first_i <= cov_last[j] < last_i
+            const int64_t beyond = scored - inside;                   // cov_last[j] >= last_i
+            const int64_t span = std::max<int64_t>(0, (int64_t)cov_last[i] - cov_first[i] + 1);
+            const int64_t columns = inside_sum - inside * ((int64_t)cov_first[i] - 1) + beyond * span;
+            acc[(size_t)i + 1] = acc[i] + kColumnsPerPair * scored + std::max<int64_t>(columns, 0);
+            for (int k = rl + 1; k <= m; k += k & -k) { cnt[k]++; sum[k] += cov_last[i]; }
+        }
+    }
     cuts[0] = 0;
     for (int p = 1; p < n_parts; ++p) {
         const int64_t want = acc[n] / n_parts * p + acc[n] % n_parts * p / n_parts;

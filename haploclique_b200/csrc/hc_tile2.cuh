@@ -82,8 +82,13 @@ __global__ void __launch_bounds__(256) build_formats_kernel(const uint16_t* __re
 //   opsB  : the lane's column of the transposed tile (32-bit word w at opsB[w*32], two B-records per word)
 //   rawA/rawB : the raw 16-bit records of the two reads in global memory, for the generic steps only
 // A-word + B-record is the shared-space address of the factor (the tile's records carry the table base).
+#ifdef HC_T2_NOINLINE_OVERLAP
+#define HC_T2_OVL_INLINE __noinline__
+#else
+#define HC_T2_OVL_INLINE __forceinline__
+#endif
 template <bool SPLIT>
-__device__ __forceinline__ void overlap2(const Args2& a, const int* hA, const int* hB, const uint32_t* opsA, const uint32_t* opsB,
+__device__ HC_T2_OVL_INLINE void overlap2(const Args2& a, const int* hA, const int* hB, const uint32_t* opsA, const uint32_t* opsB,
                                          const uint16_t* rawA, const uint16_t* rawB, uint32_t m, Lane& L, int shape) {
     const uint32_t op = m & 15u;
     bool more = (op == M_OVL || op == M_OVL2 || op == M_OVLQX || op == M_SOVL) && !L.gap && !L.undef;
@@ -396,7 +401,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) score_tile2_kernel(const Ar
                     if (!L.undef) {
                         if (MAP) prob0 = prob0_run;
                         else if (L.tc >= a.P.ladder_len) L.undef = true;
-                        else prob0 = __ldg(a.P.ladder + L.tc);
+                        else if (!a.P.no_prob0 || a.detail != nullptr) prob0 = __ldg(a.P.ladder + L.tc);   // with no_prob0 only the detail output shows it
                     }
                     if (L.undef) status = HC_ST_UNDEFINED;
                     else if (!L.gap && L.cc != 0) {
@@ -415,7 +420,9 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) score_tile2_kernel(const Ar
                         }
                     }
                 }
+#ifndef HC_T2_NO_ADJ_WRITE      /* experiment: how much of the pass the scattered atomicOr costs (profiles/r02_adjacency_write_cost.txt) */
                 if (edge) atomicOr(&a.adj[infA.word_off + (rel >> 5)], 1u << (rel & 31));
+#endif
                 if (a.detail != nullptr && active && rel >= 0) {
                     hc_pair_result r;
                     r.status = status; r.edge = edge; r.gap = L.gap; r.cc = L.cc; r.tc = L.tc; r.ambiguous = ambiguous;
@@ -426,7 +433,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) score_tile2_kernel(const Ar
                     const unsigned long long slot = atomicAdd(&a.stats->ambiguous, 1ull);
                     if (a.amb != nullptr && slot < (unsigned long long)a.amb_cap) {
                         hc_ambiguous am;
-                        am.i = i; am.j = j; am.cc = L.cc; am.tc = L.tc; am.probM = L.probM; am.prob0 = prob0;
+                        am.i = i; am.j = j; am.cc = L.cc; am.tc = L.tc; am.probM = L.probM;
+                        am.prob0 = (!MAP && a.P.no_prob0 && a.detail == nullptr) ? __ldg(a.P.ladder + L.tc) : prob0;
                         am.score = score; am.cutoff = cutoff; am.edge = edge; am.edge_device = edge;
                         a.amb[slot] = am;
                     }

@@ -16,7 +16,7 @@ import numpy as np
 from .records import AlignmentRecord, ReadBatch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhcgpu.so")
+LIB_PATH = os.environ.get("HC_LIBHCGPU") or os.path.join(_HERE, "libhcgpu.so")     # HC_LIBHCGPU: an experiment build of the same library
 
 HC_OK = 0
 KERNEL_AUTO, KERNEL_GENERIC, KERNEL_TILED, KERNEL_TILED2, KERNEL_STREAMED = 0, 1, 2, 3, 4

@@ -257,8 +257,8 @@ int hc_quasi_score_band(hc_ctx* ctx, const hc_quasi_params* params, int32_t row_
 
 /* ---- Several GPUs behind one handle ----------------------------------------------------------------
  * The band shards by rows with no exchange step: a pair depends on its two reads only. hc_partition_rows cuts the
- * position-sorted batch into n_parts consecutive row ranges balanced by the prefix sum of the band widths (= ordered pairs
- * inside the band), and gives for each part the first read it has to hold: its left halo, i.e. every earlier read whose
+ * position-sorted batch into n_parts consecutive row ranges of equal scoring work (scored pairs -- pairs inside the band whose
+ * covered intervals intersect -- weighted by the columns they share), and gives for each part the first read it has to hold: its left halo, i.e. every earlier read whose
  * covered interval can reach one of its rows (from the running maximum of cov_last, not a constant). When everything
  * overlaps (deep amplicons, super-read rounds) the halo reaches read 0 and the parts become equal-area row blocks of the
  * replicated set. first[p] is a multiple of 32, so part p's local band layout is the global one shifted by first[p] and

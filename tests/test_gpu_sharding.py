@@ -44,8 +44,8 @@ def test_C3_shaped_position_windows_give_the_unsharded_words(world):
     assert words.shape == full.words.shape and (words == full.words).all()
     for k in ("pairs_scored", "pairs_walked", "edges", "sum_cc", "sum_tc"):
         assert sum(s[k] for s in stats) == full.stats[k], k
-    # balanced by pairs, not by reads
-    share = np.array([s["pairs_total"] for s in stats], float)
+    # balanced by scored pairs, not by reads
+    share = np.array([s["pairs_scored"] for s in stats], float)
     assert share.max() / share.mean() < 1.1
     # one process, `world` contexts on this GPU
     multi = edge.NewEdgeCalculator(devices=[0] * world, **kw)
@@ -75,16 +75,18 @@ def test_C4_shaped_amplicon_parts_give_the_unsharded_words():
 
 def test_super_read_round_degenerates_to_row_blocks_of_the_replicated_set():
     """BASELINE configs[4] shape: everything overlaps, so every part's halo reaches read 0 and the cuts become equal-area
-    row blocks (what SURVEY.md 8(e) prescribes when position windows degenerate)."""
+    row blocks of equal pair count (what SURVEY.md 8(e) prescribes when position windows degenerate)."""
     b = synth.super_reads(700, seed=5)
     kw = dict(bench.PARAMS, maxPosition=b.max_position() + 10)
     full = _unsharded(b, kw)
     cuts, first = edge.partition_rows(b, 4)
     assert (first == 0).all()
-    area = np.diff(cuts.astype(np.int64) ** 2)
-    assert area.max() / area.mean() < 1.2
-    words, _ = _as_ranks_do(b, kw, 4)
+    words, stats = _as_ranks_do(b, kw, 4)
     assert (words == full.words).all()
+    share = np.array([215 * s["pairs_scored"] + s["sum_cc"] for s in stats], float)
+    # the cut estimates a pair's columns from the covered spans; super-read pairs often stop early at an indel conflict, so the
+    # realised work is only roughly even
+    assert share.max() / share.mean() < 2.0 and share.min() / share.mean() > 0.5
     multi = edge.NewEdgeCalculator(devices=[0, 0, 0, 0], **kw)
     multi.upload(b)
     assert (multi.score_band().words == full.words).all()

@@ -73,7 +73,7 @@ def got_close(a, b, tol):
 @pytest.mark.timeout(300)
 def test_super_read_round_row_blocks_partition_rows_and_pairs():
     """C5 (every read overlaps most others): the halo reaches read 0, so each rank holds the reads up to the end of its
-    block of rows; the blocks partition the rows, have about equal pair area, and their scored pairs add up."""
+    block of rows; the blocks partition the rows, hold equal shares of the scoring work, and their scored pairs add up."""
     sys.path.insert(0, ROOT)
     import bench
     full, _ = bench.generate("C5", 600)
@@ -82,12 +82,20 @@ def test_super_read_round_row_blocks_partition_rows_and_pairs():
     l0, b0, f0 = bench.shard(full, 0, 2)
     l1, b1, f1 = bench.shard(full, 1, 2)
     assert b0 == 0 and f0 == 0 and f1 == 0 and l0.n == b1 and l1.n == full.n
-    assert abs(l0.n * (l0.n - 1) / 2 - full.n * (full.n - 1) / 4) < 0.03 * full.n * full.n      # equal pair area
+    # equal shares of the scoring work: 215 per scored pair + the columns the covered spans share (super-reads: the columns count)
+    def work(batch, row_begin):
+        w = 0
+        for i in range(row_begin, batch.n):
+            hit = batch.cov_last[:i] >= batch.cov_first[i]
+            w += 215 * int(hit.sum()) + int((np.minimum(batch.cov_last[:i][hit], batch.cov_last[i]) - batch.cov_first[i] + 1).clip(0).sum())
+        return w
+    w0, w1 = work(l0, 0), work(l1, b1)
+    assert abs(w0 - w1) < 0.03 * (w0 + w1)
     assert _run(2, "C5", 600, 29300 + os.getpid() % 300) == want
 
 
 def test_partition_is_balanced_by_band_pairs_and_slices_rebase():
-    """hc_partition_rows / hc_packed_slice on the host: cuts at equal shares of the band-width prefix sum; a slice's
+    """hc_partition_rows / hc_packed_slice on the host: cuts at equal shares of the scoring work (scored pairs weighted by shared columns); a slice's
     headers are the parent's with the op offsets re-based and its records are the parent's."""
     import ctypes as C
     sys.path.insert(0, ROOT)
@@ -100,9 +108,10 @@ def test_partition_is_balanced_by_band_pairs_and_slices_rebase():
         assert cuts[0] == 0 and cuts[-1] == full.n and (np.diff(cuts) >= 0).all() and (first % 32 == 0).all()
         pmax = np.maximum.accumulate(full.cov_last)
         col0 = np.minimum(np.searchsorted(pmax, full.cov_first, side="left"), np.arange(full.n)) & ~31
-        width = np.arange(full.n) - col0
-        share = np.array([width[cuts[p]:cuts[p + 1]].sum() for p in range(parts)], float)
-        assert share.max() - share.min() <= 2 * width.max()
+        # the weight of a row = the pairs it scores: earlier reads whose covered interval reaches its first covered position
+        scored = np.array([int((full.cov_last[col0[i]:i] >= full.cov_first[i]).sum()) for i in range(full.n)])
+        share = np.array([scored[cuts[p]:cuts[p + 1]].sum() for p in range(parts)], float)
+        assert share.max() / share.mean() < 1.15             # the weight also counts the columns the pairs share
         for p in range(parts):
             assert first[p] == (col0[cuts[p]:cuts[p + 1]].min() if cuts[p + 1] > cuts[p] else cuts[p] & ~31)
     pk = edge.PackedBatch(full)
