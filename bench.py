@@ -7,7 +7,8 @@ Workloads (synthetic, seeded; `config.workload` names the one ti
   C2  the same mix at 100k fragments (BASELINE configs[1])                      -- `also.C2` at N=1, or --workload C2
   C4  1.5 kb amplicon, 2x150 reads, dense tiles (BASELINE configs[3])           -- `also.C4` at 200k fragments; full size
       (1M fragments = 2M reads, 2.3e11 scored pairs, 20 s per pass) with --workload C4
-  C5  a super-read round: 4000 records of 0.5-9.7 kb, 76 quality codes (BASELINE configs[4]) -- `also.C5`
+  C5  a super-read round: 4000 records of 0.5-9.7 kb, 76 quality codes (BASELINE configs[4]) -- `also.C5` (synthetic shape up
+      to full-length haplotypes) and `also.C5r` (a round captured from the reference's own loop: 3529 Clique_* records)
 A step = one pass of the hot path over the whole read set: every ordered pair (later read i, earlier read j) inside
 the sorted-start band is decided exactly as NewEdgeCalculator::edgeBetween would and the banded adjacency bitset is
 produced. "Scored" pairs = pairs that pass the reference's first reject (covered intervals intersect,
@@ -68,6 +69,12 @@ def generate(name, n_frag=None, workers=1):
     C3 / C4 are drawn in chunks of 50k fragments (the same reads whatever `workers` is)."""
     from haploclique_b200 import synth
     from haploclique_b200.records import ReadBatch
+    if name == "C5r":
+        # a super-read round captured from the unmodified reference's own loop (tests/golden/make_superread_rounds.py): the
+        # input of round 1 on 1000 synthetic fragments, 3529 records (3515 Clique_*), 90 quality codes
+        b = ReadBatch.load(os.path.join(ROOT, "tests", "golden", "superreads_synth_it1.npz"))
+        return b, dict(n_frag=b.n, frag_min=int(b.cig_len.reshape(-1, 2).sum(1).min()), frag_max=int(b.cig_len.reshape(-1, 2).sum(1).max()),
+                       genome_len=2500, captured=True)
     if name == "C5":
         kw = dict(synth.C5)
         n = n_frag or kw["n_frag"]
@@ -98,6 +105,9 @@ def shard(batch, rank, world):
 
 
 def workload_text(name, cfg):
+    if name == "C5r":
+        return ("C5r: super-read round captured from the reference's own loop (input of round 1 on 1000 synthetic fragments, genome 2500, "
+                "seed 11): %d records of %d-%d ops, Clique_* names, 90 quality codes" % (cfg["n_frag"], cfg["frag_min"], cfg["frag_max"]))
     if name == "C5":
         return "C5: synthetic super-read round, %d records of %d-%d columns (70 %% Clique_*, posterior qualities up to char 126), genome %d, seed %d" % (
             cfg["n_frag"], cfg["frag_min"], cfg["frag_max"], cfg["genome_len"], SEED)
@@ -344,7 +354,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="auto", choices=["auto", "C2", "C3", "C4", "C5"])
+    ap.add_argument("--workload", default="auto", choices=["auto", "C2", "C3", "C4", "C5", "C5r"])
     ap.add_argument("--params", default="defaults + no_prob0", choices=sorted(PARAM_SETS))
     ap.add_argument("--n-frag", type=int, default=0, help="override the fragment count (debugging only)")
     ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "tiled", "tiled2", "streamed"])
@@ -363,7 +373,7 @@ def main():
             return 0
         # the CPU arm scores a bounded sample; a 100k-fragment draw of the same mix has the same local read density
         from haploclique_b200 import synth
-        full = (synth.C5 if wname == "C5" else synth.CONFIGS[wname])["n_frag"]
+        full = 3529 if wname == "C5r" else (synth.C5 if wname == "C5" else synth.CONFIGS[wname])["n_frag"]
         n_draw = min(args.n_frag or full, 100_000)
         batch, cfg = generate(wname, n_draw, workers=min(cores, 8))
         cfg["n_frag"] = args.n_frag or full
@@ -520,6 +530,7 @@ def main():
                                                         local_rank, peaks, min(k, 3), cores, with_cpu)
             also["C4"] = also_leg("C4", 200_000, "defaults + no_prob0", local_rank, peaks, min(k, 3), cores, with_cpu)
             also["C5"] = also_leg("C5", None, "defaults + no_prob0", local_rank, peaks, k, cores, with_cpu)
+            also["C5r"] = also_leg("C5r", None, "defaults + no_prob0", local_rank, peaks, k, cores, with_cpu)
             out["also"] = also
         print(json.dumps(out))
     if world > 1:

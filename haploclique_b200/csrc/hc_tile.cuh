@@ -73,6 +73,7 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     const uint32_t addr = smem_u32(bar);
+    unsigned long long t0 = 0;
     for (unsigned spins = 0;; ++spins) {
         uint32_t ok;
         asm volatile(
@@ -82,7 +83,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
             "selp.u32 %0, 1, 0, p;\n"
             "}\n" : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
         if (ok) return;
-        if (spins > (1u << 24)) __trap();           // a bulk copy that never lands must fail loudly, not hang the GPU
+        // a bulk copy that never lands must fail loudly, not hang the GPU: give up after two seconds of wall clock (the
+        // nanosecond timer is read only every 4096 polls)
+        if ((spins & 4095u) == 4095u) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 2000000000ull) __trap();
+        }
     }
 }
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {

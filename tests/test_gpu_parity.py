@@ -487,3 +487,31 @@ def test_pair_list_and_quasi_pair_list_share_one_context():
     q2 = quasi_pairs(200_000)
     new_pairs(pi.shape[0])
     assert (q2[:100_000]["q"].view(np.uint64) == q1["q"].view(np.uint64)).all()
+
+
+def test_super_read_rounds_captured_from_the_reference_loop():
+    """BASELINE configs[4] on the real thing: the inputs of rounds 1-3 of the reference's own loop (unmodified CLEVER,
+    CliqueCollector and merge; tests/golden/make_superread_rounds.py) on 1000 synthetic fragments. Round 1 (3529 Clique_*
+    records, 90 quality codes): every band kernel that takes it produces the same words, the edge count is the one the
+    reference's loop printed for that round (341035), and a sample of band pairs matches the oracle on every field. Rounds 2
+    and 3 (391 / 215 records): every band slot against the oracle."""
+    import bench
+    b = common.load_batch("superreads_synth_it1.npz")
+    assert b.n == 3529 and int(b.is_clique.sum()) == 3515
+    kw = dict(bench.PARAMS, maxPosition=2700)
+    calc = edge.NewEdgeCalculator(**kw)
+    calc.upload(b)
+    res = {}
+    for name, mode in (("auto", edge.KERNEL_AUTO), ("streamed", edge.KERNEL_STREAMED), ("generic", edge.KERNEL_GENERIC)):
+        calc.set_kernel(mode)
+        res[name] = calc.score_band(amb_cap=0)
+    assert (res["auto"].words == res["generic"].words).all() and (res["streamed"].words == res["generic"].words).all()
+    assert res["generic"].count() == 341035                     # "1: 391  edges: 341035" of the reference CLI on this input
+    rng = np.random.default_rng(2)
+    i = rng.integers(200, b.n, 60_000).astype(np.int32)
+    j = (i - rng.integers(1, 200, i.size)).astype(np.int32)
+    common.assert_pairs_equal(calc.score_pairs(i, j), pyoracle.Oracle(b, **kw).pairs(i, j), "captured round 1")
+    for it, n in ((2, 391), (3, 215)):
+        bb = common.load_batch("superreads_synth_it%d.npz" % it)
+        assert bb.n == n
+        _tiled_detail_vs_oracle(bb, kw, "captured round %d" % it, edge.KERNEL_STREAMED)
