@@ -515,3 +515,6 @@ def test_super_read_rounds_captured_from_the_reference_loop():
         bb = common.load_batch("superreads_synth_it%d.npz" % it)
         assert bb.n == n
         _tiled_detail_vs_oracle(bb, kw, "captured round %d" % it, edge.KERNEL_STREAMED)
+    c2 = edge.NewEdgeCalculator(**kw)
+    c2.upload(common.load_batch("superreads_synth_it2.npz"))
+    assert c2.score_band(amb_cap=0).count() == 1153               # the reference loop's edge count on round 2's input
