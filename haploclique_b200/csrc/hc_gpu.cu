@@ -517,7 +517,7 @@ struct hc_ctx {
     // scoring plan of the last range: row windows with their work items (build_plan)
     struct Win { int r0, r1; size_t item0, n_items; long long word0, n_words; };
     std::vector<int4> items; std::vector<int32_t> colidx; std::vector<Win> wins;
-    int plan_begin = -1, plan_end = -1, plan_ctas = 0; bool plan_windows = false;
+    int plan_begin = -1, plan_end = -1, plan_ctas = 0; bool plan_windows = false, plan_by_rows = false;
     cudaStream_t copy_stream = nullptr;                     // D2H of finished row windows, beside the compute streams
     cudaStream_t stream2 = nullptr;                         // odd row windows: their CTAs fill the SMs the previous window's tail frees
     cudaEvent_t ev_go = nullptr, ev_join = nullptr;
@@ -749,6 +749,9 @@ int item_window_div() {
     return v;
 }
 
+// The order in which the persistent CTAs take the work items: row-major unless HC_ITEM_ORDER=blocks (read at every plan build)
+bool items_by_rows() { const char* e = std::getenv("HC_ITEM_ORDER"); return !(e && e[0] == 'b'); }
+
 // Work items of the tiled kernels for rows [w0,w1) of the laid-out range (c->lay_begin .. c->lay_end).
 // Columns (the earlier reads j) are taken in windows of W consecutive reads; inside a window they are sorted by
 // (single/paired, last covered position) and cut into blocks of 32. For a later row read i the length of the
@@ -816,11 +819,12 @@ void build_items_range(hc_ctx* c, int w0, int w1, int n_ctas, std::vector<int4>&
     for (size_t b = 0; b < blks.size(); ++b)
         for (long long r = first[b]; r <= last[b]; r += chunk)
             items.push_back(make_int4((int)(base_blk + b), (int)r, (int)std::min<long long>(r + chunk, (long long)last[b] + 1), 0));
-    // Order of the items = order in which the persistent CTAs take them. Row-major (HC_ITEM_ORDER=rows): the CTAs running at
-    // the same time work on the same few thousand rows against different column blocks, so a row's stream comes from HBM
-    // once and from L2 afterwards; block-major (the default until measured otherwise): they share a column block instead.
-    static const bool by_rows = [] { const char* e = std::getenv("HC_ITEM_ORDER"); return e && e[0] == 'r'; }();
-    if (by_rows)
+    // Order of the items = order in which the persistent CTAs take them. Row-major: the CTAs running at the same time work on
+    // the same few thousand rows against different column blocks, so a row's stream and its adjacency words come from HBM
+    // once and from L2 afterwards. Block-major (HC_ITEM_ORDER=blocks, the order of generation) shares a column block instead
+    // and re-fetches the rows: C3 on one B200, ncu: 784 GB read + 43 GB written per pass against 28 GB + 4 GB row-major (L2
+    // hit rate 75 % -> 98 %), at the same kernel time (4933 -> 4927 ms) and 30 W less (profiles/r02_item_order_traffic.txt).
+    if (items_by_rows())
         std::stable_sort(items.begin() + item0, items.end(), [chunk](const int4& a, const int4& b) { return a.y / chunk < b.y / chunk; });
 }
 
@@ -835,7 +839,8 @@ constexpr int kMaxWindows = 16;
 // The scoring plan of rows [row_begin,row_end) (needs compute_layout of the same range): row windows of about equal
 // numbers of adjacency words, each with its own work items.
 void build_plan(hc_ctx* c, int row_begin, int row_end, int n_ctas, bool windows) {
-    if (c->plan_begin == row_begin && c->plan_end == row_end && c->plan_ctas == n_ctas && c->plan_windows == windows) return;
+    if (c->plan_begin == row_begin && c->plan_end == row_end && c->plan_ctas == n_ctas && c->plan_windows == windows &&
+        c->plan_by_rows == items_by_rows()) return;
     c->items.clear();
     c->colidx.clear();
     c->wins.clear();
@@ -861,7 +866,7 @@ void build_plan(hc_ctx* c, int row_begin, int row_end, int n_ctas, bool windows)
         c->wins.push_back(win);
         r = r1;
     }
-    c->plan_begin = row_begin; c->plan_end = row_end; c->plan_ctas = n_ctas; c->plan_windows = windows;
+    c->plan_begin = row_begin; c->plan_end = row_end; c->plan_ctas = n_ctas; c->plan_windows = windows; c->plan_by_rows = items_by_rows();
 }
 
 // similarityCriterion's last lines (src/NewEdgeCalculator.cpp:1132-1140) on the host, with glibc's log10: the decision for
