@@ -517,7 +517,7 @@ struct hc_ctx {
     // scoring plan of the last range: row windows with their work items (build_plan)
     struct Win { int r0, r1; size_t item0, n_items; long long word0, n_words; };
     std::vector<int4> items; std::vector<int32_t> colidx; std::vector<Win> wins;
-    int plan_begin = -1, plan_end = -1, plan_ctas = 0; bool plan_windows = false, plan_by_rows = false;
+    int plan_begin = -1, plan_end = -1, plan_ctas = 0; bool plan_windows = false, plan_by_rows = false, plan_warp_items = false;
     cudaStream_t copy_stream = nullptr;                     // D2H of finished row windows, beside the compute streams
     cudaStream_t stream2 = nullptr;                         // odd row windows: their CTAs fill the SMs the previous window's tail frees
     cudaEvent_t ev_go = nullptr, ev_join = nullptr;
@@ -688,7 +688,7 @@ TileGeom stream_geometry(const hc_ctx* c) {
     size_t o = 0;
     o += ((size_t)2 * c->K * c->K * 8 + 15) & ~(size_t)15;
     o += (size_t)tile::TP_COUNT * tile::TP_WORDS * 4;
-    o += 16 * 32 * 4;
+    o += (size_t)tile::kWarps * 16 * 32 * 4;                       // every warp's own copy of its column block's headers
     o += (size_t)tile::kWarps * 2 * 64;
     o += tile::kWarps * 2 * 8;
     o += 8 * 8;
@@ -749,6 +749,11 @@ int item_window_div() {
     return v;
 }
 
+int warp_item_min_rows() {
+    static const int v = [] { const char* e = std::getenv("HC_WARP_ITEM_ROWS"); return e ? std::max(1, std::atoi(e)) : 8; }();
+    return v;
+}
+
 // The order in which the persistent CTAs take the work items: row-major unless HC_ITEM_ORDER=blocks (read at every plan build)
 bool items_by_rows() { const char* e = std::getenv("HC_ITEM_ORDER"); return !(e && e[0] == 'b'); }
 
@@ -759,7 +764,7 @@ bool items_by_rows() { const char* e = std::getenv("HC_ITEM_ORDER"); return !(e 
 // a block run loops of nearly the same length; and a block stops being scheduled at the first row that starts
 // behind the block's furthest end, so lanes are not spent on the reference's first reject (:1252).
 // An item = (block, chunk of rows that can reach it). Items and blocks are appended to `items` / `colidx`.
-void build_items_range(hc_ctx* c, int w0, int w1, int n_ctas, std::vector<int4>& items, std::vector<int32_t>& colidx) {
+void build_items_range(hc_ctx* c, int w0, int w1, int n_ctas, bool warp_items, std::vector<int4>& items, std::vector<int32_t>& colidx) {
     const int nrows = w1 - w0;
     if (nrows <= 0 || w1 < 2) return;
     const int32_t* col0 = c->lay_col0.data() + (w0 - c->lay_begin);
@@ -815,6 +820,10 @@ void build_items_range(hc_ctx* c, int w0, int w1, int n_ctas, std::vector<int4>&
     }
     long long chunk = (total + (long long)n_ctas * 16 - 1) / ((long long)n_ctas * 16);
     chunk = std::max<long long>(32, std::min<long long>(chunk, 4096));
+    if (warp_items) {                            // streamed kernel: an item is taken by one warp, not by the 24 warps of a CTA
+        chunk = (total + (long long)n_ctas * tile::kWarps * 8 - 1) / ((long long)n_ctas * tile::kWarps * 8);
+        chunk = std::max<long long>(warp_item_min_rows(), std::min<long long>(chunk, 256));
+    }
     const size_t item0 = items.size();
     for (size_t b = 0; b < blks.size(); ++b)
         for (long long r = first[b]; r <= last[b]; r += chunk)
@@ -838,9 +847,9 @@ constexpr int kMaxWindows = 16;
 
 // The scoring plan of rows [row_begin,row_end) (needs compute_layout of the same range): row windows of about equal
 // numbers of adjacency words, each with its own work items.
-void build_plan(hc_ctx* c, int row_begin, int row_end, int n_ctas, bool windows) {
+void build_plan(hc_ctx* c, int row_begin, int row_end, int n_ctas, bool windows, bool warp_items = false) {
     if (c->plan_begin == row_begin && c->plan_end == row_end && c->plan_ctas == n_ctas && c->plan_windows == windows &&
-        c->plan_by_rows == items_by_rows()) return;
+        c->plan_by_rows == items_by_rows() && c->plan_warp_items == warp_items) return;
     c->items.clear();
     c->colidx.clear();
     c->wins.clear();
@@ -859,14 +868,14 @@ void build_plan(hc_ctx* c, int row_begin, int row_end, int n_ctas, bool windows)
         hc_ctx::Win win;
         win.r0 = r; win.r1 = r1;
         win.item0 = c->items.size();
-        build_items_range(c, r, r1, n_ctas, c->items, c->colidx);
+        build_items_range(c, r, r1, n_ctas, warp_items, c->items, c->colidx);
         win.n_items = c->items.size() - win.item0;
         win.word0 = c->lay_off[r - row_begin];
         win.n_words = c->lay_off[r1 - row_begin] - win.word0;
         c->wins.push_back(win);
         r = r1;
     }
-    c->plan_begin = row_begin; c->plan_end = row_end; c->plan_ctas = n_ctas; c->plan_windows = windows; c->plan_by_rows = items_by_rows();
+    c->plan_begin = row_begin; c->plan_end = row_end; c->plan_ctas = n_ctas; c->plan_windows = windows; c->plan_by_rows = items_by_rows(); c->plan_warp_items = warp_items;
 }
 
 // similarityCriterion's last lines (src/NewEdgeCalculator.cpp:1132-1140) on the host, with glibc's log10: the decision for
@@ -1117,7 +1126,7 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     // the host, while the copies and the device-side builds above are in flight (hc_score_band(0, n) finds them cached)
     if (p->n_reads > 1 && (tile_eligible(c) || tile2_eligible(c) || stream_eligible(c))) {
         compute_layout(c, 0, p->n_reads);
-        build_plan(c, 0, p->n_reads, c->sm_count, true);
+        build_plan(c, 0, p->n_reads, c->sm_count, true, !tile_eligible(c) && !tile2_eligible(c));
     }
     CU_TRY(c, cudaStreamSynchronize(c->stream));
     return HC_OK;
@@ -1218,7 +1227,7 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
             }
             if (per_sm < 1) { c->err = "hc_score_band: tiled kernel does not fit on an SM"; return HC_E_CUDA; }
             const int n_ctas = c->sm_count * per_sm;
-            build_plan(c, row_begin, row_end, n_ctas, detail == nullptr);
+            build_plan(c, row_begin, row_end, n_ctas, detail == nullptr, use_stream);
             const size_t n_items = c->items.size();
             if ((rc = grow(c, c->d_items, c->items_cap, std::max<size_t>(n_items, 1))) != HC_OK) return rc;
             CU_TRY(c, cudaMemcpyAsync(c->d_items, c->items.data(), sizeof(int4) * n_items, cudaMemcpyHostToDevice, c->stream));
@@ -1251,7 +1260,7 @@ static int score_band_impl(hc_ctx* c, int32_t row_begin, int32_t row_end, uint32
                 cudaStream_t ks = (k & 1) ? c->stream2 : c->stream;
                 if (w.n_items > 0) {
                     a.items = c->d_items + w.item0; a.n_items = (int)w.n_items; a.item_counter = c->d_item_counter + k;
-                    const int blocks = (int)std::min<size_t>(w.n_items, (size_t)n_ctas);
+                    const int blocks = (int)std::min<size_t>(use_stream ? (w.n_items + tile::kWarps - 1) / tile::kWarps : w.n_items, (size_t)n_ctas);
                     if (use_tile2 && split && map) tile2::score_tile2_kernel<true, true><<<blocks, threads, smem_bytes, ks>>>(a);
                     else if (use_tile2 && split) tile2::score_tile2_kernel<true, false><<<blocks, threads, smem_bytes, ks>>>(a);
                     else if (use_tile2 && map) tile2::score_tile2_kernel<false, true><<<blocks, threads, smem_bytes, ks>>>(a);

@@ -341,6 +341,57 @@ __device__ __forceinline__ void overlap(const Args& a, const int* hA, const int*
         TILE_MUL((AW) >> 24, (BW) >> 24, (x__ & 0x70000u) != 0u);                         \
     } while (0)
     for (;;) {
+        if (G) {
+            // -- streamed operands: the lane's own stream comes in 16-byte loads (eight columns; a 4-byte load per lane costs the
+            //    same 32 L1 wavefronts), the row's stream -- the same address in every lane -- in words. Single columns up to
+            //    the lane's next 16-byte boundary, eight per iteration from there, single columns for the rest of the run.
+            if (more && !qx) {
+                const int run = min(min(hi - ref + 1, nA - ca), nB - cb);
+                if (run >= 1) {
+                    const int ia = aoff + ca, ib = boff + cb;
+                    const uint16_t* qa16 = opsA + ia;
+                    const uint16_t* qb16 = reinterpret_cast<const uint16_t*>(opsB) + ib;
+                    int done = 0;
+                    bool stop = false;
+                    while (done < run && ((ib + done) & 7)) {
+                        const uint32_t ra = ldh<true>(qa16 + done), rb = ldh<true>(qb16 + done);
+                        if ((ra | rb) & 0x38u) { stop = true; break; }
+                        TILE_MUL(ra >> 8, rb >> 8, ((ra ^ rb) & 0x7u) != 0u);
+                        done++;
+                    }
+                    if (!stop && done + 8 <= run) {
+                        const uint32_t* pa = opsA32 + ((ia + done) >> 1);
+                        int sha = ((ia + done) & 1) * 16;
+                        asm volatile("" : "+r"(sha));
+                        const uint4* pb = reinterpret_cast<const uint4*>(qb16 + done);
+                        uint32_t a0 = __ldg(pa);
+                        uint4 v = __ldg(pb);
+                        for (;;) {
+                            const uint32_t a1 = __ldg(pa + 1), a2 = __ldg(pa + 2), a3 = __ldg(pa + 3), a4 = __ldg(pa + 4);
+                            const bool again = done + 16 <= run;
+                            uint4 vn = v;
+                            if (again) vn = __ldg(pb + 1);
+                            const uint32_t A01 = __funnelshift_r(a0, a1, sha), A23 = __funnelshift_r(a1, a2, sha);
+                            const uint32_t A45 = __funnelshift_r(a2, a3, sha), A67 = __funnelshift_r(a3, a4, sha);
+                            if ((A01 | A23 | A45 | A67 | v.x | v.y | v.z | v.w) & 0x00380038u) { stop = true; break; }
+                            TILE_MUL2(A01, v.x);
+                            TILE_MUL2(A23, v.y);
+                            TILE_MUL2(A45, v.z);
+                            TILE_MUL2(A67, v.w);
+                            done += 8; pa += 4; pb += 1; a0 = a4; v = vn;
+                            if (!again) break;
+                        }
+                    }
+                    while (done < run) {
+                        const uint32_t ra = ldh<true>(qa16 + done), rb = ldh<true>(qb16 + done);
+                        if ((ra | rb) & 0x38u) break;
+                        TILE_MUL(ra >> 8, rb >> 8, ((ra ^ rb) & 0x7u) != 0u);
+                        done++;
+                    }
+                    ca += done; cb += done; ref += done; cc += done;
+                }
+            }
+        } else
         // -- four (then two, then one) columns per iteration while both reads show M
         if (more && !qx) {
             const int run = min(min(hi - ref + 1, nA - ca), nB - cb);
@@ -487,7 +538,7 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
     size_t o = 0;
     double* Tsm = reinterpret_cast<double*>(smem + o);            o += ((size_t)2 * K * K * 8 + 15) & ~(size_t)15;
     uint32_t* progsm = reinterpret_cast<uint32_t*>(smem + o);     o += TP_COUNT * TP_WORDS * 4;
-    int* hBsm = reinterpret_cast<int*>(smem + o);                 o += 16 * 32 * 4;
+    int* hBsm = reinterpret_cast<int*>(smem + o);                 o += (size_t)(G ? nwarps : 1) * 16 * 32 * 4;
     uint32_t* tileB = reinterpret_cast<uint32_t*>(smem + o);      o += (size_t)a.maxw * 128;
     unsigned char* rowbuf = smem + o;                             o += (size_t)nwarps * 2 * (64 + a.abuf_bytes);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + o);       o += (size_t)nwarps * 2 * 8;
@@ -509,7 +560,10 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
     unsigned char* const mybuf0 = rowbuf + (size_t)(warp * 2) * bufstride;
     uint32_t parity = 0;       // bit k = phase parity of this warp's barrier k
     const unsigned char* Tb = reinterpret_cast<const unsigned char*>(Tsm);
-    const int* hB = hBsm + lane;
+    // G: nothing but the column headers is shared by the warps of a CTA, so every warp takes work items of its own (its
+    // own copy of the headers, no CTA-wide barrier: rows of a super-read round differ in length by an order of magnitude)
+    int* const hBmine = hBsm + (G ? warp * 16 * 32 : 0);
+    const int* hB = hBmine + lane;
 
     auto load_info = [&](int row, int r1) {
         RowInfo ri;
@@ -531,17 +585,33 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
         if (ob) bulk_g2s(mybuf0 + k * bufstride + 64, a.ops + ri.ops_off, ob, bar);
     };
 
+    if (G) __syncthreads();                      // tables and programs are in place
     for (;;) {
-        __syncthreads();
-        if (tid == 0) ctl[0] = atomicAdd(a.item_counter, 1);
-        __syncthreads();
-        const int item = ctl[0];
+        int item = 0;
+        if (G) {
+            if (lane == 0) item = atomicAdd(a.item_counter, 1);
+            item = __shfl_sync(FULL, item, 0);
+        } else {
+            __syncthreads();
+            if (tid == 0) ctl[0] = atomicAdd(a.item_counter, 1);
+            __syncthreads();
+            item = ctl[0];
+        }
         if (item >= a.n_items) break;
         const int4 it = a.items[item];
         const int blk = it.x, r0 = it.y, r1 = it.z;
         const int jmine = __ldg(a.colidx + (size_t)blk * 32 + lane);       // this lane's column read (every warp agrees)
         // ---- stage the 32 column reads: headers transposed, op streams interleaved word-wise
-        for (int f = warp; f < 16; f += nwarps) hBsm[f * 32 + lane] = jmine >= 0 ? __ldg(reinterpret_cast<const int*>(a.hdr + jmine) + f) : 0;
+        if (G) {
+#pragma unroll
+            for (int f4 = 0; f4 < 4; ++f4) {
+                const int4 v = jmine >= 0 ? __ldg(reinterpret_cast<const int4*>(a.hdr + jmine) + f4) : make_int4(0, 0, 0, 0);
+                hBmine[(4 * f4 + 0) * 32 + lane] = v.x; hBmine[(4 * f4 + 1) * 32 + lane] = v.y;
+                hBmine[(4 * f4 + 2) * 32 + lane] = v.z; hBmine[(4 * f4 + 3) * 32 + lane] = v.w;
+            }
+        } else {
+            for (int f = warp; f < 16; f += nwarps) hBsm[f * 32 + lane] = jmine >= 0 ? __ldg(reinterpret_cast<const int*>(a.hdr + jmine) + f) : 0;
+        }
         const uint32_t* opsB = tileB + lane;
         const uint16_t* rawB = a.ops + (jmine >= 0 ? (unsigned)__ldg(reinterpret_cast<const int*>(a.hdr + jmine) + 8) : 0u);
         if (G) {
@@ -560,11 +630,16 @@ __global__ void __launch_bounds__(kThreads, HC_TILE_MINBLOCKS) score_tile_kernel
                 }
             }
         }
-        if (tid == 0) ctl[1] = r0;
-        __syncthreads();
+        int next_row = r0;                           // G: the rows of the item are this warp's
+        if (G) __syncwarp();
+        else {
+            if (tid == 0) ctl[1] = r0;
+            __syncthreads();
+        }
 
         // ---- rows: two grabbed ahead, the next row's bytes in flight while this one is walked
         auto grab = [&]() {
+            if (G) return next_row++;
             int r = 0;
             if (lane == 0) r = atomicAdd(&ctl[1], 1);
             return __shfl_sync(FULL, r, 0);
