@@ -22,6 +22,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <mutex>
 #include <thread>
 #include <vector>
 
@@ -1513,6 +1514,71 @@ int hc_score_pairs(hc_ctx* c, const int32_t* pi, const int32_t* pj, int64_t npai
 }
 
 }  // extern "C"
+
+// ---- hc_score_pairs without any allocation --------------------------------------------------------------------------
+// The pair kernel's device-side scratch (the pair lists it reads and the result records it writes, which hc_score_pairs
+// keeps in grow-only cudaMalloc buffers) in a file-scope array: HC_STATIC_MAX_PAIRS * (48 + 4 + 4) bytes = 896 KiB, held by
+// every GPU that loads the library until the process ends. In host code `g_pairs_scratch` is only a stand-in for the
+// symbol; the device address comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) unsigned char g_pairs_scratch[(size_t)HC_STATIC_MAX_PAIRS * (sizeof(hc_pair_result) + 2 * sizeof(int32_t))];
+
+namespace {
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_static_mu;
+unsigned char* g_static_addr[kMaxStaticDevices] = {};
+
+// Device address of g_pairs_scratch on c->device (the current device on entry).
+int static_scratch(hc_ctx* c, unsigned char** out) {
+    if (c->device < 0 || c->device >= kMaxStaticDevices) { c->err = "hc_score_pairs_static: device ordinal beyond 63"; return HC_E_INVALID; }
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_addr[c->device]) {
+        void* ptr = nullptr;
+        CU_TRY(c, cudaGetSymbolAddress(&ptr, g_pairs_scratch));
+        if (!ptr) { c->err = "hc_score_pairs_static: cudaGetSymbolAddress gave no address"; return HC_E_CUDA; }
+        g_static_addr[c->device] = static_cast<unsigned char*>(ptr);
+    }
+    *out = g_static_addr[c->device];
+    return HC_OK;
+}
+}  // namespace
+
+extern "C" int hc_score_pairs_static(hc_ctx* c, const int32_t* pi, const int32_t* pj, int64_t npairs, hc_pair_result* out) {
+    if (!c || npairs < 0 || (npairs > 0 && (!pi || !pj || !out))) return HC_E_INVALID;
+    if (!c->d_hdr) { c->err = "hc_score_pairs_static: no batch uploaded"; return HC_E_STATE; }
+    if (npairs > HC_STATIC_MAX_PAIRS) {
+        c->err = "hc_score_pairs_static: " + std::to_string((long long)npairs) + " pairs in one call, the static scratch holds " +
+                 std::to_string((int)HC_STATIC_MAX_PAIRS) + " (HC_STATIC_MAX_PAIRS); split the list or use hc_score_pairs";
+        return HC_E_INVALID;
+    }
+    for (int64_t k = 0; k < npairs; ++k)
+        if (pi[k] < 0 || pi[k] >= c->n_reads || pj[k] < 0 || pj[k] >= c->n_reads) { c->err = "hc_score_pairs_static: read index out of range"; return HC_E_INVALID; }
+    if (npairs == 0) return HC_OK;
+    CU_TRY(c, cudaSetDevice(c->device));
+    unsigned char* base = nullptr;
+    const int rc = static_scratch(c, &base);
+    if (rc != HC_OK) return rc;
+    hc_pair_result* d_res = reinterpret_cast<hc_pair_result*>(base);
+    int32_t* d_pi = reinterpret_cast<int32_t*>(base + (size_t)HC_STATIC_MAX_PAIRS * sizeof(hc_pair_result));
+    int32_t* d_pj = d_pi + HC_STATIC_MAX_PAIRS;
+    // the array keeps the last call's records: the slots of this call start from zero
+    CU_TRY(c, cudaMemsetAsync(d_res, 0, sizeof(hc_pair_result) * npairs, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(d_pi, pi, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(d_pj, pj, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, c->stream));
+    const int threads = 128;
+    const int blocks = (int)std::min<long long>((npairs + threads - 1) / threads, (long long)c->sm_count * 16);
+    score_pairs_kernel<<<blocks, threads, 0, c->stream>>>(dev_params(c), c->d_hdr, c->d_ops, d_pi, d_pj, npairs, d_res);
+    CU_TRY(c, cudaGetLastError());
+    CU_TRY(c, cudaMemcpyAsync(out, d_res, sizeof(hc_pair_result) * npairs, cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    const DevParams P = dev_params(c);                   // near-threshold pairs: the host's decision, as in hc_score_pairs
+    for (int64_t k = 0; k < npairs; ++k) {
+        if (!out[k].ambiguous) continue;
+        const bool cl1 = c->ncov_flags[pi[k]] & HC_FLAG_IS_CLIQUE, cl2 = c->ncov_flags[pj[k]] & HC_FLAG_IS_CLIQUE;
+        const double cutoff = P.log_cutoff[(cl1 && cl2) ? 0 : ((cl1 || cl2) ? 1 : 2)];
+        out[k].edge = host_decide(c, out[k].probM, out[k].prob0, out[k].cc, out[k].tc, cutoff, &out[k].score) ? 1 : 0;
+    }
+    return HC_OK;
+}
 
 // ---- several GPUs behind one handle ------------------------------------------------------------------------------
 struct hc_multi {

@@ -19,7 +19,9 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("HC_LIBHCGPU") or os.path.join(_HERE, "libhcgpu.so")     # HC_LIBHCGPU: an experiment build of the same library
 
 HC_OK = 0
+HC_E_INVALID = -1
 KERNEL_AUTO, KERNEL_GENERIC, KERNEL_TILED, KERNEL_TILED2, KERNEL_STREAMED = 0, 1, 2, 3, 4
+STATIC_MAX_PAIRS = 16384                                  # include/hc_edge.h: HC_STATIC_MAX_PAIRS
 ST_REJECT_COV, ST_REJECT_LAYOUT, ST_WALKED, ST_UNDEFINED = 0, 1, 2, 3
 
 
@@ -89,6 +91,7 @@ def load_library():
         L.hc_score_band.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32,
                                     C.c_void_p]
         L.hc_score_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+        L.hc_score_pairs_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
         L.hc_score_band_detail.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
         L.hc_set_kernel.argtypes = [C.c_void_p, C.c_int32]
         L.hc_last_kernel.argtypes = [C.c_void_p]
@@ -461,6 +464,15 @@ class NewEdgeCalculator(EdgeCalculator):
         pj = np.ascontiguousarray(pj, np.int32)
         out = np.zeros(pi.shape[0], PAIR_RESULT_DTYPE)
         self._check(self.L.hc_score_pairs(self._ctx, _ptr(pi), _ptr(pj), pi.shape[0], _ptr(out)), "hc_score_pairs")
+        return out
+
+    def score_pairs_static(self, pi, pj) -> np.ndarray:
+        """hc_score_pairs_static: the same results from a static device scratch array, no device allocation (at most
+        STATIC_MAX_PAIRS pairs per call)."""
+        pi = np.ascontiguousarray(pi, np.int32)
+        pj = np.ascontiguousarray(pj, np.int32)
+        out = np.zeros(pi.shape[0], PAIR_RESULT_DTYPE)
+        self._check(self.L.hc_score_pairs_static(self._ctx, _ptr(pi), _ptr(pj), pi.shape[0], _ptr(out)), "hc_score_pairs_static")
         return out
 
     def tables(self):

@@ -216,6 +216,17 @@ int hc_last_kernel(const hc_ctx* ctx);
 /* Scores an explicit list of ordered pairs (ap1 = pi[k], ap2 = pj[k]), full detail per pair. */
 int hc_score_pairs(hc_ctx* ctx, const int32_t* pi, const int32_t* pj, int64_t npairs, hc_pair_result* out);
 
+/* hc_score_pairs for callers that must not allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc). No counterpart in the reference.
+ * Same inputs, outputs and results as hc_score_pairs; the kernel's device-side scratch (the pair lists and the result
+ * records) lives in a static device array of HC_STATIC_MAX_PAIRS * 56 bytes = 896 KiB that every GPU which loads the
+ * library holds until the process exits. The call makes no cudaMalloc / cudaFree and calls no allocating library routine;
+ * npairs > HC_STATIC_MAX_PAIRS fails with HC_E_INVALID and a message. All calls on a device share the one array (it keeps
+ * the previous call's contents; the slots a call uses are cleared first), so calls that overlap on the same GPU -- from
+ * two contexts or two host threads -- race: serialise them. The batch must already be resident (hc_upload allocates). */
+#define HC_STATIC_MAX_PAIRS 16384
+int hc_score_pairs_static(hc_ctx* ctx, const int32_t* pi, const int32_t* pj, int64_t npairs, hc_pair_result* out);
+
 /* ---- QuasispeciesEdgeCalculator (src/QuasispeciesEdgeCalculator.cpp), the reference's older scorer: same
  * EdgeCalculator interface (src/EdgeCalculator.h:29), constructor src/QuasispeciesEdgeCalculator.h:57. It runs on
  * the batch hc_upload made resident and uses the context's allele-frequency map (its SIMPSON_MAP; entries equal to
