@@ -518,7 +518,7 @@ struct hc_ctx {
     // scoring plan of the last range: row windows with their work items (build_plan)
     struct Win { int r0, r1; size_t item0, n_items; long long word0, n_words; };
     std::vector<int4> items; std::vector<int32_t> colidx; std::vector<Win> wins;
-    int plan_begin = -1, plan_end = -1, plan_ctas = 0; bool plan_windows = false, plan_by_rows = false, plan_warp_items = false;
+    int plan_begin = -1, plan_end = -1, plan_ctas = 0; bool plan_windows = false, plan_by_rows = false, plan_warp_items = false, plan_sig = false;
     cudaStream_t copy_stream = nullptr;                     // D2H of finished row windows, beside the compute streams
     cudaStream_t stream2 = nullptr;                         // odd row windows: their CTAs fill the SMs the previous window's tail frees
     cudaEvent_t ev_go = nullptr, ev_join = nullptr;
@@ -527,6 +527,7 @@ struct hc_ctx {
     std::vector<hc_ambiguous> amb_host;                     // near-threshold pairs of the last pass, re-decided
     int32_t* d_colidx = nullptr; size_t colidx_cap = 0;
     std::vector<int32_t> cov_last, cov_first_smin; std::vector<uint8_t> is_single;
+    std::vector<uint32_t> indel_sig;                        // per read: hash of its (position, I / D) events, 0 = none (build_items_range)
     std::string err;
 };
 
@@ -755,15 +756,30 @@ int warp_item_min_rows() {
     return v;
 }
 
+// Column reads of a window are grouped by indel signature before the end sort (HC_ITEM_SIG=0 turns it off); a signature
+// carried by fewer than item_sig_min() reads of the window (HC_ITEM_SIG_MIN) goes to the window's common "rare" group.
+bool item_sig() { const char* e = std::getenv("HC_ITEM_SIG"); return !(e && e[0] == '0'); }     // read at every plan build
+int item_sig_min() {
+    static const int v = [] { const char* e = std::getenv("HC_ITEM_SIG_MIN"); return e ? std::max(1, std::atoi(e)) : 8; }();
+    return v;
+}
+
 // The order in which the persistent CTAs take the work items: row-major unless HC_ITEM_ORDER=blocks (read at every plan build)
 bool items_by_rows() { const char* e = std::getenv("HC_ITEM_ORDER"); return !(e && e[0] == 'b'); }
 
 // Work items of the tiled kernels for rows [w0,w1) of the laid-out range (c->lay_begin .. c->lay_end).
 // Columns (the earlier reads j) are taken in windows of W consecutive reads; inside a window they are sorted by
-// (single/paired, last covered position) and cut into blocks of 32. For a later row read i the length of the
-// lock-step loop against j depends on min(end_i, end_j) but not on j's start (j starts first), so the 32 lanes of
+// (single/paired, indel signature, last covered position) and cut into blocks of 32. For a later row read i the length
+// of the lock-step loop against j depends on min(end_i, end_j) but not on j's start (j starts first), so the 32 lanes of
 // a block run loops of nearly the same length; and a block stops being scheduled at the first row that starts
 // behind the block's furthest end, so lanes are not spent on the reference's first reject (:1252).
+// The indel signature: a walk stops at the first column where one read shows an insertion or deletion the other lacks
+// (overlapCheckgap's gap, :173-231) -- on C2 30 % of the walked pairs near a haplotype's indel -- and a warp runs as long as
+// its longest lane. Column reads that carry the same indels stop against a given row read at the same column or not at
+// all, so grouping them lets whole warps stop (CPU simulation over the oracle's per-pair column counts, C2 rows 50000-50300:
+// lane-columns lost to stopped lanes 22.5 % -> 8.5-11 %). Which reads share a block changes no result. Measured on one B200:
+// C4 (every read covers two of the ten haplotype indels) 19.61 -> 17.44 s per pass at full size, 839 -> 752 ms at 200k
+// fragments; C2 (one read in eleven carries an indel) 56.6 -> 56.9 ms (profiles/r02_sig_sweep.json).
 // An item = (block, chunk of rows that can reach it). Items and blocks are appended to `items` / `colidx`.
 void build_items_range(hc_ctx* c, int w0, int w1, int n_ctas, bool warp_items, std::vector<int4>& items, std::vector<int32_t>& colidx) {
     const int nrows = w1 - w0;
@@ -787,20 +803,43 @@ void build_items_range(hc_ctx* c, int w0, int w1, int n_ctas, bool warp_items, s
     const size_t base_blk = colidx.size() / 32;
     colidx.resize((base_blk + blk0[nwin]) * 32, -1);
     int32_t* cix = colidx.data() + base_blk * 32;
+    // not for the streamed kernel's per-warp items: on super-read rounds, where nearly every read carries indels of its own,
+    // the grouping costs the end sort more than it gains (C5 6.72 -> 6.97 ms, C5r 1.12 -> 1.14 ms)
+    const bool by_sig = item_sig() && !warp_items && c->indel_sig.size() == (size_t)c->n_reads;
+    const size_t sig_min = (size_t)item_sig_min();
     parallel_ranges(nwin, 16, [&](int wa, int wb) {
-        std::vector<uint64_t> order;                 // key = single/paired, last covered position, read index
+        // key = (single/paired, signature group), (last covered position, read index)
+        std::vector<std::pair<uint64_t, uint64_t>> order;
+        std::vector<uint32_t> sigs;
         for (int w = wa; w < wb; ++w) {
             const int c0 = jlo + w * W, c1 = std::min(c0 + W, jhi);
             order.resize(c1 - c0);
-            for (int j = c0; j < c1; ++j)
-                order[j - c0] = ((uint64_t)(c->is_single[j] ? 0 : 1) << 63) |
-                                ((uint64_t)(uint32_t)(c->cov_last[j] + (1 << 30)) << 32) | (uint32_t)j;
+            sigs.clear();
+            if (by_sig) {                            // signatures carried by at least sig_min reads of this window, sorted
+                for (int j = c0; j < c1; ++j) if (c->indel_sig[j]) sigs.push_back(c->indel_sig[j]);
+                std::sort(sigs.begin(), sigs.end());
+                size_t keep = 0;
+                for (size_t a = 0; a < sigs.size();) {
+                    size_t b = a;
+                    while (b < sigs.size() && sigs[b] == sigs[a]) ++b;
+                    if (b - a >= sig_min) sigs[keep++] = sigs[a];
+                    a = b;
+                }
+                sigs.resize(keep);
+            }
+            for (int j = c0; j < c1; ++j) {
+                uint64_t group = 0;                  // no indel
+                if (by_sig && c->indel_sig[j])
+                    group = std::binary_search(sigs.begin(), sigs.end(), c->indel_sig[j]) ? c->indel_sig[j] : 0xffffffffull;
+                order[j - c0] = std::make_pair(((uint64_t)(c->is_single[j] ? 0 : 1) << 32) | group,
+                                               ((uint64_t)(uint32_t)(c->cov_last[j] + (1 << 30)) << 32) | (uint32_t)j);
+            }
             std::sort(order.begin(), order.end());
             for (size_t p = 0; p < order.size(); p += 32) {
                 Blk b{INT32_MAX, INT32_MIN};
                 const size_t bi = blk0[w] + p / 32;
                 for (size_t q = p; q < p + 32 && q < order.size(); ++q) {
-                    const int j = (int)(uint32_t)order[q];
+                    const int j = (int)(uint32_t)order[q].second;
                     cix[bi * 32 + (q - p)] = j;
                     b.first_j = std::min(b.first_j, j);
                     b.maxend = std::max(b.maxend, c->cov_last[j]);
@@ -850,7 +889,7 @@ constexpr int kMaxWindows = 16;
 // numbers of adjacency words, each with its own work items.
 void build_plan(hc_ctx* c, int row_begin, int row_end, int n_ctas, bool windows, bool warp_items = false) {
     if (c->plan_begin == row_begin && c->plan_end == row_end && c->plan_ctas == n_ctas && c->plan_windows == windows &&
-        c->plan_by_rows == items_by_rows() && c->plan_warp_items == warp_items) return;
+        c->plan_by_rows == items_by_rows() && c->plan_warp_items == warp_items && c->plan_sig == item_sig()) return;
     c->items.clear();
     c->colidx.clear();
     c->wins.clear();
@@ -876,7 +915,7 @@ void build_plan(hc_ctx* c, int row_begin, int row_end, int n_ctas, bool windows,
         c->wins.push_back(win);
         r = r1;
     }
-    c->plan_begin = row_begin; c->plan_end = row_end; c->plan_ctas = n_ctas; c->plan_windows = windows; c->plan_by_rows = items_by_rows(); c->plan_warp_items = warp_items;
+    c->plan_begin = row_begin; c->plan_end = row_end; c->plan_ctas = n_ctas; c->plan_windows = windows; c->plan_by_rows = items_by_rows(); c->plan_warp_items = warp_items; c->plan_sig = item_sig();
 }
 
 // similarityCriterion's last lines (src/NewEdgeCalculator.cpp:1132-1140) on the host, with glibc's log10: the decision for
@@ -1123,6 +1162,33 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     }
     int smin = INT32_MAX;
     for (int r = p->n_reads - 1; r >= 0; --r) { smin = std::min(smin, c->cov_first[r]); c->cov_first_smin[r] = smin; }
+    // indel signatures (build_items_range groups column reads by them): FNV-1a over the (reference position, op) of every I
+    // and D op; only segments flagged "not plain" are read
+    c->indel_sig.assign((size_t)p->n_reads, 0u);
+    if (p->n_reads > 0)
+        hc::parallel_ranges(p->n_reads, 8192, [&](int r0, int r1) {
+            for (int r = r0; r < r1; ++r) {
+                const hc_read_hdr& h = p->hdr[r];
+                if (!((h.seg_flags[0] | h.seg_flags[1]) & HC_SEG_NOT_PLAIN)) continue;
+                uint32_t f = 2166136261u;
+                bool any = false;
+                for (int sg = 0; sg < 2; ++sg) {
+                    if (!(h.seg_flags[sg] & HC_SEG_NOT_PLAIN)) continue;
+                    const uint16_t* o = p->ops + h.ops_off[sg];
+                    int pos = h.ext[2 * sg];                      // clip-extended start: every op but I takes one position
+                    for (int k = 0; k < h.n_ops[sg]; ++k) {
+                        const uint32_t op = HC_REC_OP((uint32_t)o[k]);
+                        if (op == HC_OP_I || op == HC_OP_D) {
+                            f = (f ^ (uint32_t)pos) * 16777619u;
+                            f = (f ^ op) * 16777619u;
+                            any = true;
+                        }
+                        if (op != HC_OP_I) ++pos;
+                    }
+                }
+                if (any) c->indel_sig[r] = f ? f : 1u;
+            }
+        });
     // the band layout and the tiled kernels' work items of the whole batch depend on the headers only: computed here, on
     // the host, while the copies and the device-side builds above are in flight (hc_score_band(0, n) finds them cached)
     if (p->n_reads > 1 && (tile_eligible(c) || tile2_eligible(c) || stream_eligible(c))) {

@@ -404,6 +404,32 @@ def test_C4_shaped_amplicon_every_band_slot(kernel):
     _tiled_detail_vs_oracle(b, kw, "C4-shape-prob0", kernel)
 
 
+@pytest.mark.parametrize("kernel", [pytest.param(edge.KERNEL_TILED, id="tiled"), pytest.param(edge.KERNEL_TILED2, id="tiled2")])
+def test_grouping_column_reads_by_indel_signature_changes_no_word(kernel, monkeypatch):
+    """The column reads of a window are grouped by indel signature before the end sort (build_items_range; HC_ITEM_SIG=0
+    turns it off, read at every plan build). Which reads share a block of 32 lanes is scheduling only: the adjacency words and
+    every counter are the same with and without it, on a C4-shaped set where one read in four carries an indel."""
+    cfg = {k: v for k, v in synth.CONFIGS["C4"].items() if k != "n_frag"}
+    b = synth.quasispecies(4000, seed=45, **cfg)
+    has_indel = np.array([(b"I" in b.cig[int(b.cig_off[2 * r]):int(b.cig_off[2 * r + 1] + b.cig_len[2 * r + 1])].tobytes()) or
+                          (b"D" in b.cig[int(b.cig_off[2 * r]):int(b.cig_off[2 * r + 1] + b.cig_len[2 * r + 1])].tobytes())
+                          for r in range(b.n)])
+    assert 0.2 < has_indel.mean() < 0.98
+    calc = edge.NewEdgeCalculator(noProb0=True, maxPosition=b.max_position() + 10)
+    calc.upload(b)
+    calc.set_kernel(kernel)
+    res = {}
+    for sig in ("1", "0"):
+        monkeypatch.setenv("HC_ITEM_SIG", sig)
+        a = calc.score_band()
+        assert calc.last_kernel() == kernel
+        res[sig] = (a.words.copy(), {k: a.stats[k] for k in ("pairs_total", "pairs_scored", "pairs_walked", "edges", "sum_cc", "sum_tc", "undefined")})
+    assert (res["1"][0] == res["0"][0]).all() and res["1"][1] == res["0"][1]
+    assert res["1"][1]["edges"] > 100_000
+    calc.set_kernel(edge.KERNEL_GENERIC)
+    assert (calc.score_band().words == res["1"][0]).all()
+
+
 def test_near_threshold_pairs_are_decided_by_glibc_log10():
     """The device's log10 is not glibc's. Pairs whose score is within ambiguity_rel_tol of the threshold are listed by the
     kernel and re-decided on the host exactly as similarityCriterion does (src/NewEdgeCalculator.cpp:1127-1140). Here the
