@@ -807,14 +807,17 @@ void build_items_range(hc_ctx* c, int w0, int w1, int n_ctas, bool warp_items, s
     // the grouping costs the end sort more than it gains (C5 6.72 -> 6.97 ms, C5r 1.12 -> 1.14 ms)
     const bool by_sig = item_sig() && !warp_items && c->indel_sig.size() == (size_t)c->n_reads;
     const size_t sig_min = (size_t)item_sig_min();
-    parallel_ranges(nwin, 16, [&](int wa, int wb) {
-        // key = (single/paired, signature group), (last covered position, read index)
-        std::vector<std::pair<uint64_t, uint64_t>> order;
+    parallel_ranges(nwin, 4, [&](int wa, int wb) {
+        // key = single/paired (bit 63) | signature group (12 bits) | last covered position above the window's lowest (27 bits) |
+        // read index inside the window (12 bits: W <= 4096)
+        std::vector<uint64_t> order;
         std::vector<uint32_t> sigs;
         for (int w = wa; w < wb; ++w) {
             const int c0 = jlo + w * W, c1 = std::min(c0 + W, jhi);
             order.resize(c1 - c0);
             sigs.clear();
+            int lowest = INT32_MAX;
+            for (int j = c0; j < c1; ++j) lowest = std::min(lowest, c->cov_last[j]);
             if (by_sig) {                            // signatures carried by at least sig_min reads of this window, sorted
                 for (int j = c0; j < c1; ++j) if (c->indel_sig[j]) sigs.push_back(c->indel_sig[j]);
                 std::sort(sigs.begin(), sigs.end());
@@ -825,21 +828,23 @@ void build_items_range(hc_ctx* c, int w0, int w1, int n_ctas, bool warp_items, s
                     if (b - a >= sig_min) sigs[keep++] = sigs[a];
                     a = b;
                 }
-                sigs.resize(keep);
+                sigs.resize(keep);                   // at most W / sig_min <= 4096 groups
             }
             for (int j = c0; j < c1; ++j) {
                 uint64_t group = 0;                  // no indel
-                if (by_sig && c->indel_sig[j])
-                    group = std::binary_search(sigs.begin(), sigs.end(), c->indel_sig[j]) ? c->indel_sig[j] : 0xffffffffull;
-                order[j - c0] = std::make_pair(((uint64_t)(c->is_single[j] ? 0 : 1) << 32) | group,
-                                               ((uint64_t)(uint32_t)(c->cov_last[j] + (1 << 30)) << 32) | (uint32_t)j);
+                if (by_sig && c->indel_sig[j]) {
+                    const auto it = std::lower_bound(sigs.begin(), sigs.end(), c->indel_sig[j]);
+                    group = (it != sigs.end() && *it == c->indel_sig[j]) ? std::min<uint64_t>((uint64_t)(it - sigs.begin()) + 1, 4094) : 4095;
+                }
+                const uint64_t rel_end = std::min<uint64_t>((uint64_t)((long long)c->cov_last[j] - lowest), (1ull << 27) - 1);
+                order[j - c0] = ((uint64_t)(c->is_single[j] ? 0 : 1) << 63) | (group << 39) | (rel_end << 12) | (uint64_t)(j - c0);
             }
             std::sort(order.begin(), order.end());
             for (size_t p = 0; p < order.size(); p += 32) {
                 Blk b{INT32_MAX, INT32_MIN};
                 const size_t bi = blk0[w] + p / 32;
                 for (size_t q = p; q < p + 32 && q < order.size(); ++q) {
-                    const int j = (int)(uint32_t)order[q].second;
+                    const int j = c0 + (int)(order[q] & 4095ull);
                     cix[bi * 32 + (q - p)] = j;
                     b.first_j = std::min(b.first_j, j);
                     b.maxend = std::max(b.maxend, c->cov_last[j]);
@@ -1165,8 +1170,8 @@ int hc_upload(hc_ctx* c, const hc_packed* p) {
     // indel signatures (build_items_range groups column reads by them): FNV-1a over the (reference position, op) of every I
     // and D op; only segments flagged "not plain" are read
     c->indel_sig.assign((size_t)p->n_reads, 0u);
-    if (p->n_reads > 0)
-        hc::parallel_ranges(p->n_reads, 8192, [&](int r0, int r1) {
+    if (p->n_reads > 0 && (tile_eligible(c) || tile2_eligible(c)))      // the streamed kernel's per-warp items do not use them
+        hc::parallel_ranges(p->n_reads, 1024, [&](int r0, int r1) {
             for (int r = r0; r < r1; ++r) {
                 const hc_read_hdr& h = p->hdr[r];
                 if (!((h.seg_flags[0] | h.seg_flags[1]) & HC_SEG_NOT_PLAIN)) continue;
