@@ -804,7 +804,7 @@ void build_items_range(hc_ctx* c, int w0, int w1, int n_ctas, bool warp_items, s
     colidx.resize((base_blk + blk0[nwin]) * 32, -1);
     int32_t* cix = colidx.data() + base_blk * 32;
     // not for the streamed kernel's per-warp items: on super-read rounds, where nearly every read carries indels of its own,
-    // the grouping costs the end sort more than it gains (C5 6.72 -> 6.97 ms, C5r 1.12 -> 1.14 ms)
+    // the grouping costs the end sort more than it gains (C5 6.72 -> 6.97 ms)
     const bool by_sig = item_sig() && !warp_items && c->indel_sig.size() == (size_t)c->n_reads;
     const size_t sig_min = (size_t)item_sig_min();
     parallel_ranges(nwin, 4, [&](int wa, int wb) {
